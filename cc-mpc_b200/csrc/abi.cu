@@ -1,0 +1,30 @@
+// abi.cu - version, last-error string and launch checking of libccmpc.
+#include <stdarg.h>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace ccmpc {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int check_launch(const char* what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        set_error("%s: %s", what, cudaGetErrorString(e));
+        return CCMPC_E_LAUNCH;
+    }
+    return CCMPC_OK;
+}
+
+}  // namespace ccmpc
+
+extern "C" int ccmpc_version(void) { return CCMPC_VERSION; }
+extern "C" const char* ccmpc_last_error_string(void) { return ccmpc::g_err; }

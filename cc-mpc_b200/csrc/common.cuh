@@ -1,0 +1,246 @@
+// common.cuh - shared device helpers of libccmpc (sm_100a).
+//
+// The 2x2 algebra of the reference path written as scalar fp64 device code:
+//   mvoe_beta / mvoe_q     makeconstraint.py:7-38   (compute_mvoe)
+//   tangent_pick           makeconstraint.py:134-207 (tangent_lines_of_slope_m,
+//                          distance_point_to_line, choose_closest_tangent)
+//   lower_bound_prob       makeconstraint.py:282-303 (compute_lower_bound)
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/ccmpc.h"
+
+namespace ccmpc {
+
+void set_error(const char* fmt, ...);
+int check_launch(const char* what);
+
+#define CCMPC_REQUIRE(cond, ...)                \
+    do {                                        \
+        if (!(cond)) {                          \
+            ccmpc::set_error(__VA_ARGS__);      \
+            return CCMPC_E_ARG;                 \
+        }                                       \
+    } while (0)
+
+struct Sym2 {
+    double xx, xy, yy;
+};
+
+__device__ __forceinline__ Sym2 ld_sym3(const double* p) { return Sym2{p[0], p[1], p[2]}; }
+__device__ __forceinline__ void st_sym3(double* p, const Sym2& s) {
+    p[0] = s.xx; p[1] = s.xy; p[2] = s.yy;
+}
+
+// a*b - c*d with one rounding error in the dominant term (Kahan).
+__device__ __forceinline__ double diff_of_products(double a, double b, double c, double d) {
+    double cd = c * d;
+    double err = fma(-c, d, cd);
+    double dop = fma(a, b, -cd);
+    return dop + err;
+}
+
+__device__ __forceinline__ double det2(const Sym2& s) { return diff_of_products(s.xx, s.yy, s.xy, s.xy); }
+
+// ---------------------------------------------------------------------------
+// MVOE fixed point (makeconstraint.py:21-32).
+//
+// With lam_1, lam_2 = eig(Sigma1^-1 Sigma2), tr = lam_1 + lam_2, dt = lam_1 lam_2:
+//   sum 1/(1+b lam) / sum lam/(1+b lam) = (2 + b tr) / (tr + 2 b dt)
+// (multiply through by (1+b lam_1)(1+b lam_2)), so the reference's iterate
+// sequence needs only trace and determinant of Sigma1^-1 Sigma2 and ONE
+// division + ONE square root per iteration instead of 4 divisions + 1 sqrt.
+// `.real` of a complex-conjugate eigenpair (makeconstraint.py:21) is tr/2 for
+// both, i.e. dt := tr^2/4 when the discriminant is negative.
+// ---------------------------------------------------------------------------
+struct MvoeSpectrum {
+    double tr, dt;
+    int status;
+};
+
+__device__ __forceinline__ MvoeSpectrum mvoe_spectrum(const Sym2& s1, const Sym2& s2) {
+    MvoeSpectrum sp;
+    double d1 = det2(s1);
+    sp.status = (d1 == 0.0 || !isfinite(d1)) ? CCMPC_ST_SINGULAR : CCMPC_ST_OK;
+    double inv = 1.0 / d1;
+    // trace(Sigma1^-1 Sigma2) = (s1.yy s2.xx - 2 s1.xy s2.xy + s1.xx s2.yy) / det(Sigma1)
+    double num = fma(s1.yy, s2.xx, fma(-2.0 * s1.xy, s2.xy, s1.xx * s2.yy));
+    sp.tr = num * inv;
+    sp.dt = det2(s2) * inv;
+    double disc = fma(sp.tr, sp.tr, -4.0 * sp.dt);
+    if (disc < 0.0) sp.dt = 0.25 * sp.tr * sp.tr;
+    return sp;
+}
+
+// Footprint fit: Sigma2 = r2 * I.
+__device__ __forceinline__ MvoeSpectrum mvoe_spectrum_iso(const Sym2& s1, double r2) {
+    MvoeSpectrum sp;
+    double d1 = det2(s1);
+    sp.status = (d1 == 0.0 || !isfinite(d1)) ? CCMPC_ST_SINGULAR : CCMPC_ST_OK;
+    double inv = 1.0 / d1;
+    sp.tr = r2 * (s1.xx + s1.yy) * inv;
+    sp.dt = r2 * r2 * inv;
+    double disc = fma(sp.tr, sp.tr, -4.0 * sp.dt);
+    if (disc < 0.0) sp.dt = 0.25 * sp.tr * sp.tr;
+    return sp;
+}
+
+// Returns beta; iters = number of fixed-point evaluations (reference loop count).
+__device__ __forceinline__ double mvoe_beta(const MvoeSpectrum& sp, double tol, int maxiter, int accel,
+                                            int& iters, int& status) {
+    double beta = 1.0;
+    const double tr = sp.tr, dt2 = 2.0 * sp.dt;
+    int it = 0;
+    if (accel) {
+        // float32 warm start: same map, stopped at a float-level tolerance.
+        float b = 1.0f;
+        const float trf = (float)tr, dtf = (float)dt2;
+        for (int k = 0; k < 64; ++k) {
+            float nb = sqrtf(__fdividef(fmaf(b, trf, 2.0f), fmaf(b, dtf, trf)));
+            bool close = fabsf(nb - b) < 1e-5f * nb;
+            b = nb;
+            if (close) break;
+        }
+        if (isfinite(b) && b > 0.0f) beta = (double)b;
+    }
+    bool converged = false;
+    for (; it < maxiter;) {
+        ++it;
+        double nb = sqrt(fma(beta, tr, 2.0) / fma(beta, dt2, tr));
+        converged = fabs(nb - beta) < tol;
+        beta = nb;
+        if (converged) break;
+    }
+    iters = it;
+    if (!converged && status == CCMPC_ST_OK) status = CCMPC_ST_NOT_CONVERGED;
+    return beta;
+}
+
+// Q = (1 + 1/beta) Sigma1 + (1 + beta) Sigma2   (makeconstraint.py:35)
+__device__ __forceinline__ Sym2 mvoe_q(const Sym2& s1, const Sym2& s2, double beta) {
+    double a = 1.0 + 1.0 / beta, b = 1.0 + beta;
+    return Sym2{fma(a, s1.xx, b * s2.xx), fma(a, s1.xy, b * s2.xy), fma(a, s1.yy, b * s2.yy)};
+}
+
+__device__ __forceinline__ Sym2 mvoe_q_iso(const Sym2& s1, double r2, double beta) {
+    double a = 1.0 + 1.0 / beta, b = (1.0 + beta) * r2;
+    return Sym2{fma(a, s1.xx, b), a * s1.xy, fma(a, s1.yy, b)};
+}
+
+// ---------------------------------------------------------------------------
+// Tangents of slope m (makeconstraint.py:134-207).  n = [-m, 1].
+// Returns best_idx (0: d = n.mu + c sqrt(n^T S n), 1: minus) or -1 when
+// n^T S n <= 0 (the reference returns no tangent).  const_idx >= 0 forces it.
+// ---------------------------------------------------------------------------
+struct Tangent {
+    double d_plus, d_minus, dist0, dist1, d_star;
+    int idx;
+};
+
+__device__ __forceinline__ Tangent tangent_pick(double mux, double muy, const Sym2& S, double c, double m,
+                                                double ax, double ay, int const_idx) {
+    Tangent t;
+    const double n0 = -m, n1 = 1.0;
+    // n @ (Sigma @ n)
+    double sx = fma(S.xx, n0, S.xy * n1);
+    double sy = fma(S.xy, n0, S.yy * n1);
+    double q = fma(n0, sx, n1 * sy);
+    if (!(q > 0.0)) {
+        t.idx = -1;
+        t.d_plus = t.d_minus = t.dist0 = t.dist1 = t.d_star = __longlong_as_double(0x7ff8000000000000LL);
+        return t;
+    }
+    double proj = fma(n0, mux, n1 * muy);
+    double half = c * sqrt(q);
+    t.d_plus = proj + half;
+    t.d_minus = proj - half;
+    double na = fma(n0, ax, n1 * ay);
+    double nrm = sqrt(fma(m, m, 1.0));
+    t.dist0 = fabs(na - t.d_plus) / nrm;
+    t.dist1 = fabs(na - t.d_minus) / nrm;
+    if (const_idx >= 0) {
+        t.idx = const_idx;
+    } else {
+        // strict '<' scan from best = inf: ties keep index 0 (makeconstraint.py:195-202)
+        const double inf = __longlong_as_double(0x7ff0000000000000LL);
+        double best = inf;
+        t.idx = 0;  // both distances NaN/inf: the reference would fail on candidates[None]
+        if (t.dist0 < best) { best = t.dist0; t.idx = 0; }
+        if (t.dist1 < best) { best = t.dist1; t.idx = 1; }
+    }
+    t.d_star = t.idx == 0 ? t.d_plus : t.d_minus;
+    return t;
+}
+
+__device__ __forceinline__ double fro_norm(const Sym2& s) {
+    return sqrt(fma(s.xx, s.xx, fma(2.0 * s.xy, s.xy, s.yy * s.yy)));
+}
+
+// chi2.ppf(p, df=2) = -2 ln(1 - p);  chi2.cdf(x, df=2) = 1 - exp(-x/2)
+__device__ __forceinline__ double chi2_ppf_df2(double p) { return -2.0 * log1p(-p); }
+__device__ __forceinline__ double chi2_cdf_df2(double x) { return -expm1(-0.5 * x); }
+
+// makeconstraint.py:282-303
+__device__ __forceinline__ double lower_bound_prob(const Sym2& ci, const Sym2& cm, const Sym2& ct, double eps_t) {
+    double base = sqrt(fro_norm(ct));
+    double alpha = sqrt(fro_norm(ci)) / base;
+    double beta = sqrt(fro_norm(cm)) / base;
+    double Gamma = normcdfinv(1.0 - eps_t);
+    double r = Gamma * (1.0 - alpha) / beta;
+    return chi2_cdf_df2(r * r);
+}
+
+// makeconstraint.py:259-280
+__device__ __forceinline__ double scale_factor(const Sym2& ci, const Sym2& cm, const Sym2& ct, double Gamma,
+                                               double target_p) {
+    double base = sqrt(fro_norm(ct));
+    double alpha = sqrt(fro_norm(ci)) / base;
+    double beta = sqrt(fro_norm(cm)) / base;
+    double chi_p = chi2_ppf_df2(target_p);
+    double s = sqrt(chi_p) * beta / Gamma + alpha;
+    return s * s;
+}
+
+// ---------------------------------------------------------------------------
+// Packed sums layout (include/ccmpc.h, ccmpc_sample_sums).
+// ---------------------------------------------------------------------------
+struct SumsLayout {
+    int T, D;
+    int o_s1, o_s2, o_coll, o_any, o_pen, o_d2s, o_yaw, len;
+    __host__ __device__ explicit SumsLayout(int T_) {
+        T = T_;
+        D = 2 * T_;
+        o_s1 = 1;
+        o_s2 = o_s1 + D;
+        o_coll = o_s2 + D * (D + 1) / 2;
+        o_any = o_coll + T;
+        o_pen = o_any + 1;
+        o_d2s = o_pen + T;
+        o_yaw = o_d2s + T;
+        len = o_yaw + T;
+    }
+    __host__ __device__ int s2(int i, int j) const {  // any order
+        return i >= j ? o_s2 + i * (i + 1) / 2 + j : o_s2 + j * (j + 1) / 2 + i;
+    }
+};
+
+// covariance entry (ddof = 1) from shifted power sums
+__device__ __forceinline__ double cov_from_sums(const double* __restrict__ s, const SumsLayout& L, int i, int j,
+                                                double n, double inv_nm1) {
+    double si = s[L.o_s1 + i], sj = s[L.o_s1 + j];
+    return (s[L.s2(i, j)] - si * sj / n) * inv_nm1;
+}
+
+// ordered atomic max on doubles (buffer initialised with 0xFF bytes)
+__device__ __forceinline__ void atomic_max_double(double* addr, double v) {
+    if (v >= 0.0) {
+        atomicMax(reinterpret_cast<long long*>(addr), __double_as_longlong(v));
+    } else {
+        atomicMin(reinterpret_cast<unsigned long long*>(addr), (unsigned long long)__double_as_longlong(v));
+    }
+}
+
+}  // namespace ccmpc

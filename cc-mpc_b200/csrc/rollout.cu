@@ -1,0 +1,191 @@
+// rollout.cu - K1: Monte Carlo conditional-Gaussian rollout of libccmpc.
+//
+// Replaces the loop body of MidlevelAgent.predict_ideal
+// (collect/in_simulation/midlevel/v8ideal/__init__.py:2662-2709): for every
+// cell (obstacle, mode) and sample
+//     A_t  = C_{t+1,t} Sigma_t^-1                      (:2684-2689)
+//     x   <- mu_{t+1} + A_t (x - mu_t) + L_t z          (:2690, :2700-2703)
+//     L_t  = chol(Sigma_{t+1} - A_t C_{t+1,t}^T)        (:2693-2696)
+// starting from the single x0 draw shared by all samples (:2664-2665).
+// The reference draws z with NumPy's MT19937 (`RandomState.standard_normal`,
+// :2699-2700); here z comes from Philox-4x32-10 (counter-based, so a sample's
+// stream depends only on (seed, cell, global sample index, step) and not on how
+// samples are split over CTAs or GPUs) through a float32 Box-Muller, or from a
+// caller-supplied noise tensor (deterministic parity mode).
+//
+// One thread per sample; per-step parameters (mu, A, L) of the cell are built
+// once per CTA in shared memory; the (128, Tsh, 2) fp64 output tile is
+// transposed through shared memory so global stores are contiguous 16-byte
+// lanes.  Algorithmic HBM bytes: 16 per (sample, timestep) written.
+#include "common.cuh"
+
+namespace ccmpc {
+
+constexpr int RO_THREADS = 128;
+
+struct Philox {
+    uint32_t c[4];
+};
+
+__device__ __forceinline__ Philox philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
+                                                uint32_t k1) {
+    const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi0 = __umulhi(M0, c0), lo0 = M0 * c0;
+        const uint32_t hi1 = __umulhi(M1, c2), lo1 = M1 * c2;
+        const uint32_t n0 = hi1 ^ c1 ^ k0, n1 = lo1, n2 = hi0 ^ c3 ^ k1, n3 = lo0;
+        c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+        k0 += W0;
+        k1 += W1;
+    }
+    return Philox{{c0, c1, c2, c3}};
+}
+
+// Box-Muller on two 32-bit words: u1 in (0, 1], angle uniform in [-pi, pi).
+__device__ __forceinline__ void box_muller(uint32_t r0, uint32_t r1, float& z0, float& z1) {
+    const float u1 = fmaf(__uint2float_rn(r0), 2.3283064365386963e-10f, 1.1641532182693481e-10f);
+    const float rad = sqrtf(-2.0f * __logf(u1));
+    const float ang = __int2float_rn((int)r1) * 1.4629180792671596e-9f;   // pi / 2^31
+    float s, c;
+    __sincosf(ang, &s, &c);
+    z0 = rad * c;
+    z1 = rad * s;
+}
+
+struct StepParams {   // per (cell, t): 11 doubles
+    double mux, muy, mnx, mny, a00, a01, a10, a11, l00, l10, l11;
+};
+
+__global__ void __launch_bounds__(RO_THREADS)
+rollout_kernel(const double* __restrict__ mean, const double* __restrict__ cov, const double* __restrict__ cross,
+               int Tm, const double* __restrict__ x0, int64_t n, int Tsh, uint32_t seed_lo, uint32_t seed_hi,
+               uint64_t sample_offset, const double* __restrict__ z_in, double* __restrict__ traj,
+               double* __restrict__ z_out, uint8_t* __restrict__ status) {
+    extern __shared__ __align__(16) double smem[];
+    StepParams* sp = reinterpret_cast<StepParams*>(smem);                       // [Tsh]
+    const int par_d = (Tsh * 11 + 1) & ~1;
+    double2* stage = reinterpret_cast<double2*>(smem + par_d);                   // [128][stride2]
+    const int stride2 = Tsh | 1;
+    const int tid = threadIdx.x;
+    const int64_t c = blockIdx.y;
+
+    if (tid < Tsh) {
+        const int t = tid;
+        const double* mt = mean + (c * Tm + t) * 2;
+        const double* St = cov + (c * Tm + t) * 4;
+        const double* Sn = cov + (c * Tm + t + 1) * 4;
+        const double* Cx = cross + ((c * Tm + t + 1) * Tm + t) * 4;
+        StepParams p;
+        p.mux = mt[0]; p.muy = mt[1]; p.mnx = mt[2]; p.mny = mt[3];
+        int st = 0;
+        // inverse of Sigma_t (np.linalg.inv of a general 2x2)
+        const double det = diff_of_products(St[0], St[3], St[1], St[2]);
+        if (det == 0.0 || !isfinite(det)) st = CCMPC_ST_SINGULAR;
+        const double id = 1.0 / det;
+        const double i00 = St[3] * id, i01 = -St[1] * id, i10 = -St[2] * id, i11 = St[0] * id;
+        p.a00 = fma(Cx[0], i00, Cx[1] * i10);
+        p.a01 = fma(Cx[0], i01, Cx[1] * i11);
+        p.a10 = fma(Cx[2], i00, Cx[3] * i10);
+        p.a11 = fma(Cx[2], i01, Cx[3] * i11);
+        // cond_cov = Sigma_{t+1} - A C^T ; Cholesky reads the lower triangle
+        const double k00 = Sn[0] - fma(p.a00, Cx[0], p.a01 * Cx[1]);
+        const double k10 = Sn[2] - fma(p.a10, Cx[0], p.a11 * Cx[1]);
+        const double k11 = Sn[3] - fma(p.a10, Cx[2], p.a11 * Cx[3]);
+        if (!(k00 > 0.0) && st == 0) st = CCMPC_ST_NO_TANGENT;
+        p.l00 = sqrt(k00);
+        p.l10 = k10 / p.l00;
+        const double r = k11 - p.l10 * p.l10;
+        if (!(r > 0.0) && st == 0) st = CCMPC_ST_NO_TANGENT;
+        p.l11 = sqrt(r);
+        sp[t] = p;
+        if (status && blockIdx.x == 0 && st) status[c] = (uint8_t)st;
+    }
+    __syncthreads();
+
+    const int64_t i0 = (int64_t)blockIdx.x * RO_THREADS;
+    const int64_t i = i0 + tid;
+    const int rows = (int)min((int64_t)RO_THREADS, n - i0);
+    if (i < n) {
+        double x = x0[2 * c], y = x0[2 * c + 1];
+        const uint64_t gi = sample_offset + (uint64_t)i;
+        const double2* zin2 = z_in ? reinterpret_cast<const double2*>(z_in) + (c * n + i) * Tsh : nullptr;
+        double2* zout2 = z_out ? reinterpret_cast<double2*>(z_out) + (c * n + i) * Tsh : nullptr;
+        float zb0 = 0.f, zb1 = 0.f;
+        for (int t = 0; t < Tsh; ++t) {
+            double zx, zy;
+            if (zin2) {
+                const double2 zz = zin2[t];
+                zx = zz.x; zy = zz.y;
+            } else {
+                if ((t & 1) == 0) {
+                    Philox r = philox4x32_10((uint32_t)gi, (uint32_t)(gi >> 32), (uint32_t)c, (uint32_t)(t >> 1),
+                                             seed_lo, seed_hi);
+                    float za, zb;
+                    box_muller(r.c[0], r.c[1], za, zb);
+                    box_muller(r.c[2], r.c[3], zb0, zb1);
+                    zx = (double)za; zy = (double)zb;
+                } else {
+                    zx = (double)zb0; zy = (double)zb1;
+                }
+            }
+            if (zout2) zout2[t] = make_double2(zx, zy);
+            const StepParams& p = sp[t];
+            const double dx = x - p.mux, dy = y - p.muy;
+            const double cmx = p.mnx + fma(dx, p.a00, dy * p.a01);
+            const double cmy = p.mny + fma(dx, p.a10, dy * p.a11);
+            x = cmx + zx * p.l00;
+            y = cmy + fma(zx, p.l10, zy * p.l11);
+            stage[tid * stride2 + t] = make_double2(x, y);
+        }
+    }
+    __syncthreads();
+    // contiguous store of the CTA's (rows, Tsh, 2) block
+    double2* out2 = reinterpret_cast<double2*>(traj) + (c * n + i0) * Tsh;
+    const int total = rows * Tsh;
+    for (int e = tid; e < total; e += RO_THREADS) {
+        const int r = e / Tsh, t = e - r * Tsh;
+        __stcs(out2 + e, stage[r * stride2 + t]);
+    }
+}
+
+__global__ void philox_kernel(const uint32_t* __restrict__ ctr, const uint32_t* __restrict__ key, int64_t M,
+                              uint32_t* __restrict__ out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= M) return;
+    Philox r = philox4x32_10(ctr[4 * i], ctr[4 * i + 1], ctr[4 * i + 2], ctr[4 * i + 3], key[2 * i], key[2 * i + 1]);
+    out[4 * i] = r.c[0]; out[4 * i + 1] = r.c[1]; out[4 * i + 2] = r.c[2]; out[4 * i + 3] = r.c[3];
+}
+
+}  // namespace ccmpc
+
+using namespace ccmpc;
+
+extern "C" int ccmpc_mc_rollout(const double* mean, const double* cov, const double* cross, int Tm,
+                                const double* x0, int64_t C, int64_t n, int Tsh, uint64_t seed,
+                                uint64_t sample_offset, const double* z, double* traj, double* z_out,
+                                uint8_t* status, void* stream) {
+    CCMPC_REQUIRE(Tsh >= 1 && Tsh <= CCMPC_MAX_T, "ccmpc_mc_rollout: need 1 <= Tsh <= %d", CCMPC_MAX_T);
+    CCMPC_REQUIRE(Tm >= Tsh + 1, "ccmpc_mc_rollout: moments must cover Tsh + 1 steps (Tm = %d, Tsh = %d)", Tm, Tsh);
+    CCMPC_REQUIRE(C >= 0 && n >= 0 && C < 65536, "ccmpc_mc_rollout: bad C / n");
+    CCMPC_REQUIRE(mean && cov && cross && x0 && traj, "ccmpc_mc_rollout: null pointer");
+    if (C == 0 || n == 0) return CCMPC_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (status) {
+        cudaError_t e = cudaMemsetAsync(status, 0, (size_t)C, st);
+        if (e != cudaSuccess) { set_error("ccmpc_mc_rollout: memset: %s", cudaGetErrorString(e)); return CCMPC_E_LAUNCH; }
+    }
+    const int par_d = (Tsh * 11 + 1) & ~1;
+    const size_t smem = (size_t)par_d * 8 + (size_t)RO_THREADS * (Tsh | 1) * 16;
+    dim3 grid((unsigned)((n + RO_THREADS - 1) / RO_THREADS), (unsigned)C);
+    rollout_kernel<<<grid, RO_THREADS, smem, st>>>(mean, cov, cross, Tm, x0, n, Tsh, (uint32_t)seed,
+                                                   (uint32_t)(seed >> 32), sample_offset, z, traj, z_out, status);
+    return check_launch("rollout_kernel");
+}
+
+extern "C" int ccmpc_philox4x32(const uint32_t* ctr, const uint32_t* key, int64_t M, uint32_t* out, void* stream) {
+    CCMPC_REQUIRE(M >= 0 && ctr && key && out, "ccmpc_philox4x32: bad arguments");
+    if (M == 0) return CCMPC_OK;
+    philox_kernel<<<(unsigned)((M + 127) / 128), 128, 0, (cudaStream_t)stream>>>(ctr, key, M, out);
+    return check_launch("philox_kernel");
+}

@@ -1,0 +1,236 @@
+/* ccmpc.h - C ABI of libccmpc.so: the CC-MPC prediction -> chance-constraint
+ * hot path as hand-written sm_100a CUDA kernels.
+ *
+ * Every entry point replaces a NumPy/SciPy call site of the reference
+ * (HyeontaeSung/CC-MPC; paths relative to its root, "v8ideal" =
+ * collect/in_simulation/midlevel/v8ideal/__init__.py, "makeconstraint" =
+ * collect/in_simulation/midlevel/v8ideal/makeconstraint.py).  The reference is
+ * pure Python, so its "FFI" for this path is a ctypes binding; INTEGRATION.md
+ * shows the stub a maintainer adds.
+ *
+ * Conventions
+ *  - All data pointers are DEVICE pointers (caller-owned, contiguous, 16-byte
+ *    aligned); `stream` is a cudaStream_t passed as void*.  The library
+ *    allocates nothing and keeps no state besides the last-error string.
+ *  - Calls enqueue work on `stream` and return without synchronising.
+ *  - Return value: 0 = ok, <0 = error (see CCMPC_E_*); the message is in
+ *    ccmpc_last_error_string().
+ *  - Symmetric 2x2 matrices travel as (xx, xy, yy) triples ("sym3"); full
+ *    2x2 blocks as 4 doubles row-major.
+ *  - Sample tensors are row-major (N, T, 2) float64, cells (= one
+ *    (obstacle, mode) each) are contiguous sample ranges given by a CSR
+ *    `offsets` array (C+1 int64, device): the layout of the reference's
+ *    np.vstack(ovehicle.pred_positions[latent_idx]) (v8ideal:890).
+ *  - Per-cell status bytes: 0 ok, 1 singular matrix (np.linalg.inv /
+ *    scipy.linalg.solve would raise LinAlgError), 2 no tangent / non-PD
+ *    (choose_closest_tangent returns None; np.linalg.cholesky would raise),
+ *    3 fixed point not converged in maxiter, 4 degenerate slope (ref_y == mu_y).
+ */
+#ifndef CCMPC_H_
+#define CCMPC_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CCMPC_VERSION 100          /* 0.1.0 */
+#define CCMPC_MAX_T 16             /* longest horizon handled (reference: ph8 / ph16) */
+
+#define CCMPC_OK 0
+#define CCMPC_E_ARG (-1)           /* bad argument */
+#define CCMPC_E_LAUNCH (-2)        /* CUDA launch / runtime failure */
+#define CCMPC_E_WORKSPACE (-3)     /* workspace too small */
+
+#define CCMPC_ST_OK 0
+#define CCMPC_ST_SINGULAR 1
+#define CCMPC_ST_NO_TANGENT 2
+#define CCMPC_ST_NOT_CONVERGED 3
+#define CCMPC_ST_DEGENERATE_SLOPE 4
+
+int ccmpc_version(void);
+const char* ccmpc_last_error_string(void);
+
+/* ---------------------------------------------------------------------------
+ * K3  batched MVOE fit.   Replaces makeconstraint.compute_mvoe (:7-38).
+ * For i < M: lambda = eig(Sigma1_i^-1 Sigma2_i).real; beta from 1.0 by
+ * beta <- sqrt(sum 1/(1+beta lam) / sum lam/(1+beta lam)) until |delta| < tol or
+ * maxiter; Q = (1+1/beta) Sigma1 + (1+beta) Sigma2.
+ *   sigma1 [M,3] sym3; sigma2 [M,3] sym3 or NULL => Sigma2 = footprint_r2 * I
+ *   (the R^2 I footprint fit of v8ideal:917-918).
+ *   beta [M], q [M,3], iters [M] int32 (nullable), status [M] uint8 (nullable).
+ *   accel = 0: the reference's iterate sequence from beta = 1 (same stopping
+ *   rule, same iteration count).  accel = 1: float32 warm start, then the same
+ *   fp64 fixed-point map until |delta| < tol (result within tol of accel = 0).
+ */
+int ccmpc_mvoe_fit(const double* sigma1, const double* sigma2, double footprint_r2,
+                   int64_t M, double tol, int maxiter, int accel,
+                   double* beta, double* q, int32_t* iters, uint8_t* status,
+                   void* stream);
+
+/* ---------------------------------------------------------------------------
+ * K3+K4  scenario sweep: footprint fit + tangent half-plane per
+ * (scenario, obstacle, timestep, mode).  Replaces, per cell, v8ideal:915-939
+ * with a given mode covariance: Q = mvoe(cov * chi_scale, R^2 I); slope m
+ * perpendicular to (ref - mu) (:923); choose_closest_tangent(mu, Q, 1, m, ref)
+ * (makeconstraint:176-207); side test (:926-939).
+ *   cov [S,O,T,K,3] sym3, mu [S,O,T,K,2], ref [S,T,2].
+ *   out: q [S,O,T,K,3], nd [S,O,T,K,3] = (n0, n1, d), idx_side [S,O,T,K] int8
+ *   (bit0 = best_idx, bit1 set when the row is n.x <= d), status [..] uint8 (nullable).
+ */
+int ccmpc_mvoe_halfplane_sweep(const double* cov, const double* mu, const double* ref,
+                               int64_t S, int O, int T, int K,
+                               double chi_scale, double footprint_r2,
+                               double tol, int maxiter, int accel,
+                               double* q, double* nd, int8_t* idx_side, uint8_t* status,
+                               void* stream);
+
+/* ---------------------------------------------------------------------------
+ * K4  tangent lines.  Replaces makeconstraint.tangent_lines_of_slope_m
+ * (:134-162), distance_point_to_line (:165-173), choose_closest_tangent
+ * (:176-207) for M independent problems.
+ *   mu [M,2], sigma [M,3], c [M], m [M], a [M,2], const_idx [M] int32 or NULL
+ *   (-1 = choose closest).  out: d12 [M,2] (d+, d-), dist [M,2], d_star [M],
+ *   idx [M] int32 (-1 when n^T Sigma n <= 0), all nullable.
+ */
+int ccmpc_tangent(const double* mu, const double* sigma, const double* c, const double* m,
+                  const double* a, const int32_t* const_idx, int64_t M,
+                  double* d12, double* dist, double* d_star, int32_t* idx, void* stream);
+
+/* compute_scale (makeconstraint:259-280) and compute_lower_bound (:282-303):
+ *   cov_infer, cov_mu, cov_t [M,3] sym3; gamma [M] (scale) ; eps [M] (lower).
+ *   out (nullable): scale [M], lower [M]. */
+int ccmpc_scale_lower(const double* cov_infer, const double* cov_mu, const double* cov_t,
+                      const double* gamma, const double* eps, double target_p, int64_t M,
+                      double* scale, double* lower, void* stream);
+
+/* ---------------------------------------------------------------------------
+ * K2+K6  one read of the sample tensor -> everything that is a sum over samples.
+ * Replaces np.mean / np.cov of every (t, tau) pair (makeconstraint:55,
+ * v8ideal:894-904, :2586-2606, :1485-1493), np.mean(yaws) (v8ideal:723) and the
+ * restated collision predicate A9 (R from v8ideal:795).
+ *
+ * Per cell c the packed sums vector (CCMPC sums layout, doubles, length
+ * ccmpc_sums_len(T)), with D = 2T and u = sample - pivot[c]:
+ *   [0]                     n
+ *   [1, 1+D)                S1[i]  = sum u_i                (i = 2t + coord)
+ *   [1+D, 1+D+D(D+1)/2)     S2[i(i+1)/2 + j] = sum u_i u_j  (i >= j)
+ *   then T entries each:    coll[t]  = #{ |ego_t - p_t|^2 < R^2 }   (exact integer)
+ *   1 entry:                any      = #{ exists t hit }
+ *   T entries:              pen[t]   = sum over hits (R^2 - |ego_t - p_t|^2)
+ *   T entries:              d2s[t]   = sum |ego_t - p_t|^2
+ *   T entries:              yaw[t]   = sum yaw_t
+ * Counts are integers < 2^53 held exactly in doubles, so one fp64 NCCL
+ * all-reduce(sum) of `sums` across sample shards is exact for them.
+ * The predicate is evaluated without FMA contraction in the order
+ *   dx = ex - px; dy = ey - py; d2 = dx*dx + dy*dy; hit = d2 < R*R.
+ *
+ *   samples [N,T,2]; offsets [C+1] int64; pivot [C,T,2];
+ *   ego [T,2] (ego_cell_stride = 0) or [C,T,2] (stride = 2T) or NULL (no counts);
+ *   yaws [N,T] or NULL.
+ *   n_total = total sample count N (for grid sizing; offsets stay on device).
+ *   workspace: ccmpc_sample_sums_workspace_bytes(n_total, C, T) bytes.
+ *   out: sums [C, ccmpc_sums_len(T)].
+ */
+int64_t ccmpc_sums_len(int T);
+size_t ccmpc_sample_sums_workspace_bytes(int64_t n_total, int64_t C, int T);
+int ccmpc_sample_sums(const double* samples, const int64_t* offsets, int64_t n_total, int64_t C, int T,
+                      const double* pivot, const double* ego, int64_t ego_cell_stride, double R,
+                      const double* yaws, double* sums, void* workspace, size_t workspace_bytes,
+                      void* stream);
+
+/* Moments as save_moments stores them (v8ideal:2586-2606) from the sums:
+ *   mean [C,T,2], cov [C,T,2,2], cross [C,T,T,2,2] (cross[t][tau] for tau < t,
+ *   = np.cov([x_t,y_t,x_tau,y_tau])[0:2,2:4]; other slots zero),
+ *   counts [C, 2T+... ] see below (nullable), yaw_mean [C,T] (nullable).
+ *   counts layout int64 [C, T+1]: coll[0..T), any. */
+int ccmpc_moments_from_sums(const double* sums, const double* pivot, int64_t C, int T,
+                            double* mean, double* cov, double* cross,
+                            int64_t* counts, double* yaw_mean, void* stream);
+
+/* ---------------------------------------------------------------------------
+ * K3+K4 on sample moments: the Minkowski half-plane loop of one MPC step.
+ * Replaces v8ideal:893-947 (predict_moments -> compute_mvoe x2 ->
+ * choose_closest_tangent -> side -> compute_lower_bound) for every cell and
+ * every pair p = t(t-1)/2 + tau, tau < t < T.  P = T(T-1)/2.
+ *   sums [C, sums_len(T)], pivot [C,T,2], ref [T,2] (ref_cell_stride 0) or [C,T,2],
+ *   eps_cell [C] (= eps_ura[o,k], v8ideal:2920-2926), prediction_horizon (:910).
+ *   out (each nullable): nd [C,P,3] = (n0,n1,d); ab [C,P,3] = (A0,A1,b) (:933-939);
+ *   idx_side [C,P] int8 (bit0 best_idx, bit1 row is n.x <= d);
+ *   q [C,P,3]; q1 [C,P,3]; betas [C,P,2]; cov_infer [C,P,3]; cov_mu [C,P,3];
+ *   prob_pair [C,P]; prob_lower [C,T] (min over tau, 1.0 at t = 0);
+ *   mean [C,T,2]; status [C,P] uint8.
+ */
+int ccmpc_minkowski_halfplanes(const double* sums, const double* pivot, const double* ref,
+                               int64_t ref_cell_stride, const double* eps_cell,
+                               int64_t C, int T, int prediction_horizon,
+                               double R, double target_p, double tol, int maxiter, int accel,
+                               double* nd, double* ab, int8_t* idx_side, double* q, double* q1,
+                               double* betas, double* cov_infer, double* cov_mu,
+                               double* prob_pair, double* prob_lower, double* mean,
+                               uint8_t* status, void* stream);
+
+/* Affine (receding-horizon) half-planes.  Replaces v8ideal:1476-1515 per
+ * (cell, t): Gamma = norm.ppf(1 - eps_cell/Tpred), sqrtm(cov_t), tangent to the
+ * radius-R circle, offset = Gamma || sqrtm(cov) [m,-1]^T ||.
+ *   out: nd [C,T,3], offset_rhs [C,T,2], idx_side [C,T] int8, mean [C,T,2], cov [C,T,3]. */
+int ccmpc_affine_halfplanes(const double* sums, const double* pivot, const double* ref,
+                            int64_t ref_cell_stride, const double* eps_cell,
+                            int64_t C, int T, int Tpred, double R,
+                            double* nd, double* offset_rhs, int8_t* idx_side,
+                            double* mean, double* cov, uint8_t* status, void* stream);
+
+/* ---------------------------------------------------------------------------
+ * A9 (ii)  violation counts of emitted half-planes over a sample tensor:
+ *   viol[c,p] = #{ n in cell c : side * (n0*px + n1*py - d) > 0 } at t = t(p),
+ * evaluated without FMA contraction (v = n0*px + n1*py; side*(v - d) > 0).
+ *   nd [C,P,3], idx_side [C,P] (bit1 => side = -1), out viol [C,P] int64 (zeroed by the call).
+ */
+int ccmpc_violation_counts(const double* samples, const int64_t* offsets, int64_t n_total,
+                           int64_t C, int T, const double* nd, const int8_t* idx_side,
+                           int64_t* viol, void* stream);
+
+/* ---------------------------------------------------------------------------
+ * K5  boxes and the 4-face outer approximation.
+ * ccmpc_vertices_of_bboxes replaces utility/npu.py vertices_of_bboxes (:308-350):
+ *   centers [N,2], theta [N], lw [2] host values -> vertices [N,4,2].
+ * ccmpc_l4_outer replaces v8ideal:627-640 + :694-736 + midlevel/util.py:171-200
+ * per (cell, t) without materialising the corners:
+ *   samples [N,T,2], yaws [N,T], yaw_mean [C,T] (from ccmpc_moments_from_sums),
+ *   out At [C,T,4,2], b0 [C,T,4].
+ */
+int ccmpc_vertices_of_bboxes(const double* centers, const double* theta, int64_t theta_is_scalar,
+                             double l, double w, int64_t N, double* vertices, void* stream);
+int ccmpc_l4_outer(const double* samples, const double* yaws, const int64_t* offsets,
+                   int64_t n_total, int64_t C, int T, const double* yaw_mean,
+                   double l, double w, double* At, double* b0, void* stream);
+
+/* ---------------------------------------------------------------------------
+ * K1  Monte Carlo rollout.  Replaces MidlevelAgent.predict_ideal's loop body
+ * (v8ideal:2662-2709) for C cells x n samples: per step t < Tsh
+ *   A = C_{t+1,t} Sigma_t^-1 ; cond_cov = Sigma_{t+1} - A C^T ; L = chol(cond_cov)
+ *   x <- mu_{t+1} + A (x - mu_t) + L z,   traj[:, t] = x      (slot t holds x_{t+1})
+ * starting from the ONE draw x0[c] the reference broadcasts to all samples
+ * (:2664-2665).
+ *   mean [C,Tm,2], cov [C,Tm,2,2], cross [C,Tm,Tm,2,2] with Tm >= Tsh + 1.
+ *   x0 [C,2].  z: NULL => Philox-4x32-10 normals (counter = (sample index,
+ *   sample_offset-based; cell; draw), key = seed; sample_offset makes the
+ *   stream independent of how samples are sharded over GPUs); else the
+ *   supplied noise [C,n,Tsh,2] (deterministic parity mode).
+ *   out traj [C,n,Tsh,2]; z_out (nullable) receives the normals used;
+ *   status [C] uint8 (1 singular Sigma_t, 2 cond_cov not PD).
+ */
+int ccmpc_mc_rollout(const double* mean, const double* cov, const double* cross, int Tm,
+                     const double* x0, int64_t C, int64_t n, int Tsh,
+                     uint64_t seed, uint64_t sample_offset, const double* z,
+                     double* traj, double* z_out, uint8_t* status, void* stream);
+
+/* Philox-4x32-10 known-answer hook: out[i] = philox(ctr[i], key[i]) (4 words each). */
+int ccmpc_philox4x32(const uint32_t* ctr, const uint32_t* key, int64_t M, uint32_t* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CCMPC_H_ */
