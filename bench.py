@@ -1,0 +1,413 @@
+#!/usr/bin/env python
+"""bench.py - the CC-MPC prediction -> constraint hot path on B200 (libccmpc.so).
+
+One JSON line.  Headline (BASELINE.json metric, first term): Monte Carlo sampled
+trajectory-steps/s of config c3 - per GPU 1M samples per obstacle, O = 8 obstacles x
+4 modes, ph16: Philox rollout -> ONE read of the trajectories for collision counts / soft
+cost / all (t, tau) moments -> one NCCL all-reduce of the packed sums when N > 1
+(weak scaling: every rank rolls its own 1M samples per obstacle, Philox sample_offset =
+rank * n).  The two other terms of the metric ride in the same line under "also":
+batched MVOE half-plane sweep fits/s (c4) and the p50 ms of the full c2 constraint build.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+# ---- workload shapes ------------------------------------------------------------
+C3 = dict(O=8, K=4, T=16, n_per_cell=250_000, seed=3)            # 1M samples / obstacle, ph16
+C4 = dict(S=4096, O=8, T=16, K=25, seed=4)                      # batched MVOE sweep
+C2 = dict(O=4, K=25, T=8, N=5000, seed=2)                       # one MPC step
+METRIC = "mc_traj_steps_per_sec"
+UNIT = "traj-steps/s"
+BYTES_PER_TRAJ_STEP_SUMS = 16        # sample_sums: x, y fp64 read once
+BYTES_PER_TRAJ_STEP_ROLLOUT = 16     # rollout: x, y fp64 written once
+
+
+def _peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """SM clock + throttle reasons during the timed region (NVML; nvidia-smi fallback)."""
+
+    def __init__(self, index=0, period=0.05):
+        self.index, self.period = index, period
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+
+    def _loop(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)
+            names = {
+                getattr(pynvml, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
+                getattr(pynvml, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+                getattr(pynvml, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+                getattr(pynvml, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+            }
+            while not self._stop.is_set():
+                self.samples.append(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM))
+                try:
+                    r = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h)
+                except Exception:
+                    r = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+                self._stop.wait(self.period)
+        except Exception as e:  # noqa: BLE001
+            self.reasons.add(f"nvml_unavailable:{type(e).__name__}")
+
+    def __enter__(self):
+        self._thr = threading.Thread(target=self._loop, daemon=True)
+        self._thr.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        self._thr.join(timeout=2)
+
+    def summary(self):
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU arm: the oracle (NumPy restatement of the reference loops) on the host cores
+# ---------------------------------------------------------------------------------------------
+def _cpu_mc_cell(args):
+    """One (obstacle, mode) cell: predict_ideal body (v8ideal:2664-2706) + counts (A9) +
+    save_moments (v8ideal:2586-2606) on the CPU oracle.  Returns traj-steps processed."""
+    seed, n, T = args
+    from oracle import restate, synth
+    sc = synth.make_scene(C3["seed"], 1, 1, T + 1)
+    mean, cov, cross = sc.moments()
+    rng = np.random.default_rng(seed)
+    traj = restate.ideal_rollout_sampled(mean[0, 0], cov[0, 0], cross[0, 0], T, n, rng)
+    restate.collision_counts(traj, synth.reference_trajectory(T))
+    restate.cell_moments(traj)
+    return n * T
+
+
+def cpu_mc_throughput(n_per_cell, T, procs, cells):
+    """traj-steps/s of the oracle over `cells` cells using `procs` worker processes."""
+    jobs = [(1000 + i, n_per_cell, T) for i in range(cells)]
+    t0 = time.perf_counter()
+    if procs <= 1:
+        done = sum(_cpu_mc_cell(j) for j in jobs)
+    else:
+        import multiprocessing as mp
+        with mp.get_context("fork").Pool(procs) as pool:
+            done = sum(pool.map(_cpu_mc_cell, jobs))
+    dt = time.perf_counter() - t0
+    return done / dt, dt
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path (oracle port; the reference is pure Python and its
+    v8ideal module does not import without carla/cvxpy) on all host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    cores = os.cpu_count() or 1
+    n = 20_000
+    T = C3["T"]
+    for _ in range(min(args.warmup, 1)):
+        cpu_mc_throughput(n, T, cores, cores)
+    vals, secs = [], []
+    steps = max(1, min(args.steps, 5))
+    for _ in range(steps):
+        v, dt = cpu_mc_throughput(n, T, cores, cores)
+        vals.append(v)
+        secs.append(dt)
+    value = float(np.sum([n * T * cores] * steps) / np.sum(secs))
+    sample = f"{cores} cells x {n} samples x ph{T} per step (c3 shape, 1/{C3['n_per_cell'] // n} of a cell each)"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+        "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * float(np.mean(secs)), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": _config(args.gpus),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+    return 0
+
+
+def _config(n_gpus):
+    return {"workload": "c3: MC collision-risk estimate, 1M samples/obstacle per GPU, O=8 x K=4 cells, ph16 "
+                        "(rollout -> counts/cost/moments -> count all-reduce)",
+            "O": C3["O"], "K": C3["K"], "T": C3["T"], "samples_per_cell_per_gpu": C3["n_per_cell"],
+            "sharding": f"samples x{n_gpus} (Philox sample_offset = rank * n)",
+            "l2": "inputs_exceed_l2 (2.05 GB trajectory tensor per step)"}
+
+
+# ---------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from ccmpc_b200 import _lib, midlevel, ops
+    from oracle import synth                      # input generators only (no reference arithmetic)
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product path has no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    lib = _lib.load(build_if_missing=False)
+    pg = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+        pg = dist.group.WORLD
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    O, K, T, n = C3["O"], C3["K"], C3["T"], args.n_per_cell
+    C = O * K
+    sc = synth.make_scene(C3["seed"], O, K, T + 1)
+    mean_h, cov_h, cross_h = sc.moments()
+    ego_h = synth.reference_trajectory(T)
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+    mean_p, cov_p, cross_p, ego_p = (pin(mean_h.reshape(C, T + 1, 2)), pin(cov_h.reshape(C, T + 1, 2, 2)),
+                                     pin(cross_h.reshape(C, T + 1, T + 1, 2, 2)), pin(ego_h))
+    mean_d, cov_d, cross_d, ego_d = (t.to(dev) for t in (mean_p, cov_p, cross_p, ego_p))
+    pivot = mean_d[:, 1:T + 1].contiguous()
+    traj = torch.empty((C, n, T, 2), dtype=torch.float64, device=dev)
+    offsets = torch.arange(C + 1, dtype=torch.int64, device=dev) * n
+    ws = ops.sample_sums_workspace(C * n, C, T, dev)
+    sums = torch.empty((C, ops.sums_len(T)), dtype=torch.float64, device=dev)
+    flat = traj.view(C * n, T, 2)
+    mom_out = None
+    sums_host = torch.empty(sums.shape, dtype=torch.float64).pin_memory()
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+
+    def step(i, events=None, from_host=False):
+        nonlocal mom_out
+        if from_host:
+            m, c, x, e = (t.to(dev, non_blocking=True) for t in (mean_p, cov_p, cross_p, ego_p))
+            pv = m[:, 1:T + 1].contiguous()
+        else:
+            m, c, x, e, pv = mean_d, cov_d, cross_d, ego_d, pivot
+        if events:
+            events[0].record()
+        ops.mc_rollout(m, c, x, None, n, T, seed=1234 + i, sample_offset=rank * n, out=traj)
+        if events:
+            events[1].record()
+        ops.sample_sums(flat, offsets, pv, ego=e, R=ops.R_EV_OV, workspace=ws, out=sums)
+        if events:
+            events[2].record()
+        if pg is not None:
+            dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=pg)
+        mom_out = ops.moments_from_sums(sums, pv, want_yaw=False, out=mom_out)
+        if from_host:
+            sums_host.copy_(sums, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+
+    # ---- device-resident timing --------------------------------------------------------------
+    for i in range(args.warmup):
+        step(i)
+    barrier()
+    l0 = lib.ccmpc_launch_count()
+    evs = [[ev(), ev(), ev()] for _ in range(args.steps)]
+    t_start, t_stop = ev(), ev()
+    with ClockSampler(local) as clocks:
+        t_start.record()
+        for i in range(args.steps):
+            step(args.warmup + i, evs[i])
+        t_stop.record()
+        barrier()
+    launches = int(lib.ccmpc_launch_count() - l0)
+    ms_total = torch.tensor([t_start.elapsed_time(t_stop)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms_total, op=dist.ReduceOp.MAX)
+    ms_step = float(ms_total.item()) / args.steps
+    units_step = C * n * T * world
+    value = units_step / (ms_step * 1e-3)
+    roll_ms = float(np.mean([e[0].elapsed_time(e[1]) for e in evs]))
+    sums_ms = float(np.mean([e[1].elapsed_time(e[2]) for e in evs]))
+
+    # ---- end-to-end through the host-facing call: H2D of the moments / ego, D2H of the sums ---
+    for i in range(3):
+        step(i, from_host=True)
+    barrier()
+    e0, e1 = ev(), ev()
+    e0.record()
+    for i in range(args.steps):
+        step(args.warmup + i, from_host=True)
+    e1.record()
+    barrier()
+    ms_e2e = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms_e2e, op=dist.ReduceOp.MAX)
+    e2e_value = units_step / (float(ms_e2e.item()) / args.steps * 1e-3)
+    h2d = int(sum(t.numel() * t.element_size() for t in (mean_p, cov_p, cross_p, ego_p)))
+    d2h = int(sums_host.numel() * sums_host.element_size())
+
+    # sanity on the result of the last step (never silently time a no-op)
+    counts = mom_out["counts"].cpu().numpy()
+    assert int(sums[0, 0].item()) == n * world, "sample count mismatch after all-reduce"
+    assert counts.min() >= 0 and counts[:, :T].max() <= n * world
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+
+    peak, peak_src = _peaks()
+    dom = "sample_sums_kernel" if sums_ms >= roll_ms else "rollout_kernel"
+    dom_ms = max(sums_ms, roll_ms)
+    ach = C * n * T * (BYTES_PER_TRAJ_STEP_SUMS if dom == "sample_sums_kernel" else BYTES_PER_TRAJ_STEP_ROLLOUT) \
+        / (dom_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
+                "frac": ach / peak, "traffic": None,
+                "kernels_ms": {"rollout_kernel": roll_ms, "sample_sums(scan+sums+finalize)": sums_ms},
+                "other_kernel": {"name": "rollout_kernel" if dom == "sample_sums_kernel" else "sample_sums_kernel",
+                                 "achieved": C * n * T * 16 / (min(sums_ms, roll_ms) * 1e-3) / 1e9}}
+
+    also = {}
+    if not args.skip_also:
+        also = bench_also(torch, ops, midlevel, synth, dev, args)
+
+    cpu = None
+    if not args.skip_cpu:
+        ncpu = 100_000
+        v, dt = cpu_mc_throughput(ncpu, T, 1, 2)
+        cpu = {"value": v, "unit": UNIT, "cores": 1, "kind": "port",
+               "sample": f"2 cells x {ncpu} samples x ph{T} ({dt:.1f} s; oracle/restate.py: predict_ideal body + "
+                         f"A9 counts + save_moments)"}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "config": _config(world),
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks.summary(),
+        "also": also,
+    }
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def bench_also(torch, ops, midlevel, synth, dev, args):
+    """The two other terms of BASELINE.json's metric, measured on rank 0's GPU."""
+    out = {}
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+    peak, _ = _peaks()
+    # ---- c4: batched MVOE footprint fit + tangent half-plane sweep ---------------------------
+    S, O, T, K = C4["S"], C4["O"], C4["T"], C4["K"]
+    rng = np.random.default_rng(C4["seed"])
+    g = torch.Generator(device=dev).manual_seed(C4["seed"])
+    sx = torch.rand((S, O, T, K), generator=g, device=dev, dtype=torch.float64) * 2.9 + 0.1
+    sy = torch.rand((S, O, T, K), generator=g, device=dev, dtype=torch.float64) * 2.9 + 0.1
+    rho = torch.rand((S, O, T, K), generator=g, device=dev, dtype=torch.float64) * 1.6 - 0.8
+    cov = torch.stack([sx * sx, rho * sx * sy, sy * sy], dim=-1).contiguous()
+    mu = torch.stack([torch.rand((S, O, T, K), generator=g, device=dev, dtype=torch.float64) * 50 + 150,
+                      torch.rand((S, O, T, K), generator=g, device=dev, dtype=torch.float64) * 40 - 100], dim=-1).contiguous()
+    ref = torch.from_numpy(np.broadcast_to(synth.reference_trajectory(T), (S, T, 2)).copy()).to(dev)
+    ref[..., 1] += 30.0      # keep |ref_y - mu_y| away from 0
+    del sx, sy, rho
+    chi = -2.0 * np.log(0.05 / O / T)
+    bufs = None
+    for accel in (False, True):
+        for _ in range(3):
+            bufs = ops.mvoe_halfplane_sweep(cov, mu, ref, chi, accel=accel, out=bufs)
+        torch.cuda.synchronize()
+        a, b = ev(), ev()
+        reps = 10
+        a.record()
+        for _ in range(reps):
+            ops.mvoe_halfplane_sweep(cov, mu, ref, chi, accel=accel, out=bufs)
+        b.record()
+        torch.cuda.synchronize()
+        ms = a.elapsed_time(b) / reps
+        M = S * O * T * K
+        bytes_per = 24 + 16 + 24 + 24 + 1 + 1
+        out["mvoe_sweep_accel" if accel else "mvoe_sweep"] = {
+            "metric": "mvoe_fits_per_sec", "value": M / (ms * 1e-3), "unit": "fits/s", "ms": ms, "fits": M,
+            "workload": f"c4: S={S} x O={O} x T={T} x K={K} footprint fit + tangent half-plane",
+            "roofline": {"bound": "hbm", "achieved": M * bytes_per / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                         "frac": M * bytes_per / (ms * 1e-3) / 1e9 / peak, "bytes_per_fit": bytes_per}}
+    assert int(bufs[3].max().item()) == 0, "MVOE sweep reported a failed cell"
+    del cov, mu, ref, bufs
+    # ---- c2: the full constraint build of one MPC step, host samples -> host rows --------------
+    sc = synth.make_scene(C2["seed"], C2["O"], C2["K"], C2["T"])
+    z, pos = synth.sample_scene(sc, C2["N"], C2["seed"])
+    step = midlevel.StepPlan.from_samples(z, pos, sc.pos_last, C2["K"], prediction_horizon=C2["T"], device=dev)
+    ref_traj = sc.ref_traj
+    for _ in range(10):
+        step.run(pos_host=step.host_samples, ref_traj=ref_traj)
+    times_e2e, times_dev = [], []
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    for _ in range(100):
+        flush.fill_(1)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        step.run(pos_host=step.host_samples, ref_traj=ref_traj)
+        times_e2e.append((time.perf_counter() - t0) * 1e3)
+    for _ in range(100):
+        flush.fill_(1)
+        a, b = ev(), ev()
+        a.record()
+        step.run_device()
+        b.record()
+        torch.cuda.synchronize()
+        times_dev.append(a.elapsed_time(b))
+    out["constraint_build_c2"] = {
+        "metric": "mpc_step_constraint_build_p50_ms", "unit": "ms", "higher_is_better": False,
+        "p50_host_to_host": float(np.percentile(times_e2e, 50)), "p95_host_to_host": float(np.percentile(times_e2e, 95)),
+        "p50_device_resident": float(np.percentile(times_dev, 50)),
+        "workload": "c2: O=4, K=25, ph8, np5000: sums+counts -> Minkowski half-planes (2800 pairs, 5600 fits) -> "
+                    "L4 polytopes -> violation counts; L2 flushed between iterations",
+        "rows": int(step.C * step.P), "launches_per_step": step.launches_per_step}
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=int(os.environ.get("WORLD_SIZE", "1")))
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--n-per-cell", type=int, default=C3["n_per_cell"])
+    ap.add_argument("--skip-cpu", action="store_true")
+    ap.add_argument("--skip-also", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "ours":
+        args.warmup = 3
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

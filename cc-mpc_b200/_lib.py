@@ -17,6 +17,7 @@ _P = c_void_p
 SIGNATURES = {
     "ccmpc_version": (c_int, []),
     "ccmpc_last_error_string": (c_char_p, []),
+    "ccmpc_launch_count": (c_uint64, []),
     "ccmpc_mvoe_fit": (c_int, [_P, _P, c_double, c_int64, c_double, c_int, c_int, _P, _P, _P, _P, _P]),
     "ccmpc_mvoe_halfplane_sweep": (c_int, [_P, _P, _P, c_int64, c_int, c_int, c_int, c_double, c_double, c_double,
                                             c_int, c_int, _P, _P, _P, _P, _P]),
@@ -25,14 +26,18 @@ SIGNATURES = {
     "ccmpc_sums_len": (c_int64, [c_int]),
     "ccmpc_sample_sums_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int]),
     "ccmpc_sample_sums": (c_int, [_P, _P, c_int64, c_int64, c_int, _P, _P, c_int64, c_double, _P, _P, _P, c_size_t, _P]),
-    "ccmpc_moments_from_sums": (c_int, [_P, _P, c_int64, c_int, _P, _P, _P, _P, _P, _P]),
+    "ccmpc_moments_from_sums": (c_int, [_P, _P, c_int64, c_int, _P, _P, _P, _P, _P, _P, _P]),
+    "ccmpc_cell_pivot": (c_int, [_P, _P, c_int64, c_int, _P, _P]),
     "ccmpc_minkowski_halfplanes": (c_int, [_P, _P, _P, c_int64, _P, c_int64, c_int, c_int, c_double, c_double,
                                             c_double, c_int, c_int] + [_P] * 12 + [_P]),
     "ccmpc_affine_halfplanes": (c_int, [_P, _P, _P, c_int64, _P, c_int64, c_int, c_int, c_double] + [_P] * 6 + [_P]),
     "ccmpc_violation_counts": (c_int, [_P, _P, c_int64, c_int64, c_int, _P, _P, _P, _P]),
     "ccmpc_vertices_of_bboxes": (c_int, [_P, _P, c_int64, c_double, c_double, c_int64, _P, _P]),
-    "ccmpc_l4_outer": (c_int, [_P, _P, _P, c_int64, c_int64, c_int, _P, c_double, c_double, _P, _P, _P]),
-    "ccmpc_mc_rollout": (c_int, [_P, _P, _P, c_int, _P, c_int64, c_int64, c_int, c_uint64, c_uint64, _P, _P, _P, _P, _P]),
+    "ccmpc_l4_outer": (c_int, [_P, _P, _P, c_int64, c_int64, c_int, _P, _P, c_double, c_double, _P, _P, _P]),
+    "ccmpc_mc_rollout": (c_int, [_P, _P, _P, c_int, _P, c_int64, c_int64, c_int, c_uint64, c_uint64, _P, _P, _P, _P, _P,
+                                  _P]),
+    "ccmpc_yaws_from_positions": (c_int, [_P, _P, c_int64, c_int64, c_int, _P, _P, _P]),
+    "ccmpc_episode_cost": (c_int, [_P, _P, _P, c_int64, c_int, c_double, c_double, _P, _P, _P]),
     "ccmpc_philox4x32": (c_int, [_P, _P, c_int64, _P, _P]),
 }
 

@@ -1,5 +1,6 @@
 // abi.cu - version, last-error string and launch checking of libccmpc.
 #include <stdarg.h>
+#include <atomic>
 #include <string.h>
 
 #include "common.cuh"
@@ -7,6 +8,7 @@
 namespace ccmpc {
 
 static thread_local char g_err[512] = "";
+static std::atomic<uint64_t> g_launches{0};
 
 void set_error(const char* fmt, ...) {
     va_list ap;
@@ -16,6 +18,7 @@ void set_error(const char* fmt, ...) {
 }
 
 int check_launch(const char* what) {
+    g_launches.fetch_add(1, std::memory_order_relaxed);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) {
         set_error("%s: %s", what, cudaGetErrorString(e));
@@ -28,3 +31,4 @@ int check_launch(const char* what) {
 
 extern "C" int ccmpc_version(void) { return CCMPC_VERSION; }
 extern "C" const char* ccmpc_last_error_string(void) { return ccmpc::g_err; }
+extern "C" uint64_t ccmpc_launch_count(void) { return ccmpc::g_launches.load(std::memory_order_relaxed); }

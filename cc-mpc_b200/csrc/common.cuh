@@ -209,7 +209,7 @@ __device__ __forceinline__ double scale_factor(const Sym2& ci, const Sym2& cm, c
 // ---------------------------------------------------------------------------
 struct SumsLayout {
     int T, D;
-    int o_s1, o_s2, o_coll, o_any, o_pen, o_d2s, o_yaw, len;
+    int o_s1, o_s2, o_coll, o_any, o_pen, o_d2s, o_yaw, o_yaw2, len;
     __host__ __device__ explicit SumsLayout(int T_) {
         T = T_;
         D = 2 * T_;
@@ -220,7 +220,8 @@ struct SumsLayout {
         o_pen = o_any + 1;
         o_d2s = o_pen + T;
         o_yaw = o_d2s + T;
-        len = o_yaw + T;
+        o_yaw2 = o_yaw + T;
+        len = o_yaw2 + T;
     }
     __host__ __device__ int s2(int i, int j) const {  // any order
         return i >= j ? o_s2 + i * (i + 1) / 2 + j : o_s2 + j * (j + 1) / 2 + i;

@@ -40,7 +40,8 @@ __global__ void vertices_kernel(const double* __restrict__ centers, const double
 // grid (C, Y): block (c, y) strides over the rows of cell c; thread = (row lane, t).
 __global__ void __launch_bounds__(L4_THREADS)
 l4_outer_kernel(const double* __restrict__ samples, const double* __restrict__ yaws,
-                const int64_t* __restrict__ offsets, int T, const double* __restrict__ yaw_mean, double l, double w,
+                const int64_t* __restrict__ offsets, int T, const double* __restrict__ yaw_mean,
+                const double* __restrict__ lw_cell, double l, double w,
                 double* __restrict__ At, double* __restrict__ b0) {
     __shared__ double s_max[L4_THREADS * 4];
     const int64_t c = blockIdx.x;
@@ -51,6 +52,7 @@ l4_outer_kernel(const double* __restrict__ samples, const double* __restrict__ y
     const double ninf = __longlong_as_double(0xfff0000000000000LL);
     double m0 = ninf, m1 = ninf, m2 = ninf, m3 = ninf;
     double ct = 1.0, stt = 0.0;
+    if (lw_cell) { l = lw_cell[2 * c]; w = lw_cell[2 * c + 1]; }
     if (rl < rpp) {
         sincos(yaw_mean[c * T + t], &stt, &ct);
         const double2* g2 = reinterpret_cast<const double2*>(samples);
@@ -106,8 +108,8 @@ extern "C" int ccmpc_vertices_of_bboxes(const double* centers, const double* the
 }
 
 extern "C" int ccmpc_l4_outer(const double* samples, const double* yaws, const int64_t* offsets, int64_t n_total,
-                              int64_t C, int T, const double* yaw_mean, double l, double w, double* At, double* b0,
-                              void* stream) {
+                              int64_t C, int T, const double* yaw_mean, const double* lw_cell, double l, double w,
+                              double* At, double* b0, void* stream) {
     CCMPC_REQUIRE(T >= 1 && T <= CCMPC_MAX_T && C >= 0 && n_total >= 0, "ccmpc_l4_outer: bad dims");
     CCMPC_REQUIRE(samples && yaws && offsets && yaw_mean && At && b0, "ccmpc_l4_outer: null pointer");
     if (C == 0) return CCMPC_OK;
@@ -121,6 +123,6 @@ extern "C" int ccmpc_l4_outer(const double* samples, const double* yaws, const i
     if (y < 1) y = 1;
     if (y > 1024) y = 1024;
     dim3 grid((unsigned)C, (unsigned)y);
-    l4_outer_kernel<<<grid, L4_THREADS, 0, st>>>(samples, yaws, offsets, T, yaw_mean, l, w, At, b0);
+    l4_outer_kernel<<<grid, L4_THREADS, 0, st>>>(samples, yaws, offsets, T, yaw_mean, lw_cell, l, w, At, b0);
     return check_launch("l4_outer_kernel");
 }

@@ -61,7 +61,7 @@ __global__ void __launch_bounds__(RO_THREADS)
 rollout_kernel(const double* __restrict__ mean, const double* __restrict__ cov, const double* __restrict__ cross,
                int Tm, const double* __restrict__ x0, int64_t n, int Tsh, uint32_t seed_lo, uint32_t seed_hi,
                uint64_t sample_offset, const double* __restrict__ z_in, double* __restrict__ traj,
-               double* __restrict__ z_out, uint8_t* __restrict__ status) {
+               double* __restrict__ z_out, uint8_t* __restrict__ status, double* __restrict__ x0_out) {
     extern __shared__ __align__(16) double smem[];
     StepParams* sp = reinterpret_cast<StepParams*>(smem);                       // [Tsh]
     const int par_d = (Tsh * 11 + 1) & ~1;
@@ -69,7 +69,27 @@ rollout_kernel(const double* __restrict__ mean, const double* __restrict__ cov, 
     const int stride2 = Tsh | 1;
     const int tid = threadIdx.x;
     const int64_t c = blockIdx.y;
+    __shared__ double s_x0[2];
 
+    if (tid == RO_THREADS - 1) {
+        if (x0) {
+            s_x0[0] = x0[2 * c];
+            s_x0[1] = x0[2 * c + 1];
+        } else {
+            // the ONE draw x0 ~ N(mean_0, cov_0) shared by all samples of the cell (v8ideal:2664-2665),
+            // from a reserved Philox counter so that every CTA (and every GPU shard) derives the same value
+            Philox r = philox4x32_10(0xFFFFFFFFu, 0xFFFFFFFFu, (uint32_t)c, 0xFFFFFFFFu, seed_lo, seed_hi);
+            float za, zb;
+            box_muller(r.c[0], r.c[1], za, zb);
+            const double* S0 = cov + (c * Tm) * 4;
+            const double l00 = sqrt(S0[0]);
+            const double l10 = S0[2] / l00;
+            const double l11 = sqrt(S0[3] - l10 * l10);
+            s_x0[0] = mean[(c * Tm) * 2] + l00 * (double)za;
+            s_x0[1] = mean[(c * Tm) * 2 + 1] + fma(l10, (double)za, l11 * (double)zb);
+        }
+        if (x0_out && blockIdx.x == 0) { x0_out[2 * c] = s_x0[0]; x0_out[2 * c + 1] = s_x0[1]; }
+    }
     if (tid < Tsh) {
         const int t = tid;
         const double* mt = mean + (c * Tm + t) * 2;
@@ -107,7 +127,7 @@ rollout_kernel(const double* __restrict__ mean, const double* __restrict__ cov, 
     const int64_t i = i0 + tid;
     const int rows = (int)min((int64_t)RO_THREADS, n - i0);
     if (i < n) {
-        double x = x0[2 * c], y = x0[2 * c + 1];
+        double x = s_x0[0], y = s_x0[1];
         const uint64_t gi = sample_offset + (uint64_t)i;
         const double2* zin2 = z_in ? reinterpret_cast<const double2*>(z_in) + (c * n + i) * Tsh : nullptr;
         double2* zout2 = z_out ? reinterpret_cast<double2*>(z_out) + (c * n + i) * Tsh : nullptr;
@@ -164,11 +184,11 @@ using namespace ccmpc;
 extern "C" int ccmpc_mc_rollout(const double* mean, const double* cov, const double* cross, int Tm,
                                 const double* x0, int64_t C, int64_t n, int Tsh, uint64_t seed,
                                 uint64_t sample_offset, const double* z, double* traj, double* z_out,
-                                uint8_t* status, void* stream) {
+                                uint8_t* status, double* x0_out, void* stream) {
     CCMPC_REQUIRE(Tsh >= 1 && Tsh <= CCMPC_MAX_T, "ccmpc_mc_rollout: need 1 <= Tsh <= %d", CCMPC_MAX_T);
     CCMPC_REQUIRE(Tm >= Tsh + 1, "ccmpc_mc_rollout: moments must cover Tsh + 1 steps (Tm = %d, Tsh = %d)", Tm, Tsh);
     CCMPC_REQUIRE(C >= 0 && n >= 0 && C < 65536, "ccmpc_mc_rollout: bad C / n");
-    CCMPC_REQUIRE(mean && cov && cross && x0 && traj, "ccmpc_mc_rollout: null pointer");
+    CCMPC_REQUIRE(mean && cov && cross && traj, "ccmpc_mc_rollout: null pointer");
     if (C == 0 || n == 0) return CCMPC_OK;
     cudaStream_t st = (cudaStream_t)stream;
     if (status) {
@@ -179,7 +199,8 @@ extern "C" int ccmpc_mc_rollout(const double* mean, const double* cov, const dou
     const size_t smem = (size_t)par_d * 8 + (size_t)RO_THREADS * (Tsh | 1) * 16;
     dim3 grid((unsigned)((n + RO_THREADS - 1) / RO_THREADS), (unsigned)C);
     rollout_kernel<<<grid, RO_THREADS, smem, st>>>(mean, cov, cross, Tm, x0, n, Tsh, (uint32_t)seed,
-                                                   (uint32_t)(seed >> 32), sample_offset, z, traj, z_out, status);
+                                                   (uint32_t)(seed >> 32), sample_offset, z, traj, z_out, status,
+                                                   x0_out);
     return check_launch("rollout_kernel");
 }
 

@@ -44,7 +44,7 @@ struct StatsGeom {
     __host__ size_t smem_bytes() const {
         size_t tile = (size_t)ch * DP;
         size_t red = (size_t)ns * ntile * 16;
-        size_t red2 = (size_t)ST_THREADS * 6;
+        size_t red2 = (size_t)ST_THREADS * 7;
         size_t m = tile > red ? tile : red;
         if (red2 > m) m = red2;
         return m * 8 + (size_t)ch * 4 + (size_t)4 * T * 8 + 16;
@@ -130,7 +130,7 @@ __global__ void __launch_bounds__(ST_THREADS, 2) sample_sums_kernel(const StatsA
     size_t tile_d = (size_t)a.ch * DP;
     size_t red_d = (size_t)a.ns * a.ntile * 16;
     size_t big = tile_d > red_d ? tile_d : red_d;
-    if ((size_t)ST_THREADS * 6 > big) big = (size_t)ST_THREADS * 6;
+    if ((size_t)ST_THREADS * 7 > big) big = (size_t)ST_THREADS * 7;
     double* tile = smem;
     double* s_piv = smem + big;                 // [2T]
     double* s_ego = s_piv + 2 * T;              // [2T]
@@ -164,7 +164,7 @@ __global__ void __launch_bounds__(ST_THREADS, 2) sample_sums_kernel(const StatsA
     double acc[16];
 #pragma unroll
     for (int i = 0; i < 16; ++i) acc[i] = 0.0;
-    double s1x = 0.0, s1y = 0.0, pen = 0.0, d2s = 0.0, yaw_sum = 0.0;
+    double s1x = 0.0, s1y = 0.0, pen = 0.0, d2s = 0.0, yaw_sum = 0.0, yaw_sq = 0.0;
     int coll = 0, any_cnt = 0;
 
     double2 pre[ST_MAXP];
@@ -208,7 +208,7 @@ __global__ void __launch_bounds__(ST_THREADS, 2) sample_sums_kernel(const StatsA
                         s_any[row] = 1;
                     }
                 }
-                if (do_yaw) yaw_sum += ypre[p];
+                if (do_yaw) { yaw_sum += ypre[p]; yaw_sq = fma(ypre[p], ypre[p], yaw_sq); }
             }
         }
         __syncthreads();
@@ -263,25 +263,27 @@ __global__ void __launch_bounds__(ST_THREADS, 2) sample_sums_kernel(const StatsA
         }
     }
     __syncthreads();
-    red[tid * 6 + 0] = s1x;
-    red[tid * 6 + 1] = s1y;
-    red[tid * 6 + 2] = (double)coll;
-    red[tid * 6 + 3] = pen;
-    red[tid * 6 + 4] = d2s;
-    red[tid * 6 + 5] = yaw_sum;
+    red[tid * 7 + 0] = s1x;
+    red[tid * 7 + 1] = s1y;
+    red[tid * 7 + 2] = (double)coll;
+    red[tid * 7 + 3] = pen;
+    red[tid * 7 + 4] = d2s;
+    red[tid * 7 + 5] = yaw_sum;
+    red[tid * 7 + 6] = yaw_sq;
     if (any_cnt) atomicAdd(&s_anycnt, any_cnt);
     __syncthreads();
     if (tid < T) {
-        double r[6] = {0, 0, 0, 0, 0, 0};
+        double r[7] = {0, 0, 0, 0, 0, 0, 0};
         for (int k = 0; k < a.rpp; ++k)
 #pragma unroll
-            for (int q = 0; q < 6; ++q) r[q] += red[(k * T + tid) * 6 + q];
+            for (int q = 0; q < 7; ++q) r[q] += red[(k * T + tid) * 7 + q];
         out[L.o_s1 + 2 * tid] = r[0];
         out[L.o_s1 + 2 * tid + 1] = r[1];
         out[L.o_coll + tid] = r[2];
         out[L.o_pen + tid] = r[3];
         out[L.o_d2s + tid] = r[4];
         out[L.o_yaw + tid] = r[5];
+        out[L.o_yaw2 + tid] = r[6];
     }
     if (tid == 0) {
         out[0] = (double)rows_unit;
@@ -306,7 +308,8 @@ __global__ void sums_finalize_kernel(const double* __restrict__ partials, const 
 // ---------------------------------------------------------------------------
 __global__ void moments_kernel(const double* __restrict__ sums, const double* __restrict__ pivot, int T,
                                double* __restrict__ mean, double* __restrict__ cov, double* __restrict__ cross,
-                               int64_t* __restrict__ counts, double* __restrict__ yaw_mean) {
+                               int64_t* __restrict__ counts, double* __restrict__ yaw_mean,
+                               double* __restrict__ yaw_var) {
     const SumsLayout L(T);
     const int64_t c = blockIdx.x;
     const double* s = sums + c * (int64_t)L.len;
@@ -341,6 +344,8 @@ __global__ void moments_kernel(const double* __restrict__ sums, const double* __
             }
             if (counts) counts[c * (T + 1) + t] = (int64_t)llrint(s[L.o_coll + t]);
             if (yaw_mean) yaw_mean[c * T + t] = s[L.o_yaw + t] / n;
+            // np.cov(yawData[:, t]) (v8ideal:876), ddof = 1
+            if (yaw_var) yaw_var[c * T + t] = (s[L.o_yaw2 + t] - s[L.o_yaw + t] * s[L.o_yaw + t] / n) * inv_nm1;
         }
     }
     if (threadIdx.x == 0 && counts) counts[c * (T + 1) + T] = (int64_t)llrint(s[L.o_any]);
@@ -394,6 +399,17 @@ violation_kernel(const double* __restrict__ samples, const int64_t* __restrict__
     __syncthreads();
     for (int p = tid; p < P; p += ST_THREADS)
         if (s_cnt[p]) atomicAdd(viol + c * P + p, (unsigned long long)s_cnt[p]);
+}
+
+// pivot[c] = first sample of cell c (zeros when the cell is empty)
+__global__ void cell_pivot_kernel(const double* __restrict__ samples, const int64_t* __restrict__ offsets,
+                                  int64_t C, int T, double* __restrict__ pivot) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= C * 2 * T) return;
+    const int64_t c = i / (2 * T);
+    const int j = (int)(i - c * 2 * T);
+    const int64_t b = offsets[c], e = offsets[c + 1];
+    pivot[i] = e > b ? samples[b * 2 * T + j] : 0.0;
 }
 
 }  // namespace ccmpc
@@ -455,10 +471,11 @@ extern "C" int ccmpc_sample_sums(const double* samples, const int64_t* offsets, 
 
 extern "C" int ccmpc_moments_from_sums(const double* sums, const double* pivot, int64_t C, int T, double* mean,
                                        double* cov, double* cross, int64_t* counts, double* yaw_mean,
-                                       void* stream) {
+                                       double* yaw_var, void* stream) {
     CCMPC_REQUIRE(T >= 1 && T <= CCMPC_MAX_T && C >= 0 && sums && pivot, "ccmpc_moments_from_sums: bad arguments");
     if (C == 0) return CCMPC_OK;
-    moments_kernel<<<(unsigned)C, 256, 0, (cudaStream_t)stream>>>(sums, pivot, T, mean, cov, cross, counts, yaw_mean);
+    moments_kernel<<<(unsigned)C, 256, 0, (cudaStream_t)stream>>>(sums, pivot, T, mean, cov, cross, counts, yaw_mean,
+                                                                  yaw_var);
     return check_launch("moments_kernel");
 }
 
@@ -481,4 +498,13 @@ extern "C" int ccmpc_violation_counts(const double* samples, const int64_t* offs
     violation_kernel<<<grid, ST_THREADS, 0, st>>>(samples, offsets, T, nd, idx_side,
                                                   reinterpret_cast<unsigned long long*>(viol));
     return check_launch("violation_kernel");
+}
+
+extern "C" int ccmpc_cell_pivot(const double* samples, const int64_t* offsets, int64_t C, int T, double* pivot,
+                                void* stream) {
+    CCMPC_REQUIRE(T >= 1 && T <= CCMPC_MAX_T && C >= 0 && offsets && pivot, "ccmpc_cell_pivot: bad arguments");
+    if (C == 0) return CCMPC_OK;
+    const int64_t tot = C * 2 * T;
+    cell_pivot_kernel<<<(unsigned)((tot + 127) / 128), 128, 0, (cudaStream_t)stream>>>(samples, offsets, C, T, pivot);
+    return check_launch("cell_pivot_kernel");
 }

@@ -1,0 +1,712 @@
+"""Planner-level constraint build: the hot methods of the reference's
+``MidlevelAgent`` (collect/in_simulation/midlevel/v8ideal/__init__.py, "v8ideal")
+on libccmpc.
+
+What is mirrored (same names, argument meaning and quirks):
+  compute_obstacle_constraints_GMM_Minkowski_idealprediction   v8ideal:781-964
+  compute_obstacle_constraints_GMM_affine                      v8ideal:1378-1539
+  predict_ideal                                                v8ideal:2620-2711
+  save_moments                                                 v8ideal:2575-2618
+  __compute_vertices / __compute_overapproximations            v8ideal:627-640, :694-736
+  eps_ura allocation                                           v8ideal:2920-2926
+The cvxpy / CPLEX solve, CARLA and plotting stay with the reference planner:
+this class hands it half-plane rows (n, d, side) / (A, b), the L4 polytopes and
+the bookkeeping tuples it stores in its ``_cov`` pickle.
+
+All arithmetic runs in the sm_100a kernels behind include/ccmpc.h; this file
+only packs cells, owns device buffers and converts results to the nested
+Python containers the reference planner indexes.  No CPU fallback.
+"""
+from __future__ import annotations
+
+import os
+import pickle
+from dataclasses import dataclass, field
+from typing import Dict, List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import ops
+
+EPS_TOTAL = 0.05                   # v8ideal:2920
+BBOX_DEFAULT = (3.7, 1.79)         # v8ideal:792
+N_IDEAL_SAMPLES = 1_000_000        # v8ideal:2640
+
+
+class InSimulationException(Exception):
+    """Same name as collect/exception.py:11 so planner-side ``except`` clauses keep working."""
+
+
+def _device(device=None) -> torch.device:
+    if not torch.cuda.is_available():
+        raise RuntimeError("ccmpc_b200 needs a CUDA device (there is no CPU fallback)")
+    return torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+
+
+def eps_allocation(K_per_obstacle: Sequence[int], eps: float = EPS_TOTAL) -> np.ndarray:
+    """eps_ura[o, k] = eps / O for k < K_o (v8ideal:2920-2926)."""
+    O = len(K_per_obstacle)
+    out = np.zeros((O, int(max(K_per_obstacle)) if O else 0))
+    for o in range(O):
+        out[o, :int(K_per_obstacle[o])] = eps / O
+    return out
+
+
+def _h2d(arr: np.ndarray, device, dtype=None) -> torch.Tensor:
+    """Host ndarray -> device through a pinned staging buffer (async on the current stream)."""
+    t = torch.from_numpy(np.ascontiguousarray(arr))
+    if dtype is not None and t.dtype != dtype:
+        t = t.to(dtype)
+    return t.pin_memory().to(device, non_blocking=True)
+
+
+@dataclass
+class CellBatch:
+    """Device-resident samples of all (obstacle, mode) cells of one MPC step.
+
+    ``samples`` is the row-major concatenation of the reference's
+    ``ovehicle.pred_positions[latent_idx]`` arrays ((N_k, T, 2) each), obstacle-major,
+    mode-minor - the layout of ``np.vstack(...)`` at v8ideal:890 - with CSR ``offsets``."""
+    samples: torch.Tensor                  # [N, T, 2] float64
+    yaws: Optional[torch.Tensor]           # [N, T] float64
+    offsets: torch.Tensor                  # [C+1] int64 (device)
+    offsets_host: np.ndarray               # [C+1] int64
+    cell_obstacle: np.ndarray              # [C] int
+    cell_mode: np.ndarray                  # [C] int
+    n_states: List[int]                    # K_o per obstacle
+    lw_cell: Optional[torch.Tensor] = None  # [C, 2] float64 (ovehicle.bbox per cell)
+    bboxes: Optional[np.ndarray] = None    # [O, 2] host
+
+    @property
+    def C(self) -> int:
+        return int(self.offsets_host.size - 1)
+
+    @property
+    def T(self) -> int:
+        return int(self.samples.shape[1])
+
+    @property
+    def O(self) -> int:
+        return len(self.n_states)
+
+    @property
+    def N(self) -> int:
+        return int(self.samples.shape[0])
+
+    def cell_index(self, o: int, k: int) -> int:
+        hit = np.nonzero((self.cell_obstacle == o) & (self.cell_mode == k))[0]
+        if hit.size == 0:
+            raise KeyError((o, k))
+        return int(hit[0])
+
+    @classmethod
+    def from_ovehicles(cls, ovehicles, device=None, with_yaws: bool = True) -> "CellBatch":
+        """Pack reference ``OVehicle`` objects (attributes ``pred_positions``, ``pred_yaws``,
+        ``n_states``, ``bbox``; midlevel/ovehicle.py:119-131) into one device batch."""
+        device = _device(device)
+        pos, yaw, offs, co, ck, ns, bb = [], [], [0], [], [], [], []
+        T = None
+        for o, ov in enumerate(ovehicles):
+            ns.append(int(ov.n_states))
+            bb.append(np.asarray(getattr(ov, "bbox", BBOX_DEFAULT), dtype=np.float64))
+            for k in range(int(ov.n_states)):
+                p = np.asarray(ov.pred_positions[k], dtype=np.float64)
+                if p.ndim != 3 or p.shape[2] != 2:
+                    raise ValueError("pred_positions[k] must be (N_k, T, 2)")
+                if T is None:
+                    T = p.shape[1]
+                elif p.shape[1] != T:
+                    raise ValueError("all cells must share the horizon T")
+                pos.append(p)
+                if with_yaws:
+                    y = np.asarray(ov.pred_yaws[k], dtype=np.float64)
+                    if y.shape != p.shape[:2]:
+                        raise ValueError("pred_yaws[k] must be (N_k, T)")
+                    yaw.append(y)
+                offs.append(offs[-1] + p.shape[0])
+                co.append(o)
+                ck.append(k)
+        if not pos:
+            raise ValueError("no cells")
+        flat = np.concatenate(pos, axis=0)
+        offsets_host = np.asarray(offs, dtype=np.int64)
+        bboxes = np.stack(bb)
+        return cls(samples=_h2d(flat, device),
+                   yaws=_h2d(np.concatenate(yaw, axis=0), device) if with_yaws else None,
+                   offsets=_h2d(offsets_host, device), offsets_host=offsets_host,
+                   cell_obstacle=np.asarray(co), cell_mode=np.asarray(ck), n_states=ns,
+                   lw_cell=_h2d(bboxes[np.asarray(co)], device), bboxes=bboxes)
+
+    @classmethod
+    def uniform(cls, traj: torch.Tensor, cell_obstacle, cell_mode, n_states) -> "CellBatch":
+        """Cells of equal size from a [C, n, T, 2] device tensor (e.g. a rollout)."""
+        C, n, T, _ = traj.shape
+        offsets_host = np.arange(C + 1, dtype=np.int64) * n
+        return cls(samples=traj.reshape(C * n, T, 2), yaws=None,
+                   offsets=torch.arange(C + 1, dtype=torch.int64, device=traj.device) * n,
+                   offsets_host=offsets_host, cell_obstacle=np.asarray(cell_obstacle),
+                   cell_mode=np.asarray(cell_mode), n_states=list(n_states))
+
+
+@dataclass
+class Moments:
+    """Sample moments of one step in the save_moments layout, device resident."""
+    mean: torch.Tensor       # [C, T, 2]
+    cov: torch.Tensor        # [C, T, 2, 2]
+    cross: torch.Tensor      # [C, T, T, 2, 2]  (tau < t filled)
+    cell_obstacle: np.ndarray
+    cell_mode: np.ndarray
+    n_states: List[int]
+    T: int
+
+    def nested(self) -> dict:
+        """The dict the reference pickles (v8ideal:2580-2610): nested lists sized
+        (O, max K, T[, T-1]) with ``None`` in unused slots."""
+        O, Kmax, T = len(self.n_states), max(self.n_states), self.T
+        mean = self.mean.cpu().numpy()
+        cov = self.cov.cpu().numpy()
+        cross = self.cross.cpu().numpy()
+        mean_l = np.empty((O, Kmax, T), dtype=object).tolist()
+        cov_l = np.empty((O, Kmax, T), dtype=object).tolist()
+        cross_l = np.empty((O, Kmax, T, max(T - 1, 0)), dtype=object).tolist()
+        for c, (o, k) in enumerate(zip(self.cell_obstacle, self.cell_mode)):
+            for t in range(T):
+                mean_l[o][k][t] = mean[c, t].copy()
+                cov_l[o][k][t] = cov[c, t].copy()
+                for tau in range(t):
+                    cross_l[o][k][t][tau] = cross[c, t, tau].copy()
+        return {"mean_p0p1": mean_l, "cov_p0p1": cov_l, "cross_cov": cross_l}
+
+    @classmethod
+    def from_nested(cls, d: dict, device=None) -> "Moments":
+        """Inverse of :meth:`nested` (reads a reference ``_moments`` pickle payload)."""
+        device = _device(device)
+        mean_l, cov_l, cross_l = d["mean_p0p1"], d["cov_p0p1"], d["cross_cov"]
+        O = len(mean_l)
+        co, ck, ns = [], [], []
+        T = None
+        for o in range(O):
+            kk = [k for k in range(len(mean_l[o])) if mean_l[o][k] is not None and mean_l[o][k][0] is not None]
+            ns.append(len(kk))
+            for k in kk:
+                co.append(o)
+                ck.append(k)
+                T = len(mean_l[o][k])
+        C = len(co)
+        mean = np.zeros((C, T, 2))
+        cov = np.zeros((C, T, 2, 2))
+        cross = np.zeros((C, T, T, 2, 2))
+        for c, (o, k) in enumerate(zip(co, ck)):
+            for t in range(T):
+                mean[c, t] = mean_l[o][k][t]
+                cov[c, t] = cov_l[o][k][t]
+                for tau in range(t):
+                    cross[c, t, tau] = cross_l[o][k][t][tau]
+        return cls(_h2d(mean, device), _h2d(cov, device), _h2d(cross, device), np.asarray(co), np.asarray(ck), ns, T)
+
+
+@dataclass
+class HalfPlanes:
+    """Rows of one builder call.  Minkowski: one row per (cell, pair p = t(t-1)/2 + tau);
+    affine: one row per (cell, t).  ``side`` = +1 for ``n.x >= rhs`` and -1 for ``n.x <= rhs``."""
+    n: np.ndarray            # [..., 2]
+    d: np.ndarray            # [...]
+    rhs: np.ndarray          # [...]  (= d for Minkowski; d +- offset for affine)
+    idx: np.ndarray          # [...] best_idx of choose_closest_tangent
+    side: np.ndarray         # [...]
+    t: np.ndarray            # [...] timestep each row constrains
+    status: np.ndarray       # [...] CCMPC_ST_*
+    cell_obstacle: np.ndarray
+    cell_mode: np.ndarray
+    extra: Dict[str, np.ndarray] = field(default_factory=dict)
+
+    def A_b(self):
+        """(A, b) with A x <= b, the form v8ideal:933-939 saves."""
+        A = -self.side[..., None] * self.n
+        b = -self.side * self.rhs
+        return A, b
+
+    def cvxpy_constraints(self, temp_x):
+        """Rows as cvxpy constraints on the planner's ``temp_x`` (v8ideal:927-936 / :1503-1515)."""
+        import cvxpy as cp  # planner-side dependency; not needed by the kernels
+        rows = []
+        flat_n = self.n.reshape(-1, 2)
+        for r in range(flat_n.shape[0]):
+            t = int(self.t.reshape(-1)[r])
+            lhs = flat_n[r].T @ cp.vstack([temp_x[t][0], temp_x[t][1]])
+            rhs = float(self.rhs.reshape(-1)[r])
+            rows.append(lhs >= rhs if self.side.reshape(-1)[r] > 0 else lhs <= rhs)
+        return rows
+
+
+def _pair_t(T: int) -> np.ndarray:
+    return np.asarray([t for t in range(T) for _ in range(t)], dtype=np.int32)
+
+
+class MidlevelConstraints:
+    """Owner of the device buffers and the per-step moment cache of one planner."""
+
+    def __init__(self, prediction_horizon: int, ego_vehicle_id: int = 0, out_dir: Optional[str] = "out/data",
+                 device=None, R: float = ops.R_EV_OV, target_p: float = ops.TARGET_P,
+                 n_ideal_samples: int = N_IDEAL_SAMPLES, seed: int = 0, accel: bool = False,
+                 frame_stride: int = 10):
+        if not 1 <= prediction_horizon <= ops.MAX_T:
+            raise ValueError(f"prediction_horizon must be in 1..{ops.MAX_T}")
+        self.prediction_horizon = int(prediction_horizon)
+        self.ego_vehicle_id = ego_vehicle_id
+        self.out_dir = out_dir
+        self.device = _device(device)
+        self.R = float(R)
+        self.target_p = float(target_p)
+        self.n_ideal_samples = int(n_ideal_samples)
+        self.seed = int(seed)
+        self.accel = bool(accel)
+        self.frame_stride = int(frame_stride)          # predict_ideal reads frame - 10 (v8ideal:2626)
+        self._moments: Dict[int, Moments] = {}
+        self._calls = 0
+        self.prob_lower_save = None
+        self.last_ideal: Optional[CellBatch] = None
+
+    # ------------------------------------------------------------------ sums
+    def _sums(self, cells: CellBatch, ego=None, pivot=None):
+        if pivot is None:
+            pivot = ops.cell_pivot(cells.samples, cells.offsets)
+        ego_t = None if ego is None else _h2d(np.asarray(ego, dtype=np.float64), self.device)
+        sums = ops.sample_sums(cells.samples, cells.offsets, pivot, ego=ego_t, yaws=cells.yaws, R=self.R)
+        return sums, pivot
+
+    def _eps_cells(self, cells: CellBatch, eps_ura) -> torch.Tensor:
+        e = np.asarray(eps_ura, dtype=np.float64)
+        return _h2d(e[cells.cell_obstacle, cells.cell_mode], self.device)
+
+    # ---------------------------------------------------------- save_moments
+    def moments_of(self, cells: CellBatch, sums=None, pivot=None) -> Moments:
+        if sums is None:
+            sums, pivot = self._sums(cells)
+        m = ops.moments_from_sums(sums, pivot, want_counts=False, want_yaw=False)
+        return Moments(m["mean"], m["cov"], m["cross"], cells.cell_obstacle, cells.cell_mode, cells.n_states, cells.T)
+
+    def save_moments(self, ovehicles, O, K, T, Tpred, ego_vehicle_id, params, _precomputed: Moments = None):
+        """v8ideal:2575-2618.  Keeps the moments on the device for the next step's
+        :meth:`predict_ideal` and (when ``out_dir`` is set) also writes the reference's
+        ``agent{id}_frame{f}_moments`` pickle.  Returns the :class:`Moments`."""
+        if _precomputed is None:
+            cells = ovehicles if isinstance(ovehicles, CellBatch) else CellBatch.from_ovehicles(
+                ovehicles, self.device, with_yaws=False)
+            if cells.T != T:
+                # the reference strides the vstack by T (:2588); only T' == T is meaningful
+                raise ValueError(f"save_moments: cells have horizon {cells.T}, T = {T}")
+            _precomputed = self.moments_of(cells)
+        frame = int(getattr(params, "frame", 0))
+        self._moments[frame] = _precomputed
+        for old in [f for f in self._moments if f < frame - 4 * self.frame_stride]:
+            del self._moments[old]
+        if self.out_dir:
+            path = os.path.join(self.out_dir, f"agent{ego_vehicle_id}_frame{frame}_moments")
+            try:
+                os.makedirs(self.out_dir, exist_ok=True)
+                with open(path, "wb") as f:
+                    pickle.dump(_precomputed.nested(), f)
+            except OSError:
+                pass    # the reference logs and continues (:2615-2618)
+        return _precomputed
+
+    def _load_moments(self, frame: int, ego_vehicle_id) -> Moments:
+        if frame in self._moments:
+            return self._moments[frame]
+        if self.out_dir:
+            path = os.path.join(self.out_dir, f"agent{ego_vehicle_id}_frame{frame}_moments")
+            if os.path.isfile(path):
+                with open(path, "rb") as f:
+                    m = Moments.from_nested(pickle.load(f), self.device)
+                self._moments[frame] = m
+                return m
+        raise InSimulationException(f"no moments of frame {frame} (predict_ideal needs the step {self.frame_stride} "
+                                    f"frames earlier, v8ideal:2626)")
+
+    # --------------------------------------------------------- predict_ideal
+    def predict_ideal_cells(self, n_states: Sequence[int], T: int, moments: Moments, x0=None, z=None,
+                            n_samples: Optional[int] = None, seed: Optional[int] = None,
+                            sample_offset: int = 0) -> CellBatch:
+        """Device form of predict_ideal: one [C, n, T, 2] rollout for all (o, k)."""
+        n = self.n_ideal_samples if n_samples is None else int(n_samples)
+        if moments.T < T + 1:
+            raise InSimulationException(f"moments cover {moments.T} steps; predict_ideal indexes [t+1] up to {T}")
+        sel, co, ck = [], [], []
+        Kmax_saved = max(moments.n_states) if moments.n_states else 0
+        for o, K_o in enumerate(n_states):
+            for k in range(int(K_o)):
+                data_idx = k if k < Kmax_saved else max(Kmax_saved - 1, 0)        # v8ideal:2652-2656
+                hit = np.nonzero((moments.cell_obstacle == o) & (moments.cell_mode == data_idx))[0]
+                if hit.size == 0:
+                    raise InSimulationException(f"saved moments have no entry for obstacle {o} mode {data_idx}")
+                sel.append(int(hit[0]))
+                co.append(o)
+                ck.append(k)
+        idx = torch.as_tensor(sel, dtype=torch.int64, device=self.device)
+        mean = moments.mean.index_select(0, idx).contiguous()
+        cov = moments.cov.index_select(0, idx).contiguous()
+        cross = moments.cross.index_select(0, idx).contiguous()
+        x0_t = None if x0 is None else _h2d(np.asarray(x0, dtype=np.float64).reshape(len(sel), 2), self.device)
+        if seed is None:
+            self._calls += 1
+            seed = (self.seed << 20) + self._calls
+        traj, _, status, x0_used = ops.mc_rollout(mean, cov, cross, x0_t, n, T, seed=seed, sample_offset=sample_offset,
+                                                  z=z)
+        cells = CellBatch.uniform(traj, co, ck, n_states)
+        cells.status = status
+        cells.x0 = x0_used
+        return cells
+
+    def predict_ideal(self, ovehicles, T, ego_vehicle_id, params, as_numpy: bool = False, **kw):
+        """v8ideal:2620-2711.  ``{ov_idx: {latent_idx: (n_samples, T, 2)}}`` - device tensors
+        (views of one buffer) unless ``as_numpy``.  A non-PD conditional covariance raises
+        ``np.linalg.LinAlgError`` like ``np.linalg.cholesky`` (:2696)."""
+        frame = int(getattr(params, "frame", 0)) - self.frame_stride
+        moments = self._load_moments(frame, ego_vehicle_id)
+        n_states = ovehicles.n_states if isinstance(ovehicles, CellBatch) else [int(ov.n_states) for ov in ovehicles]
+        cells = self.predict_ideal_cells(n_states, T, moments, **kw)
+        st = cells.status.cpu().numpy()
+        if st.any():
+            bad = int(np.nonzero(st)[0][0])
+            raise np.linalg.LinAlgError("Singular matrix" if st[bad] == ops.ST_SINGULAR
+                                        else "Matrix is not positive definite")
+        self.last_ideal = cells
+        n = cells.N // cells.C
+        traj = cells.samples.reshape(cells.C, n, T, 2)
+        out: Dict[int, Dict[int, object]] = {}
+        for c, (o, k) in enumerate(zip(cells.cell_obstacle, cells.cell_mode)):
+            out.setdefault(int(o), {})[int(k)] = traj[c].cpu().numpy() if as_numpy else traj[c]
+        return out
+
+    # --------------------------------------------------------------- builders
+    def minkowski(self, cells: CellBatch, ref_traj, eps_ura, ego=None, want_violations: bool = False,
+                  fields=ops.MINK_FIELDS):
+        """Device core of v8ideal:881-947 on one CellBatch -> (out dict of device tensors, sums, pivot)."""
+        T = cells.T
+        ref = _h2d(np.asarray(ref_traj, dtype=np.float64)[:T, :2], self.device)
+        sums, pivot = self._sums(cells, ego=ego)
+        out = ops.minkowski_alloc(cells.C, T, self.device, fields=fields)
+        ops.minkowski_halfplanes(sums, pivot, ref, self._eps_cells(cells, eps_ura), self.prediction_horizon,
+                                 R=self.R, target_p=self.target_p, accel=self.accel, out=out)
+        if want_violations:
+            out["viol"] = ops.violation_counts(cells.samples, cells.offsets, out["nd"], out["idx_side"])
+        return out, sums, pivot
+
+    def _l4(self, cells: CellBatch, sums, pivot):
+        mom = ops.moments_from_sums(sums, pivot, want_cross=False, want_counts=True, want_yaw=True)
+        At, b0 = ops.l4_outer(cells.samples, cells.yaws, cells.offsets, mom["yaw_mean"], lw_cell=cells.lw_cell)
+        return At, b0, mom
+
+    @staticmethod
+    def _nested_tko(cells: CellBatch, arr: np.ndarray, T: int):
+        """[C, T, ...] -> nested list [t][k][o] sized (T, max K, O) (v8ideal:631, :714-716)."""
+        O, Kmax = cells.O, max(cells.n_states)
+        out = np.empty((T, Kmax, O), dtype=object).tolist()
+        for c, (o, k) in enumerate(zip(cells.cell_obstacle, cells.cell_mode)):
+            for t in range(T):
+                out[t][k][o] = arr[c, t]
+        return out
+
+    @staticmethod
+    def _nested_ok(cells: CellBatch, vec: np.ndarray):
+        O, Kmax = cells.O, max(cells.n_states)
+        out = np.empty((O, Kmax), dtype=object).tolist()
+        for c, (o, k) in enumerate(zip(cells.cell_obstacle, cells.cell_mode)):
+            out[o][k] = vec[c]
+        return out
+
+    def _ov_state(self, cells: CellBatch, mom: dict):
+        """ovStateMean_tau_1 / ovStateCov_tau_1 tuples (v8ideal:871-876)."""
+        mean = mom["mean"].cpu().numpy()
+        cov = mom["cov"].cpu().numpy()
+        ym = mom["yaw_mean"].cpu().numpy()
+        yv = mom["yaw_var"].cpu().numpy()
+        f = lambda v: self._nested_ok(cells, v)
+        ov_mean = (f(mean[:, 0, 0]), f(mean[:, 0, 1]), f(ym[:, 0]))
+        ov_cov = (f(cov[:, 0, 0, 0]), f(cov[:, 0, 1, 1]), f(yv[:, 0]))
+        # OV_injuction (v8ideal:834-844): per obstacle, decided by its LAST latent
+        inj = [None] * cells.O
+        for c, o in enumerate(cells.cell_obstacle):
+            inj[o] = not (mean[c, 0, 0] >= 190 or mean[c, 0, 1] <= -80)
+        return ov_mean, ov_cov, inj
+
+    def _vertices(self, cells: CellBatch):
+        """Lazy ``vertices[t][k][o]`` (N_k, 4, 2) device tensors (v8ideal:627-640)."""
+        T = cells.T
+
+        def make():
+            out = np.empty((T, max(cells.n_states), cells.O), dtype=object).tolist()
+            for c, (o, k) in enumerate(zip(cells.cell_obstacle, cells.cell_mode)):
+                b, e = cells.offsets_host[c], cells.offsets_host[c + 1]
+                for t in range(T):
+                    out[t][k][o] = ops.vertices_of_bboxes(cells.samples[b:e, t].contiguous(),
+                                                          cells.yaws[b:e, t].contiguous(), cells.bboxes[o])
+            return out
+        return make
+
+    def compute_obstacle_constraints_GMM_Minkowski_idealprediction(
+            self, params, ovehicles, Delta2=None, Omicron=None, temp_x=None, eps_ura=None, segments=None,
+            Tsh=None, ref_traj=None, ego=None, want_violations=False):
+        """v8ideal:781-964.  Returns the reference's 9-tuple
+        ``(constraints, vertices, A_union, b_union, OVconstraint, direct, ovStateMean_tau_1,
+        ovStateCov_tau_1, 0)`` where ``constraints`` is a :class:`HalfPlanes` (or the list of
+        cvxpy rows when ``temp_x`` is given) and ``vertices`` is a zero-argument callable that
+        materialises the per-sample box corners on demand (only plots read them)."""
+        cells = ovehicles if isinstance(ovehicles, CellBatch) else CellBatch.from_ovehicles(ovehicles, self.device)
+        Tpred = self.prediction_horizon
+        T = int(Tsh if Tsh is not None else Tpred)
+        if eps_ura is None:
+            eps_ura = eps_allocation(cells.n_states)
+        if cells.T != Tpred:
+            raise ValueError(f"cells carry horizon {cells.T}; the planner's prediction_horizon is {Tpred}")
+        # sums of the raw predictions: L4 polytopes, [tau+1|tau] bookkeeping, and the rows when T == Tpred
+        if T < Tpred:
+            self.predict_ideal(cells, T, self.ego_vehicle_id, params)               # :824-825
+            work = self.last_ideal
+            out, sums_w, pivot_w = self.minkowski(work, ref_traj, eps_ura, ego=ego, want_violations=want_violations)
+            sums_c, pivot_c = self._sums(cells)
+        else:
+            work = cells
+            out, sums_w, pivot_w = self.minkowski(cells, ref_traj, eps_ura, ego=ego, want_violations=want_violations)
+            sums_c, pivot_c = sums_w, pivot_w
+        At, b0, mom = self._l4(cells, sums_c, pivot_c)                               # :951-954
+        moments = self.moments_of(work, sums_w, pivot_w)
+        # ---- one synchronising copy of the small results
+        host = {k: v.cpu().numpy() for k, v in out.items()}
+        A_union = self._nested_tko(cells, At.cpu().numpy(), Tpred)
+        b_union = self._nested_tko(cells, b0.cpu().numpy(), Tpred)
+        ov_mean, ov_cov, inj = self._ov_state(cells, mom)
+        OVconstraint = any(bool(v) for v in inj)
+        direct = [None] * cells.O
+        side = np.where(host["idx_side"] & 2, -1, 1).astype(np.int32)
+        C, P = side.shape
+        hp = HalfPlanes(n=host["nd"][..., :2], d=host["nd"][..., 2], rhs=host["nd"][..., 2],
+                        idx=(host["idx_side"] & 1).astype(np.int32), side=side,
+                        t=np.broadcast_to(_pair_t(T), (C, P)).copy(), status=host["status"],
+                        cell_obstacle=work.cell_obstacle, cell_mode=work.cell_mode,
+                        extra={k: host[k] for k in host if k not in ("nd", "idx_side", "status")})
+        self.save_moments(None, cells.O, cells.n_states, T, Tpred, self.ego_vehicle_id, params,
+                          _precomputed=moments)                                       # :960
+        # prob_lower_save[t] is overwritten across (o, k): the last cell wins (:947)
+        prob_lower_save = host["prob_lower"][-1].tolist() if "prob_lower" in host else None
+        if T == Tpred:
+            self.prob_lower_save = prob_lower_save                                    # :961-962
+        hp.extra["prob_lower_save"] = np.asarray(prob_lower_save)
+        constraints = hp.cvxpy_constraints(temp_x) if temp_x is not None else hp
+        return (constraints, self._vertices(cells), A_union, b_union, OVconstraint, direct, ov_mean, ov_cov, 0)
+
+    def compute_obstacle_constraints_GMM_affine(
+            self, params, ovehicles, Delta2=None, Omicron=None, temp_x=None, eps_ura=None, segments=None,
+            Tsh=None, ref_traj=None):
+        """v8ideal:1378-1539 (receding horizon, nominal).  Same 9-tuple; rows are
+        ``n.x >= d + offset`` / ``n.x <= d - offset`` (:1503-1515)."""
+        cells = ovehicles if isinstance(ovehicles, CellBatch) else CellBatch.from_ovehicles(ovehicles, self.device)
+        Tpred = self.prediction_horizon
+        T = int(Tsh if Tsh is not None else Tpred)
+        if eps_ura is None:
+            eps_ura = eps_allocation(cells.n_states)
+        if cells.T != Tpred:
+            raise ValueError(f"cells carry horizon {cells.T}; the planner's prediction_horizon is {Tpred}")
+        ref_np = np.zeros((Tpred, 2))
+        r = np.asarray(ref_traj, dtype=np.float64)[:, :2]
+        ref_np[:min(T, r.shape[0])] = r[:T]
+        sums, pivot = self._sums(cells)
+        out = ops.affine_halfplanes(sums, pivot, _h2d(ref_np, self.device), self._eps_cells(cells, eps_ura), Tpred,
+                                    R=self.R)
+        At, b0, mom = self._l4(cells, sums, pivot)
+        host = {k: v.cpu().numpy()[:, :T] for k, v in out.items()}
+        A_union = self._nested_tko(cells, At.cpu().numpy(), Tpred)
+        b_union = self._nested_tko(cells, b0.cpu().numpy(), Tpred)
+        ov_mean, ov_cov, inj = self._ov_state(cells, mom)
+        side = np.where(host["idx_side"] & 2, -1, 1).astype(np.int32)
+        C = side.shape[0]
+        hp = HalfPlanes(n=host["nd"][..., :2], d=host["nd"][..., 2], rhs=host["offset_rhs"][..., 1],
+                        idx=(host["idx_side"] & 1).astype(np.int32), side=side,
+                        t=np.broadcast_to(np.arange(T, dtype=np.int32), (C, T)).copy(), status=host["status"],
+                        cell_obstacle=cells.cell_obstacle, cell_mode=cells.cell_mode,
+                        extra=dict(offset=host["offset_rhs"][..., 0], mean=host["mean"], cov=host["cov"]))
+        constraints = hp.cvxpy_constraints(temp_x) if temp_x is not None else hp
+        # the affine builder only reports OV presence when out_junction is set (:1443-1446); callers that
+        # need it pass the flag through params
+        OVconstraint = any(bool(v) for v in inj) if getattr(params, "out_junction", True) else False
+        return (constraints, self._vertices(cells), A_union, b_union, OVconstraint, [None] * cells.O, ov_mean,
+                ov_cov, 0)
+
+    # ------------------------------------------------------ MC risk estimate
+    def mc_collision_risk(self, moments: Moments, n_states, T: int, ego_xy, n_samples: Optional[int] = None,
+                          seed: Optional[int] = None, sample_offset: int = 0, process_group=None,
+                          want_moments: bool = True):
+        """Stage 1 of the path: rollout n samples per (o, k) cell from the moments, then ONE read of
+        the trajectories -> collision counts (A9), soft cost and the shifted power sums; with a
+        ``process_group`` the packed sums are all-reduced (sum) across sample shards.
+
+        Returns dict(sums [C, L] device, counts [C, T+1] int64 device, pivot, cells)."""
+        cells = self.predict_ideal_cells(n_states, T, moments, n_samples=n_samples, seed=seed,
+                                         sample_offset=sample_offset)
+        # common pivot on every rank: the moment means x_{t+1} ~ mean[t+1]  
+        idx = [int(np.nonzero((moments.cell_obstacle == o) & (moments.cell_mode == min(k, max(moments.n_states) - 1)))[0][0])
+               for o, k in zip(cells.cell_obstacle, cells.cell_mode)]
+        pivot = moments.mean.index_select(0, torch.as_tensor(idx, device=self.device))[:, 1:T + 1].contiguous()
+        sums, _ = self._sums(cells, ego=ego_xy, pivot=pivot)
+        if process_group is not None:
+            import torch.distributed as dist
+            dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=process_group)
+        mom = ops.moments_from_sums(sums, pivot, want_cross=want_moments, want_counts=True, want_yaw=False)
+        return dict(sums=sums, counts=mom["counts"], pivot=pivot, cells=cells, moments=mom)
+
+
+class StepPlan:
+    """Fixed-shape constraint build of one MPC step with every buffer pre-allocated and the whole
+    launch sequence (H2D of the samples and the reference trajectory, yaws, one-pass sums + counts,
+    moments, Minkowski half-planes, L4 polytopes, violation counts, D2H of the packed results)
+    captured once in a CUDA graph: one graph launch + one stream synchronise per MPC step.
+
+    This is the latency path for BASELINE.json's "MPC-step constraint build p50 ms"; the arithmetic is
+    the same kernels :class:`MidlevelConstraints` calls (v8ideal:881-947, :627-640, :694-736)."""
+
+    _FIELDS = (("nd", "f8", ("C", "P", 3)), ("ab", "f8", ("C", "P", 3)), ("prob_lower", "f8", ("C", "T")),
+               ("mean", "f8", ("C", "T", 2)), ("cov", "f8", ("C", "T", 2, 2)), ("At", "f8", ("C", "T", 4, 2)),
+               ("b0", "f8", ("C", "T", 4)), ("yaw_mean", "f8", ("C", "T")), ("yaw_var", "f8", ("C", "T")),
+               ("counts", "i8", ("C", "T1")), ("viol", "i8", ("C", "P")), ("idx_side", "i1", ("C", "P")),
+               ("status", "u1", ("C", "P")))
+    _TORCH = {"f8": torch.float64, "i8": torch.int64, "i1": torch.int8, "u1": torch.uint8}
+    _NP = {"f8": np.float64, "i8": np.int64, "i1": np.int8, "u1": np.uint8}
+
+    def __init__(self, offsets_host, cell_obstacle, cell_mode, n_states, pos_last_cell, T: int,
+                 prediction_horizon: int, eps_ura=None, device=None, bbox=BBOX_DEFAULT, R: float = ops.R_EV_OV,
+                 target_p: float = ops.TARGET_P, accel: bool = False, use_graph: bool = True):
+        self.device = _device(device)
+        self.offsets_host = np.asarray(offsets_host, dtype=np.int64)
+        self.cell_obstacle, self.cell_mode = np.asarray(cell_obstacle), np.asarray(cell_mode)
+        self.n_states = list(n_states)
+        self.T, self.prediction_horizon = int(T), int(prediction_horizon)
+        self.C = int(self.offsets_host.size - 1)
+        self.N = int(self.offsets_host[-1])
+        self.P = self.T * (self.T - 1) // 2
+        self.R, self.target_p, self.accel = float(R), float(target_p), bool(accel)
+        dev = self.device
+        if eps_ura is None:
+            eps_ura = eps_allocation(self.n_states)
+        self.eps_cell = _h2d(np.asarray(eps_ura, dtype=np.float64)[self.cell_obstacle, self.cell_mode], dev)
+        self.offsets = _h2d(self.offsets_host, dev)
+        self.pos_last = _h2d(np.asarray(pos_last_cell, dtype=np.float64).reshape(self.C, 2), dev)
+        self.lw_cell = _h2d(np.broadcast_to(np.asarray(bbox, dtype=np.float64), (self.C, 2)).copy(), dev)
+        self.host_samples = torch.empty((self.N, self.T, 2), dtype=torch.float64).pin_memory()
+        self.host_ref = torch.empty((self.T, 2), dtype=torch.float64).pin_memory()
+        self.samples = torch.empty((self.N, self.T, 2), dtype=torch.float64, device=dev)
+        self.ref = torch.empty((self.T, 2), dtype=torch.float64, device=dev)
+        self.yaws = torch.empty((self.N, self.T), dtype=torch.float64, device=dev)
+        self.pivot = torch.empty((self.C, self.T, 2), dtype=torch.float64, device=dev)
+        self.sums = torch.empty((self.C, ops.sums_len(self.T)), dtype=torch.float64, device=dev)
+        self.ws = ops.sample_sums_workspace(self.N, self.C, self.T, dev)
+        # ---- one output arena on the device, one pinned mirror on the host
+        dims = {"C": self.C, "P": self.P, "T": self.T, "T1": self.T + 1}
+        off, self._layout = 0, {}
+        for name, ty, shp in self._FIELDS:
+            shape = tuple(dims.get(s, s) for s in shp)
+            nbytes = int(np.prod(shape)) * np.dtype(self._NP[ty]).itemsize
+            self._layout[name] = (off, nbytes, ty, shape)
+            off = (off + nbytes + 15) // 16 * 16
+        self.arena = torch.zeros(max(off, 16), dtype=torch.uint8, device=dev)
+        self.host_arena = torch.zeros(max(off, 16), dtype=torch.uint8).pin_memory()
+        self.out = {n: self.arena[o:o + b].view(self._TORCH[ty]).view(shape)
+                    for n, (o, b, ty, shape) in self._layout.items()}
+        hb = self.host_arena.numpy()
+        self.host_out = {n: hb[o:o + b].view(self._NP[ty]).reshape(shape)
+                         for n, (o, b, ty, shape) in self._layout.items()}
+        self._mom = dict(mean=self.out["mean"], cov=self.out["cov"], cross=None, counts=self.out["counts"],
+                         yaw_mean=self.out["yaw_mean"], yaw_var=self.out["yaw_var"])
+        self._mink = {k: self.out[k] for k in ("nd", "ab", "idx_side", "prob_lower", "status")}
+        self._ego_is_ref = True
+        self._graph_full = self._graph_dev = None
+        self.launches_per_step = None
+        if use_graph:
+            self._capture()
+
+    @classmethod
+    def from_samples(cls, z, pos, pos_last, K: int, prediction_horizon: int, device=None, **kw) -> "StepPlan":
+        """Bucket each obstacle's samples by latent z in sample order (v8ideal:489-494) on the host ONCE to fix
+        the cell layout; ``host_samples`` is filled with the grouped tensor and ``perm`` keeps the mapping."""
+        z = np.asarray(z)
+        pos = np.asarray(pos, dtype=np.float64)
+        O, N, T = pos.shape[0], pos.shape[1], pos.shape[2]
+        perm, offs, co, ck, ns = [], [0], [], [], []
+        for o in range(O):
+            order = np.argsort(z[o], kind="stable")
+            zs = z[o][order]
+            ks = np.unique(zs)
+            ns.append(int(ks.size))
+            for j, k in enumerate(ks):
+                sel = order[zs == k]
+                perm.append(o * N + sel)
+                offs.append(offs[-1] + sel.size)
+                co.append(o)
+                ck.append(j)
+        plan = cls(np.asarray(offs), co, ck, ns, np.asarray(pos_last)[np.asarray(co)], T, prediction_horizon,
+                   device=device, **kw)
+        plan.perm = np.concatenate(perm)
+        plan.host_samples.copy_(torch.from_numpy(pos.reshape(O * N, T, 2)[plan.perm]))
+        plan.cell_latent = np.asarray([np.unique(z[o])[k] for o, k in zip(co, ck)])
+        return plan
+
+    # -------------------------------------------------------------- launches
+    def _enqueue_device(self):
+        ops.yaws_from_positions(self.samples, self.offsets, self.pos_last, out=self.yaws)
+        ops.cell_pivot(self.samples, self.offsets, out=self.pivot)
+        ops.sample_sums(self.samples, self.offsets, self.pivot, ego=self.ref, yaws=self.yaws, R=self.R,
+                        workspace=self.ws, out=self.sums)
+        ops.moments_from_sums(self.sums, self.pivot, out=self._mom)
+        ops.minkowski_halfplanes(self.sums, self.pivot, self.ref, self.eps_cell, self.prediction_horizon, R=self.R,
+                                 target_p=self.target_p, accel=self.accel, out=self._mink)
+        ops.l4_outer(self.samples, self.yaws, self.offsets, self.out["yaw_mean"], lw_cell=self.lw_cell,
+                     out=(self.out["At"], self.out["b0"]))
+        ops.violation_counts(self.samples, self.offsets, self.out["nd"], self.out["idx_side"], out=self.out["viol"])
+
+    def _enqueue_full(self):
+        self.samples.copy_(self.host_samples, non_blocking=True)
+        self.ref.copy_(self.host_ref, non_blocking=True)
+        self._enqueue_device()
+        self.host_arena.copy_(self.arena, non_blocking=True)
+
+    def _capture(self):
+        from . import _lib
+        lib = _lib.load()
+        self.samples.copy_(self.host_samples)
+        self.ref.copy_(self.host_ref)
+        side = torch.cuda.Stream(device=self.device)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):                      # warm-up outside capture
+            l0 = lib.ccmpc_launch_count()
+            self._enqueue_full()
+            self.launches_per_step = int(lib.ccmpc_launch_count() - l0)
+        side.synchronize()
+        self._graph_full, self._graph_dev = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self._graph_full, stream=side):
+            self._enqueue_full()
+        with torch.cuda.graph(self._graph_dev, stream=side):
+            self._enqueue_device()
+        torch.cuda.current_stream().wait_stream(side)
+
+    # ------------------------------------------------------------------ runs
+    def run_device(self):
+        """Samples and reference already in ``self.samples`` / ``self.ref``; results stay in ``self.out``."""
+        if self._graph_dev is not None:
+            self._graph_dev.replay()
+        else:
+            self._enqueue_device()
+
+    def run(self, pos_host=None, ref_traj=None) -> dict:
+        """Host in -> host out.  ``pos_host`` (N, T, 2) grouped samples (``None``: reuse ``host_samples``),
+        ``ref_traj`` (>=T, >=2).  Returns NumPy views of the pinned result buffer (valid until the next run)."""
+        if pos_host is not None and pos_host is not self.host_samples:
+            self.host_samples.copy_(torch.as_tensor(pos_host).reshape(self.N, self.T, 2))
+        if ref_traj is not None:
+            self.host_ref.copy_(torch.from_numpy(np.ascontiguousarray(np.asarray(ref_traj, dtype=np.float64)[:self.T, :2])))
+        if self._graph_full is not None:
+            self._graph_full.replay()
+        else:
+            self._enqueue_full()
+        torch.cuda.current_stream().synchronize()
+        return self.host_out

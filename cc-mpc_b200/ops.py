@@ -1,0 +1,375 @@
+"""Batched tensor twins of the reference's constraint-path functions.
+
+Thin, allocation-only wrappers over the C ABI of libccmpc.so
+(include/ccmpc.h): every function takes torch CUDA tensors, allocates the
+outputs, and enqueues the kernels on the *current* torch CUDA stream without
+synchronising.  There is no CPU path: a non-CUDA tensor raises.
+
+Reference call sites (relative to the reference root; "makeconstraint" =
+collect/in_simulation/midlevel/v8ideal/makeconstraint.py, "v8ideal" =
+collect/in_simulation/midlevel/v8ideal/__init__.py) are cited per function.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional
+
+import torch
+
+from . import _lib
+
+R_EV_OV = 3.4        # v8ideal:795
+TARGET_P = 0.9999    # v8ideal:912
+MAX_T = 16           # CCMPC_MAX_T
+
+ST_OK, ST_SINGULAR, ST_NO_TANGENT, ST_NOT_CONVERGED, ST_DEGENERATE_SLOPE = range(5)
+
+
+def _p(t: Optional[torch.Tensor]):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _chk(t: Optional[torch.Tensor], dtype, name: str, shape_tail=None):
+    if t is None:
+        return None
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise TypeError(f"{name}: expected a CUDA tensor (libccmpc has no CPU path)")
+    if t.dtype != dtype:
+        raise TypeError(f"{name}: expected dtype {dtype}, got {t.dtype}")
+    if not t.is_contiguous():
+        raise ValueError(f"{name}: tensor must be contiguous")
+    if shape_tail is not None and tuple(t.shape[-len(shape_tail):]) != tuple(shape_tail):
+        raise ValueError(f"{name}: trailing shape {tuple(t.shape)} does not end with {tuple(shape_tail)}")
+    return t
+
+
+def _new(shape, dtype, like: torch.Tensor):
+    return torch.empty(shape, dtype=dtype, device=like.device)
+
+
+F64, I64, I32, I8, U8 = torch.float64, torch.int64, torch.int32, torch.int8, torch.uint8
+
+
+# ---------------------------------------------------------------------------
+# K3  compute_mvoe (makeconstraint:7-38), batched
+# ---------------------------------------------------------------------------
+def mvoe_fit(sigma1, sigma2=None, footprint_r2: float = R_EV_OV ** 2, tol: float = 1e-8, maxiter: int = 1000,
+             accel: bool = False, want_iters: bool = True):
+    """sigma1 [..., 3] sym3; sigma2 [..., 3] or None (=> footprint_r2 * I).
+    Returns (beta [...], q [..., 3], iters [...] int32 | None, status [...] uint8)."""
+    lib = _lib.load()
+    _chk(sigma1, F64, "sigma1", (3,))
+    if sigma2 is not None:
+        _chk(sigma2, F64, "sigma2", (3,))
+        if sigma2.shape != sigma1.shape:
+            raise ValueError("sigma1 and sigma2 must have the same shape")
+    lead = sigma1.shape[:-1]
+    M = sigma1.numel() // 3
+    beta = _new(lead, F64, sigma1)
+    q = _new(tuple(lead) + (3,), F64, sigma1)
+    iters = _new(lead, I32, sigma1) if want_iters else None
+    status = _new(lead, U8, sigma1)
+    _lib.check(lib.ccmpc_mvoe_fit(_p(sigma1), _p(sigma2), float(footprint_r2), M, float(tol), int(maxiter),
+                                  int(bool(accel)), _p(beta), _p(q), _p(iters), _p(status), _stream()),
+               "ccmpc_mvoe_fit")
+    return beta, q, iters, status
+
+
+def mvoe_halfplane_sweep(cov, mu, ref, chi_scale: float, footprint_r2: float = R_EV_OV ** 2, tol: float = 1e-8,
+                         maxiter: int = 1000, accel: bool = False, out=None):
+    """cov [S,O,T,K,3], mu [S,O,T,K,2], ref [S,T,2] -> (q, nd, idx_side, status) (v8ideal:915-939 per cell)."""
+    lib = _lib.load()
+    _chk(cov, F64, "cov", (3,))
+    _chk(mu, F64, "mu", (2,))
+    _chk(ref, F64, "ref", (2,))
+    S, O, T, K = cov.shape[:4]
+    if tuple(mu.shape) != (S, O, T, K, 2) or tuple(ref.shape) != (S, T, 2):
+        raise ValueError("mvoe_halfplane_sweep: shape mismatch")
+    if out is None:
+        out = (_new((S, O, T, K, 3), F64, cov), _new((S, O, T, K, 3), F64, cov),
+               _new((S, O, T, K), I8, cov), _new((S, O, T, K), U8, cov))
+    q, nd, idx_side, status = out
+    _lib.check(lib.ccmpc_mvoe_halfplane_sweep(_p(cov), _p(mu), _p(ref), S, O, T, K, float(chi_scale),
+                                              float(footprint_r2), float(tol), int(maxiter), int(bool(accel)),
+                                              _p(q), _p(nd), _p(idx_side), _p(status), _stream()),
+               "ccmpc_mvoe_halfplane_sweep")
+    return q, nd, idx_side, status
+
+
+# ---------------------------------------------------------------------------
+# K4  tangent lines (makeconstraint:134-207), batched
+# ---------------------------------------------------------------------------
+def tangent(mu, sigma, c, m, a, const_idx=None):
+    """-> d12 [M,2] (d+, d-), dist [M,2], d_star [M], idx [M] int32 (-1: no tangent)."""
+    lib = _lib.load()
+    _chk(mu, F64, "mu", (2,)); _chk(sigma, F64, "sigma", (3,)); _chk(c, F64, "c"); _chk(m, F64, "m")
+    _chk(a, F64, "a", (2,)); _chk(const_idx, I32, "const_idx")
+    M = m.numel()
+    d12 = _new((M, 2), F64, mu); dist = _new((M, 2), F64, mu)
+    d_star = _new((M,), F64, mu); idx = _new((M,), I32, mu)
+    _lib.check(lib.ccmpc_tangent(_p(mu), _p(sigma), _p(c), _p(m), _p(a), _p(const_idx), M, _p(d12), _p(dist),
+                                 _p(d_star), _p(idx), _stream()), "ccmpc_tangent")
+    return d12, dist, d_star, idx
+
+
+def scale_lower(cov_infer, cov_mu, cov_t, gamma=None, eps=None, target_p: float = TARGET_P):
+    """compute_scale (makeconstraint:259-280) and compute_lower_bound (:282-303), batched over [M,3] triples."""
+    lib = _lib.load()
+    for t, n in ((cov_infer, "cov_infer"), (cov_mu, "cov_mu"), (cov_t, "cov_t")):
+        _chk(t, F64, n, (3,))
+    _chk(gamma, F64, "gamma"); _chk(eps, F64, "eps")
+    M = cov_infer.numel() // 3
+    scale = _new((M,), F64, cov_infer) if gamma is not None else None
+    lower = _new((M,), F64, cov_infer) if eps is not None else None
+    _lib.check(lib.ccmpc_scale_lower(_p(cov_infer), _p(cov_mu), _p(cov_t), _p(gamma), _p(eps), float(target_p), M,
+                                     _p(scale), _p(lower), _stream()), "ccmpc_scale_lower")
+    return scale, lower
+
+
+# ---------------------------------------------------------------------------
+# K2 + K6  one read of the sample tensor -> all sums over samples
+# ---------------------------------------------------------------------------
+def sums_len(T: int) -> int:
+    n = _lib.load().ccmpc_sums_len(int(T))
+    if n < 0:
+        raise ValueError(f"T = {T} outside 1..{MAX_T}")
+    return int(n)
+
+
+def sums_layout(T: int) -> dict:
+    """Offsets into the packed sums vector (mirror of SumsLayout in csrc/common.cuh)."""
+    D = 2 * T
+    o_s1 = 1
+    o_s2 = o_s1 + D
+    o_coll = o_s2 + D * (D + 1) // 2
+    o_any = o_coll + T
+    o_pen = o_any + 1
+    o_d2s = o_pen + T
+    o_yaw = o_d2s + T
+    o_yaw2 = o_yaw + T
+    return dict(n=0, s1=o_s1, s2=o_s2, coll=o_coll, any=o_any, pen=o_pen, d2s=o_d2s, yaw=o_yaw, yaw2=o_yaw2,
+                len=o_yaw2 + T)
+
+
+def sample_sums_workspace(n_total: int, C: int, T: int, device) -> torch.Tensor:
+    nbytes = _lib.load().ccmpc_sample_sums_workspace_bytes(int(n_total), int(C), int(T))
+    return torch.empty(max(int(nbytes), 16), dtype=torch.uint8, device=device)
+
+
+def cell_pivot(samples, offsets, out=None):
+    """pivot[c] = first sample of cell c (zeros for an empty cell): the shift of the one-pass power sums."""
+    lib = _lib.load()
+    _chk(samples, F64, "samples", (2,)); _chk(offsets, I64, "offsets")
+    T = samples.shape[1]
+    C = offsets.numel() - 1
+    if out is None:
+        out = _new((C, T, 2), F64, samples)
+    _lib.check(lib.ccmpc_cell_pivot(_p(samples), _p(offsets), C, T, _p(out), _stream()), "ccmpc_cell_pivot")
+    return out
+
+
+def sample_sums(samples, offsets, pivot, ego=None, yaws=None, R: float = R_EV_OV, workspace=None, out=None):
+    """samples [N,T,2], offsets [C+1] int64, pivot [C,T,2], ego [T,2] | [C,T,2] | None, yaws [N,T] | None
+    -> sums [C, sums_len(T)] (np.mean/np.cov of every (t,tau) pair, makeconstraint:55; counts A9)."""
+    lib = _lib.load()
+    _chk(samples, F64, "samples", (2,)); _chk(offsets, I64, "offsets"); _chk(pivot, F64, "pivot", (2,))
+    _chk(ego, F64, "ego", (2,)); _chk(yaws, F64, "yaws")
+    N, T = samples.shape[0], samples.shape[1]
+    C = offsets.numel() - 1
+    if tuple(pivot.shape) != (C, T, 2):
+        raise ValueError("pivot must be [C,T,2]")
+    stride = 0
+    if ego is not None:
+        if tuple(ego.shape) == (T, 2):
+            stride = 0
+        elif tuple(ego.shape) == (C, T, 2):
+            stride = 2 * T
+        else:
+            raise ValueError("ego must be [T,2] or [C,T,2]")
+    if yaws is not None and tuple(yaws.shape) != (N, T):
+        raise ValueError("yaws must be [N,T]")
+    if workspace is None:
+        workspace = sample_sums_workspace(N, C, T, samples.device)
+    if out is None:
+        out = _new((C, sums_len(T)), F64, samples)
+    _lib.check(lib.ccmpc_sample_sums(_p(samples), _p(offsets), N, C, T, _p(pivot), _p(ego), stride, float(R),
+                                     _p(yaws), _p(out), _p(workspace), workspace.numel(), _stream()),
+               "ccmpc_sample_sums")
+    return out
+
+
+def moments_from_sums(sums, pivot, want_cross=True, want_counts=True, want_yaw=True, out=None):
+    """-> dict(mean [C,T,2], cov [C,T,2,2], cross [C,T,T,2,2], counts [C,T+1] int64, yaw_mean [C,T], yaw_var [C,T])
+    in the save_moments layout (v8ideal:2586-2606)."""
+    lib = _lib.load()
+    _chk(sums, F64, "sums"); _chk(pivot, F64, "pivot", (2,))
+    C, T = pivot.shape[0], pivot.shape[1]
+    if out is None:
+        out = dict(mean=_new((C, T, 2), F64, sums), cov=_new((C, T, 2, 2), F64, sums),
+                   cross=_new((C, T, T, 2, 2), F64, sums) if want_cross else None,
+                   counts=_new((C, T + 1), I64, sums) if want_counts else None,
+                   yaw_mean=_new((C, T), F64, sums) if want_yaw else None,
+                   yaw_var=_new((C, T), F64, sums) if want_yaw else None)
+    _lib.check(lib.ccmpc_moments_from_sums(_p(sums), _p(pivot), C, T, _p(out["mean"]), _p(out["cov"]),
+                                           _p(out.get("cross")), _p(out.get("counts")), _p(out.get("yaw_mean")),
+                                           _p(out.get("yaw_var")), _stream()), "ccmpc_moments_from_sums")
+    return out
+
+
+MINK_FIELDS = ("nd", "ab", "idx_side", "q", "q1", "betas", "cov_infer", "cov_mu", "prob_pair", "prob_lower", "mean",
+               "status")
+
+
+def minkowski_alloc(C: int, T: int, device, fields=MINK_FIELDS) -> dict:
+    P = T * (T - 1) // 2
+    shapes = dict(nd=((C, P, 3), F64), ab=((C, P, 3), F64), idx_side=((C, P), I8), q=((C, P, 3), F64),
+                  q1=((C, P, 3), F64), betas=((C, P, 2), F64), cov_infer=((C, P, 3), F64), cov_mu=((C, P, 3), F64),
+                  prob_pair=((C, P), F64), prob_lower=((C, T), F64), mean=((C, T, 2), F64), status=((C, P), U8))
+    return {k: torch.empty(shapes[k][0], dtype=shapes[k][1], device=device) for k in fields}
+
+
+def minkowski_halfplanes(sums, pivot, ref, eps_cell, prediction_horizon: int, R: float = R_EV_OV,
+                         target_p: float = TARGET_P, tol: float = 1e-8, maxiter: int = 1000, accel: bool = False,
+                         out: Optional[dict] = None):
+    """Minkowski half-plane loop of one MPC step (v8ideal:893-947) for every cell and (t, tau) pair."""
+    lib = _lib.load()
+    _chk(sums, F64, "sums"); _chk(pivot, F64, "pivot", (2,)); _chk(ref, F64, "ref", (2,)); _chk(eps_cell, F64, "eps")
+    C, T = pivot.shape[0], pivot.shape[1]
+    if tuple(ref.shape) == (T, 2):
+        stride = 0
+    elif tuple(ref.shape) == (C, T, 2):
+        stride = 2 * T
+    else:
+        raise ValueError("ref must be [T,2] or [C,T,2]")
+    if eps_cell.numel() != C:
+        raise ValueError("eps_cell must have C entries")
+    if out is None:
+        out = minkowski_alloc(C, T, sums.device)
+    g = out.get
+    _lib.check(lib.ccmpc_minkowski_halfplanes(
+        _p(sums), _p(pivot), _p(ref), stride, _p(eps_cell), C, T, int(prediction_horizon), float(R), float(target_p),
+        float(tol), int(maxiter), int(bool(accel)), _p(g("nd")), _p(g("ab")), _p(g("idx_side")), _p(g("q")),
+        _p(g("q1")), _p(g("betas")), _p(g("cov_infer")), _p(g("cov_mu")), _p(g("prob_pair")), _p(g("prob_lower")),
+        _p(g("mean")), _p(g("status")), _stream()), "ccmpc_minkowski_halfplanes")
+    return out
+
+
+def affine_halfplanes(sums, pivot, ref, eps_cell, Tpred: int, R: float = R_EV_OV, out: Optional[dict] = None):
+    """Affine half-plane loop (v8ideal:1476-1515) per (cell, t)."""
+    lib = _lib.load()
+    _chk(sums, F64, "sums"); _chk(pivot, F64, "pivot", (2,)); _chk(ref, F64, "ref", (2,)); _chk(eps_cell, F64, "eps")
+    C, T = pivot.shape[0], pivot.shape[1]
+    stride = 0 if tuple(ref.shape) == (T, 2) else 2 * T
+    if out is None:
+        dev = sums.device
+        out = dict(nd=torch.empty((C, T, 3), dtype=F64, device=dev),
+                   offset_rhs=torch.empty((C, T, 2), dtype=F64, device=dev),
+                   idx_side=torch.empty((C, T), dtype=I8, device=dev),
+                   mean=torch.empty((C, T, 2), dtype=F64, device=dev),
+                   cov=torch.empty((C, T, 3), dtype=F64, device=dev),
+                   status=torch.empty((C, T), dtype=U8, device=dev))
+    _lib.check(lib.ccmpc_affine_halfplanes(_p(sums), _p(pivot), _p(ref), stride, _p(eps_cell), C, T, int(Tpred),
+                                           float(R), _p(out["nd"]), _p(out["offset_rhs"]), _p(out["idx_side"]),
+                                           _p(out["mean"]), _p(out["cov"]), _p(out["status"]), _stream()),
+               "ccmpc_affine_halfplanes")
+    return out
+
+
+def violation_counts(samples, offsets, nd, idx_side, out=None):
+    """A9 (ii): #{samples on the ego side of each emitted half-plane} -> [C,P] int64."""
+    lib = _lib.load()
+    _chk(samples, F64, "samples", (2,)); _chk(offsets, I64, "offsets"); _chk(nd, F64, "nd", (3,))
+    _chk(idx_side, I8, "idx_side")
+    N, T = samples.shape[0], samples.shape[1]
+    C = offsets.numel() - 1
+    P = T * (T - 1) // 2
+    if out is None:
+        out = _new((C, P), I64, samples)
+    _lib.check(lib.ccmpc_violation_counts(_p(samples), _p(offsets), N, C, T, _p(nd), _p(idx_side), _p(out),
+                                          _stream()), "ccmpc_violation_counts")
+    return out
+
+
+# ---------------------------------------------------------------------------
+# K5  boxes and L4 outer approximation
+# ---------------------------------------------------------------------------
+def vertices_of_bboxes(centers, theta, lw):
+    """utility/npu.py:308-350 on device: centers [N,2], theta [N] or [1], lw (l, w) -> [N,4,2]."""
+    lib = _lib.load()
+    _chk(centers, F64, "centers", (2,)); _chk(theta, F64, "theta")
+    N = centers.shape[0]
+    scalar = 1 if theta.numel() == 1 and N != 1 else 0
+    if not scalar and theta.numel() != N:
+        raise ValueError("theta must have 1 or N entries")
+    out = _new((N, 4, 2), F64, centers)
+    _lib.check(lib.ccmpc_vertices_of_bboxes(_p(centers), _p(theta), scalar, float(lw[0]), float(lw[1]), N, _p(out),
+                                            _stream()), "ccmpc_vertices_of_bboxes")
+    return out
+
+
+def l4_outer(samples, yaws, offsets, yaw_mean, lw=(3.7, 1.79), lw_cell=None, out=None):
+    """v8ideal:627-640 + :694-736 + midlevel/util.py:171-200 per (cell, t) -> At [C,T,4,2], b0 [C,T,4]."""
+    lib = _lib.load()
+    _chk(samples, F64, "samples", (2,)); _chk(yaws, F64, "yaws"); _chk(offsets, I64, "offsets")
+    _chk(yaw_mean, F64, "yaw_mean"); _chk(lw_cell, F64, "lw_cell", (2,))
+    N, T = samples.shape[0], samples.shape[1]
+    C = offsets.numel() - 1
+    if out is None:
+        out = (_new((C, T, 4, 2), F64, samples), _new((C, T, 4), F64, samples))
+    At, b0 = out
+    _lib.check(lib.ccmpc_l4_outer(_p(samples), _p(yaws), _p(offsets), N, C, T, _p(yaw_mean), _p(lw_cell),
+                                  float(lw[0]), float(lw[1]), _p(At), _p(b0), _stream()), "ccmpc_l4_outer")
+    return At, b0
+
+
+def yaws_from_positions(samples, offsets, pos_last, out=None):
+    """midlevel/ovehicle.py:72-76 on device: samples [N,T,2], offsets [C+1], pos_last [C,2] -> yaws [N,T]."""
+    lib = _lib.load()
+    _chk(samples, F64, "samples", (2,)); _chk(offsets, I64, "offsets"); _chk(pos_last, F64, "pos_last", (2,))
+    N, T = samples.shape[0], samples.shape[1]
+    C = offsets.numel() - 1
+    if out is None:
+        out = _new((N, T), F64, samples)
+    _lib.check(lib.ccmpc_yaws_from_positions(_p(samples), _p(offsets), N, C, T, _p(pos_last), _p(out), _stream()),
+               "ccmpc_yaws_from_positions")
+    return out
+
+
+# ---------------------------------------------------------------------------
+# K1  Monte Carlo rollout (predict_ideal, v8ideal:2662-2709)
+# ---------------------------------------------------------------------------
+def mc_rollout(mean, cov, cross, x0, n: int, Tsh: int, seed: int = 0, sample_offset: int = 0, z=None,
+               want_z: bool = False, out=None):
+    """mean [C,Tm,2], cov [C,Tm,2,2], cross [C,Tm,Tm,2,2], x0 [C,2] | None (device draw)
+    -> traj [C,n,Tsh,2], z_used | None, status [C] uint8, x0_used [C,2]."""
+    lib = _lib.load()
+    _chk(mean, F64, "mean", (2,)); _chk(cov, F64, "cov", (2, 2)); _chk(cross, F64, "cross", (2, 2))
+    _chk(x0, F64, "x0", (2,)); _chk(z, F64, "z", (2,))
+    C, Tm = mean.shape[0], mean.shape[1]
+    if tuple(cov.shape) != (C, Tm, 2, 2) or tuple(cross.shape) != (C, Tm, Tm, 2, 2) or \
+            (x0 is not None and tuple(x0.shape) != (C, 2)):
+        raise ValueError("mc_rollout: moment shapes do not agree")
+    if z is not None and tuple(z.shape) != (C, n, Tsh, 2):
+        raise ValueError("z must be [C,n,Tsh,2]")
+    traj = out if out is not None else _new((C, n, Tsh, 2), F64, mean)
+    z_out = _new((C, n, Tsh, 2), F64, mean) if want_z else None
+    status = _new((C,), U8, mean)
+    x0_out = _new((C, 2), F64, mean)
+    _lib.check(lib.ccmpc_mc_rollout(_p(mean), _p(cov), _p(cross), Tm, _p(x0), C, int(n), int(Tsh),
+                                    int(seed) & 0xFFFFFFFFFFFFFFFF, int(sample_offset), _p(z), _p(traj), _p(z_out),
+                                    _p(status), _p(x0_out), _stream()), "ccmpc_mc_rollout")
+    return traj, z_out, status, x0_out
+
+
+def philox4x32(ctr, key):
+    """Philox-4x32-10 known-answer hook: ctr [M,4] int32 bits, key [M,2] -> [M,4]."""
+    lib = _lib.load()
+    _chk(ctr, I32, "ctr", (4,)); _chk(key, I32, "key", (2,))
+    M = ctr.shape[0]
+    out = torch.empty_like(ctr)
+    _lib.check(lib.ccmpc_philox4x32(_p(ctr), _p(key), M, _p(out), _stream()), "ccmpc_philox4x32")
+    return out

@@ -52,6 +52,8 @@ extern "C" {
 
 int ccmpc_version(void);
 const char* ccmpc_last_error_string(void);
+/* number of libccmpc kernels launched by this process so far (every kernel launch is counted once) */
+uint64_t ccmpc_launch_count(void);
 
 /* ---------------------------------------------------------------------------
  * K3  batched MVOE fit.   Replaces makeconstraint.compute_mvoe (:7-38).
@@ -122,6 +124,7 @@ int ccmpc_scale_lower(const double* cov_infer, const double* cov_mu, const doubl
  *   T entries:              pen[t]   = sum over hits (R^2 - |ego_t - p_t|^2)
  *   T entries:              d2s[t]   = sum |ego_t - p_t|^2
  *   T entries:              yaw[t]   = sum yaw_t
+ *   T entries:              yaw2[t]  = sum yaw_t^2
  * Counts are integers < 2^53 held exactly in doubles, so one fp64 NCCL
  * all-reduce(sum) of `sums` across sample shards is exact for them.
  * The predicate is evaluated without FMA contraction in the order
@@ -144,11 +147,16 @@ int ccmpc_sample_sums(const double* samples, const int64_t* offsets, int64_t n_t
 /* Moments as save_moments stores them (v8ideal:2586-2606) from the sums:
  *   mean [C,T,2], cov [C,T,2,2], cross [C,T,T,2,2] (cross[t][tau] for tau < t,
  *   = np.cov([x_t,y_t,x_tau,y_tau])[0:2,2:4]; other slots zero),
- *   counts [C, 2T+... ] see below (nullable), yaw_mean [C,T] (nullable).
+ *   counts (nullable), yaw_mean [C,T] and yaw_var [C,T] (= np.cov(yaw_t), v8ideal:876) (nullable).
  *   counts layout int64 [C, T+1]: coll[0..T), any. */
 int ccmpc_moments_from_sums(const double* sums, const double* pivot, int64_t C, int T,
                             double* mean, double* cov, double* cross,
-                            int64_t* counts, double* yaw_mean, void* stream);
+                            int64_t* counts, double* yaw_mean, double* yaw_var, void* stream);
+
+/* pivot [C,T,2] = first sample of each cell (zeros for an empty cell): the
+ * shift of the one-pass power sums when no better one (GMM mode mean) is known. */
+int ccmpc_cell_pivot(const double* samples, const int64_t* offsets, int64_t C, int T,
+                     double* pivot, void* stream);
 
 /* ---------------------------------------------------------------------------
  * K3+K4 on sample moments: the Minkowski half-plane loop of one MPC step.
@@ -199,13 +207,24 @@ int ccmpc_violation_counts(const double* samples, const int64_t* offsets, int64_
  * ccmpc_l4_outer replaces v8ideal:627-640 + :694-736 + midlevel/util.py:171-200
  * per (cell, t) without materialising the corners:
  *   samples [N,T,2], yaws [N,T], yaw_mean [C,T] (from ccmpc_moments_from_sums),
- *   out At [C,T,4,2], b0 [C,T,4].
+ *   lw_cell [C,2] per-cell (length, width) = ovehicle.bbox, or NULL => (l, w) for all,
+ *   out At [C,T,4,2], b0 [C,T,4] (NaN for an empty cell).
  */
 int ccmpc_vertices_of_bboxes(const double* centers, const double* theta, int64_t theta_is_scalar,
                              double l, double w, int64_t N, double* vertices, void* stream);
 int ccmpc_l4_outer(const double* samples, const double* yaws, const int64_t* offsets,
                    int64_t n_total, int64_t C, int T, const double* yaw_mean,
-                   double l, double w, double* At, double* b0, void* stream);
+                   const double* lw_cell, double l, double w, double* At, double* b0, void* stream);
+
+/* ---------------------------------------------------------------------------
+ * A2  per-sample yaw from consecutive predicted positions.  Replaces
+ * midlevel/ovehicle.py:72-76: yaw[n,0] = atan2(p[n,0] - pos_last[cell]),
+ * yaw[n,t] = atan2(p[n,t] - p[n,t-1]).
+ *   samples [N,T,2], offsets [C+1], pos_last [C,2] (last observed position of the
+ *   cell's obstacle), out yaws [N,T].
+ */
+int ccmpc_yaws_from_positions(const double* samples, const int64_t* offsets, int64_t n_total, int64_t C,
+                              int T, const double* pos_last, double* yaws, void* stream);
 
 /* ---------------------------------------------------------------------------
  * K1  Monte Carlo rollout.  Replaces MidlevelAgent.predict_ideal's loop body
@@ -215,7 +234,9 @@ int ccmpc_l4_outer(const double* samples, const double* yaws, const int64_t* off
  * starting from the ONE draw x0[c] the reference broadcasts to all samples
  * (:2664-2665).
  *   mean [C,Tm,2], cov [C,Tm,2,2], cross [C,Tm,Tm,2,2] with Tm >= Tsh + 1.
- *   x0 [C,2].  z: NULL => Philox-4x32-10 normals (counter = (sample index,
+ *   x0 [C,2], or NULL => drawn on the device as mean_0 + chol(cov_0) z from a reserved
+ *   Philox counter (the same value on every CTA and every GPU shard); x0_out [C,2]
+ *   (nullable) receives the value used.  z: NULL => Philox-4x32-10 normals (counter = (sample index,
  *   sample_offset-based; cell; draw), key = seed; sample_offset makes the
  *   stream independent of how samples are sharded over GPUs); else the
  *   supplied noise [C,n,Tsh,2] (deterministic parity mode).
@@ -225,7 +246,16 @@ int ccmpc_l4_outer(const double* samples, const double* yaws, const int64_t* off
 int ccmpc_mc_rollout(const double* mean, const double* cov, const double* cross, int Tm,
                      const double* x0, int64_t C, int64_t n, int Tsh,
                      uint64_t seed, uint64_t sample_offset, const double* z,
-                     double* traj, double* z_out, uint8_t* status, void* stream);
+                     double* traj, double* z_out, uint8_t* status, double* x0_out, void* stream);
+
+/* ---------------------------------------------------------------------------
+ * A12  closed-loop episode cost.  Replaces getData_singleEpisode.cost_final
+ * (dataForCost_ref.py:198-232) for E episodes (the loop of montecarlo_cost_ref.py:55-77).
+ *   x_last [E,2] last stored position; U [E,Hmax,2] controls (padded); lengths [E] int32 = H.
+ *   out cost [E], costU [E]; H < 2 => NaN (the reference raises).
+ */
+int ccmpc_episode_cost(const double* x_last, const double* U, const int32_t* lengths, int64_t E, int Hmax,
+                       double goal_x, double goal_y, double* cost, double* costU, void* stream);
 
 /* Philox-4x32-10 known-answer hook: out[i] = philox(ctr[i], key[i]) (4 words each). */
 int ccmpc_philox4x32(const uint32_t* ctr, const uint32_t* key, int64_t M, uint32_t* out, void* stream);

@@ -1,0 +1,120 @@
+"""CPU-only checks: the C-ABI library loads and exports every symbol include/ccmpc.h declares
+(no compute calls), the host logic (sharding, eps allocation), and the no-fallback guarantee."""
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    src = open(os.path.join(ROOT, "include", "ccmpc.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(ccmpc_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    from ccmpc_b200 import _lib
+    lib = _lib.load()
+    names = _declared()
+    assert len(names) >= 20
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/ccmpc.h but not exported by libccmpc.so"
+        assert n in _lib.SIGNATURES, f"{n} has no ctypes signature"
+    assert sorted(_lib.SIGNATURES) == names, "ctypes table and header disagree"
+    assert lib.ccmpc_version() == 100
+    assert lib.ccmpc_sums_len(8) == 1 + 16 + 16 * 17 // 2 + 8 + 1 + 8 + 8 + 8 + 8
+    assert lib.ccmpc_sums_len(0) == -1 and lib.ccmpc_sums_len(17) == -1
+    assert lib.ccmpc_sample_sums_workspace_bytes(5000 * 4, 100, 8) > 0
+
+
+def test_library_is_sm100a_only():
+    import subprocess
+    from ccmpc_b200 import _build
+    out = subprocess.run(["cuobjdump", "-lelf", _build.LIB], capture_output=True, text=True).stdout
+    archs = set(re.findall(r"sm_(\d+a?)", out))
+    assert archs == {"100a"}, archs
+
+
+def test_no_cpu_fallback():
+    from ccmpc_b200 import ops
+    with pytest.raises(TypeError):
+        ops.mvoe_fit(torch.ones((4, 3), dtype=torch.float64))
+    with pytest.raises(TypeError):
+        ops.sample_sums(torch.zeros((4, 2, 2), dtype=torch.float64), torch.tensor([0, 4]), torch.zeros((1, 2, 2)))
+    if not torch.cuda.is_available():
+        from ccmpc_b200 import makeconstraint
+        with pytest.raises(RuntimeError):
+            makeconstraint.compute_mvoe(np.eye(2), np.eye(2))
+
+
+def test_sums_layout_mirror():
+    from ccmpc_b200 import _lib, ops
+    for T in range(1, 17):
+        assert ops.sums_layout(T)["len"] == _lib.load().ccmpc_sums_len(T)
+
+
+def test_eps_allocation_matches_oracle():
+    from ccmpc_b200 import midlevel
+    from oracle import restate
+    for ks in ([3], [1, 4, 2], [25] * 4):
+        np.testing.assert_array_equal(midlevel.eps_allocation(ks), restate.eps_allocation(ks))
+
+
+def test_shard_range_partitions():
+    from ccmpc_b200 import sharding
+    for total in (0, 1, 7, 4096, 1_000_000):
+        for world in (1, 2, 3, 8):
+            r = [sharding.shard_range(total, k, world) for k in range(world)]
+            assert r[0][0] == 0 and r[-1][1] == total
+            assert all(r[k][1] == r[k + 1][0] for k in range(world - 1))
+            sizes = [b - a for a, b in r]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def _gloo_worker(rank, world, port, q):
+    import torch.distributed as dist
+    from ccmpc_b200 import ops, sharding
+    from oracle import restate, synth
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    try:
+        T, n = 4, 1001
+        sc = synth.make_scene(5, 1, 2, T)
+        _, pos = synth.sample_scene(sc, n, 5)
+        ego = sc.ref_traj + np.array([0.0, 8.0])       # close enough to collide sometimes
+        lo, n_loc = sharding.sample_shard(n)
+        L = ops.sums_layout(T)
+        sums = torch.zeros((1, L["len"]), dtype=torch.float64)
+        part = pos[0, lo:lo + n_loc]
+        coll, any_, pen, d2s = restate.collision_counts(part, ego, R=30.0)
+        sums[0, 0] = n_loc
+        sums[0, L["coll"]:L["coll"] + T] = torch.from_numpy(coll.astype(np.float64))
+        sums[0, L["any"]] = float(any_)
+        sums[0, L["pen"]:L["pen"] + T] = torch.from_numpy(pen)
+        sharding.allreduce_sums(sums)
+        counts = sharding.counts_from_sums(sums, T)
+        wc, wa, wp, _ = restate.collision_counts(pos[0], ego, R=30.0)
+        ok = (int(sums[0, 0]) == n and np.array_equal(counts[0, :T].numpy(), wc) and int(counts[0, T]) == wa
+              and np.allclose(sums[0, L["pen"]:L["pen"] + T].numpy(), wp, rtol=1e-12) and wc.sum() > 0)
+        q.put((rank, bool(ok)))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_count_allreduce_world2_gloo():
+    """N > 1 host path on CPU: per-shard counts all-reduced over gloo equal the unsharded counts exactly."""
+    import socket
+    import torch.multiprocessing as mp
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_gloo_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    assert sorted(res) == [(0, True), (1, True)]

@@ -1,0 +1,441 @@
+"""CUDA path (through the C ABI of libccmpc.so) against the goldens produced by the
+reference's own functions and against the CPU oracle on the same seeded inputs.
+
+Bars (BASELINE.json north_star): counts, best_idx and side bit-exact; matrices,
+half-plane coefficients and costs within 1e-5 relative - the kernels are fp64, so the
+tests hold them to far tighter tolerances, written next to each check."""
+import numpy as np
+import pytest
+import torch
+
+from _util import relerr
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-5          # the contract
+TIGHT = 1e-9         # what fp64 kernels actually deliver on well-conditioned inputs
+
+
+@pytest.fixture(scope="module")
+def dev():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from ccmpc_b200 import _lib
+    _lib.load(build_if_missing=False)          # the CUDA library must be there: no fallback
+    return torch.device("cuda:0")
+
+
+def sym3(S):
+    S = np.asarray(S)
+    return np.stack([S[..., 0, 0], S[..., 0, 1], S[..., 1, 1]], axis=-1)
+
+
+def full(q3):
+    q3 = np.asarray(q3)
+    out = np.empty(q3.shape[:-1] + (2, 2))
+    out[..., 0, 0] = q3[..., 0]; out[..., 0, 1] = q3[..., 1]
+    out[..., 1, 0] = q3[..., 1]; out[..., 1, 1] = q3[..., 2]
+    return out
+
+
+def T_(a, dev, dtype=torch.float64):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(dtype).to(dev)
+
+
+# ----------------------------------------------------------------------------- K3
+def test_mvoe_fit_matches_reference_golden(dev, golden):
+    from ccmpc_b200 import ops
+    from oracle import restate
+    g = golden("ref_mvoe")
+    beta, q, iters, status = ops.mvoe_fit(T_(sym3(g["Sigma1"]), dev), T_(sym3(g["Sigma2"]), dev))
+    assert not status.any()
+    np.testing.assert_allclose(beta.cpu().numpy(), g["beta"], rtol=1e-7)     # both stop at |delta| < 1e-8
+    assert relerr(full(q.cpu().numpy()), g["Q"]) < 1e-8
+    for i in range(len(g["beta"])):
+        assert np.max(np.abs(full(q.cpu().numpy()[i]) - g["Q"][i])) <= 1e-7 * np.max(np.abs(g["Q"][i]))
+    # same iterate sequence => same iteration count as the restated loop
+    it_ref = np.array([restate.mvoe(a, b, return_iters=True)[2] for a, b in zip(g["Sigma1"], g["Sigma2"])])
+    it = iters.cpu().numpy()
+    assert np.mean(it == it_ref) > 0.97 and np.max(np.abs(it - it_ref)) <= 1
+    # accelerated start converges to the same fixed point
+    beta_a, q_a, it_a, st_a = ops.mvoe_fit(T_(sym3(g["Sigma1"]), dev), T_(sym3(g["Sigma2"]), dev), accel=True)
+    assert not st_a.any()
+    np.testing.assert_allclose(beta_a.cpu().numpy(), g["beta"], rtol=1e-6)
+    assert relerr(full(q_a.cpu().numpy()), g["Q"]) < 1e-7
+    assert it_a.float().mean() < iters.float().mean()
+
+
+def test_mvoe_fit_footprint_form_and_edge_cases(dev):
+    from ccmpc_b200 import ops
+    from oracle import restate
+    rng = np.random.default_rng(11)
+    from oracle.synth import random_spd, sym_to_full
+    s1 = random_spd(rng, (1000,))
+    R2 = 3.4 ** 2
+    beta, q, _, status = ops.mvoe_fit(T_(s1, dev), None, footprint_r2=R2)
+    assert not status.any()
+    for i in range(0, 1000, 37):
+        b, Q = restate.mvoe(sym_to_full(s1[i]), np.eye(2) * R2)
+        assert abs(beta[i].item() - b) < 1e-7
+        assert relerr(full(q[i].cpu().numpy()), Q) < 1e-8
+    # KATs: radius 1 (+) radius 2 = radius 3
+    beta, q, _, _ = ops.mvoe_fit(T_([[1.0, 0.0, 1.0]], dev), T_([[4.0, 0.0, 4.0]], dev))
+    assert abs(beta.item() - 0.5) < 1e-8 and relerr(q.cpu().numpy(), [[9.0, 0.0, 9.0]]) < 1e-8
+    # empty batch, singular Sigma1, maxiter exhaustion
+    b0, q0, _, _ = ops.mvoe_fit(torch.empty((0, 3), dtype=torch.float64, device=dev), None)
+    assert b0.numel() == 0 and q0.shape == (0, 3)
+    _, _, _, st = ops.mvoe_fit(T_([[1.0, 1.0, 1.0]], dev), T_([[1.0, 0.0, 1.0]], dev))
+    assert st.item() == ops.ST_SINGULAR
+    _, _, it, st = ops.mvoe_fit(T_([[1.0, 0.2, 2.0]], dev), T_([[30.0, 0.0, 0.5]], dev), maxiter=2)
+    assert st.item() == ops.ST_NOT_CONVERGED and it.item() == 2
+
+
+# ----------------------------------------------------------------------------- K4
+def test_tangent_matches_reference_golden(dev, golden):
+    from ccmpc_b200 import ops
+    g = golden("ref_tangent")
+    args = [T_(g["mu"], dev), T_(sym3(g["Sigma"]), dev), T_(g["c"], dev), T_(g["m"], dev), T_(g["a"], dev)]
+    d12, dist, d_star, idx = ops.tangent(*args)
+    np.testing.assert_array_equal(idx.cpu().numpy(), g["idx"])                # bit-exact index
+    np.testing.assert_allclose(d12.cpu().numpy()[:, 0], g["d1"], rtol=1e-12, atol=1e-12)
+    np.testing.assert_allclose(d12.cpu().numpy()[:, 1], g["d2"], rtol=1e-12, atol=1e-12)
+    np.testing.assert_allclose(dist.cpu().numpy(), g["dist"], rtol=1e-10, atol=1e-12)
+    np.testing.assert_allclose(d_star.cpu().numpy(), g["d_star"], rtol=1e-12, atol=1e-12)
+    for j in (0, 1):
+        ci = torch.full((len(g["c"]),), j, dtype=torch.int32, device=dev)
+        _, _, ds, ix = ops.tangent(*args, const_idx=ci)
+        np.testing.assert_allclose(ds.cpu().numpy(), g["d_forced"][:, j], rtol=1e-12, atol=1e-12)
+        assert (ix.cpu().numpy() == j).all()
+    # no tangent: n^T Sigma n <= 0
+    _, _, _, ix = ops.tangent(T_([[0.0, 0.0]], dev), T_([[0.0, 0.0, 0.0]], dev), T_([1.0], dev), T_([0.3], dev),
+                              T_([[1.0, 1.0]], dev))
+    assert ix.item() == -1
+
+
+def test_scale_lower_matches_reference_golden(dev, golden):
+    from ccmpc_b200 import ops
+    g = golden("ref_scale_lower")
+    scale, lower = ops.scale_lower(T_(sym3(g["cov_infer"]), dev), T_(sym3(g["cov_mu"]), dev), T_(sym3(g["cov_t"]), dev),
+                                   gamma=T_(g["Gamma"], dev), eps=T_(g["eps"], dev))
+    np.testing.assert_allclose(scale.cpu().numpy(), g["scale"], rtol=1e-11)
+    np.testing.assert_allclose(lower.cpu().numpy(), g["lower"], rtol=1e-9, atol=1e-14)
+
+
+# ------------------------------------------------------ scalar drop-in twins
+def test_makeconstraint_scalar_api(dev, golden):
+    from ccmpc_b200 import makeconstraint as mc
+    b, Q = mc.compute_mvoe(np.array([[2, .5], [.5, 1]]), np.array([[1, -.2], [-.2, 3]]))
+    assert b == pytest.approx(0.8915954797056089, rel=1e-7)
+    np.testing.assert_allclose(Q, [[6.134765219261006, 0.6824733389477273], [0.6824733389477273, 7.796371308894525]],
+                               rtol=1e-7)
+    with pytest.raises(np.linalg.LinAlgError):
+        mc.compute_mvoe(np.zeros((2, 2)), np.eye(2))
+    n, d, idx = mc.choose_closest_tangent([1, 2], [[2, .5], [.5, 1]], 1, 0.5, [10, 3])
+    np.testing.assert_array_equal(n, [-0.5, 1.0])
+    assert d == pytest.approx(0.5) and idx == 1
+    n, d, idx = mc.choose_closest_tangent([1, 2], [[2, .5], [.5, 1]], 1, 0.5, [10, 30])
+    assert d == pytest.approx(2.5) and idx == 0
+    assert mc.choose_closest_tangent([0, 0], np.zeros((2, 2)), 1.0, 0.3, [1, 1]) == (None, None, None, None)
+    assert mc.tangent_lines_of_slope_m([0, 0], np.zeros((2, 2)), 1.0, 0.3) == []
+    (n1, d1), (n2, d2) = mc.tangent_lines_of_slope_m([1, 2], [[2, .5], [.5, 1]], 1, 0.5)
+    assert d1 == pytest.approx(2.5) and d2 == pytest.approx(0.5)
+    assert mc.distance_point_to_line(np.array([-0.5, 1.0]), 0.5, [10, 3]) == pytest.approx(
+        abs(-5 + 3 - 0.5) / np.sqrt(1.25), rel=1e-12)
+    ci, cm = np.array([[.5, .1], [.1, .4]]), np.array([[.3, .05], [.05, .2]])
+    assert mc.compute_lower_bound(ci, cm, ci + cm, 0.05 / 8) == pytest.approx(0.29104264152591025, rel=1e-9)
+    assert mc.compute_scale(ci, cm, ci + cm, 2.497705474412374) == pytest.approx(3.3529447079923145, rel=1e-11)
+    g = golden("ref_predict_moments")
+    for i in range(0, 64, 7):
+        a, b_, c = mc.predict_moments(list(g["rows"][i]))
+        assert relerr(a, g["cov_infer"][i]) < TIGHT and relerr(b_, g["cov_mu"][i]) < TIGHT
+        assert relerr(c, g["cov_t"][i]) < TIGHT
+    with pytest.raises(np.linalg.LinAlgError):
+        x = np.arange(10.0)
+        mc.predict_moments([x, x * 2, np.ones(10), np.ones(10)])       # Sigma_tau = 0
+
+
+# ----------------------------------------------------- per-step pipeline goldens
+def _pipeline(dev, g):
+    from ccmpc_b200 import ops
+    samples, offsets = T_(g["samples"], dev), T_(g["offsets"], dev, torch.int64)
+    pivot = ops.cell_pivot(samples, offsets)
+    sums = ops.sample_sums(samples, offsets, pivot)
+    eps = T_(g["eps_ura"][g["cell_obstacle"], g["cell_mode"]], dev)
+    return samples, offsets, pivot, sums, eps
+
+
+def test_minkowski_halfplanes_match_reference_golden(dev, golden):
+    """ref_pipeline.npz was produced by the reference's predict_moments / compute_mvoe /
+    choose_closest_tangent / compute_lower_bound inside the restated loop of v8ideal:881-947."""
+    from ccmpc_b200 import ops
+    g = golden("ref_pipeline")
+    T = int(g["T"])
+    samples, offsets, pivot, sums, eps = _pipeline(dev, g)
+    out = ops.minkowski_halfplanes(sums, pivot, T_(g["ref_traj"], dev), eps, prediction_horizon=T)
+    h = {k: v.cpu().numpy() for k, v in out.items()}
+    assert not h["status"].any()
+    np.testing.assert_array_equal(h["idx_side"] & 1, g["mk_idx"])                          # bit-exact
+    np.testing.assert_array_equal(np.where(h["idx_side"] & 2, -1, 1), g["mk_side"])        # bit-exact
+    assert relerr(h["nd"][..., :2], g["mk_n"]) < TIGHT and relerr(h["nd"][..., 2], g["mk_d"]) < TIGHT
+    assert relerr(h["ab"][..., :2], g["mk_A"]) < TIGHT and relerr(h["ab"][..., 2], g["mk_b"]) < TIGHT
+    for i in np.ndindex(g["mk_d"].shape):                                                   # per-matrix 1e-5 bar
+        assert relerr(full(h["q"][i]), g["mk_Q"][i]) < 1e-7
+        assert relerr(full(h["q1"][i]), g["mk_Q1"][i]) < 1e-7
+        assert relerr(full(h["cov_infer"][i]), g["mk_cov_infer"][i]) < TIGHT
+        assert relerr(full(h["cov_mu"][i]), g["mk_cov_mu"][i]) < TIGHT
+    np.testing.assert_allclose(h["betas"][..., 0], g["mk_beta1"], rtol=1e-6)
+    np.testing.assert_allclose(h["betas"][..., 1], g["mk_beta2"], rtol=1e-6)
+    np.testing.assert_allclose(h["prob_pair"], g["mk_prob_pair"], rtol=1e-7, atol=1e-12)
+    np.testing.assert_allclose(h["prob_lower"], g["mk_prob_lower"], rtol=1e-7, atol=1e-12)
+    assert relerr(h["mean"], g["mk_mean"]) < 1e-13
+
+
+def test_affine_halfplanes_match_reference_golden(dev, golden):
+    from ccmpc_b200 import ops
+    g = golden("ref_pipeline")
+    T = int(g["T"])
+    samples, offsets, pivot, sums, eps = _pipeline(dev, g)
+    out = ops.affine_halfplanes(sums, pivot, T_(g["ref_traj"], dev), eps, Tpred=T)
+    h = {k: v.cpu().numpy() for k, v in out.items()}
+    assert not h["status"].any()
+    np.testing.assert_array_equal(h["idx_side"] & 1, g["af_idx"])
+    np.testing.assert_array_equal(np.where(h["idx_side"] & 2, -1, 1), g["af_side"])
+    assert relerr(h["nd"][..., :2], g["af_n"]) < TIGHT and relerr(h["nd"][..., 2], g["af_d"]) < TIGHT
+    np.testing.assert_allclose(h["offset_rhs"][..., 0], g["af_offset"], rtol=1e-8)
+    assert relerr(h["offset_rhs"][..., 1], g["af_rhs"]) < TIGHT
+    assert relerr(h["mean"], g["af_mean"]) < 1e-13
+    assert relerr(full(h["cov"]), g["af_cov"]) < TIGHT
+
+
+# --------------------------------------------------------- K2 + K6 sums / counts
+def _ragged_cells(rng, T, sizes, spread=3.0, centre=(170.0, -80.0)):
+    chunks, offs = [], [0]
+    for n in sizes:
+        mu = np.asarray(centre) + rng.normal(size=(T, 2)) * 4
+        L = rng.normal(size=(T, 2, 2)) * spread / 3
+        x = mu + np.einsum("tij,ntj->nti", L, rng.normal(size=(n, T, 2)))
+        chunks.append((x - 100).astype(np.float32).astype(np.float64) + 100)
+        offs.append(offs[-1] + n)
+    flat = np.concatenate(chunks) if chunks else np.zeros((0, T, 2))
+    return flat, np.asarray(offs, np.int64)
+
+
+@pytest.mark.parametrize("T,sizes", [(8, [200, 1, 0, 5000, 37, 4097]), (16, [1800, 1792, 1793, 3, 20000]),
+                                     (1, [10, 300]), (3, [2, 999, 0, 0, 64]), (5, [12345]), (7, [0, 0, 17])])
+def test_sample_sums_counts_bit_exact_and_moments(dev, T, sizes):
+    from ccmpc_b200 import ops
+    from oracle import restate
+    rng = np.random.default_rng(100 + T)
+    flat, offs = _ragged_cells(rng, T, sizes)
+    ego = np.asarray([170.0, -80.0]) + rng.normal(size=(T, 2)) * 2
+    yaws = rng.uniform(-np.pi, np.pi, size=flat.shape[:2])
+    samples, offsets = T_(flat, dev), T_(offs, dev, torch.int64)
+    pivot = ops.cell_pivot(samples, offsets)
+    sums = ops.sample_sums(samples, offsets, pivot, ego=T_(ego, dev), yaws=T_(yaws, dev))
+    mom = ops.moments_from_sums(sums, pivot)
+    L = ops.sums_layout(T)
+    assert sums.shape[1] == L["len"] == ops.sums_len(T)
+    s = sums.cpu().numpy()
+    counts = mom["counts"].cpu().numpy()
+    for c, n in enumerate(sizes):
+        pos = flat[offs[c]:offs[c + 1]]
+        assert s[c, 0] == n
+        coll, any_, pen, d2s = restate.collision_counts(pos, ego)
+        np.testing.assert_array_equal(counts[c, :T], coll)                     # bit-exact integer counts
+        assert counts[c, T] == any_
+        np.testing.assert_array_equal(s[c, L["coll"]:L["coll"] + T], coll.astype(np.float64))
+        np.testing.assert_allclose(s[c, L["pen"]:L["pen"] + T], pen, rtol=1e-12, atol=1e-9)
+        np.testing.assert_allclose(s[c, L["d2s"]:L["d2s"] + T], d2s, rtol=1e-12)
+        if n >= 2:
+            mean, cov, cross = restate.cell_moments(pos)
+            assert relerr(mom["mean"][c].cpu().numpy(), mean) < 1e-13
+            for t in range(T):
+                tol = TIGHT if n > 2 * T else 1e-6
+                assert relerr(mom["cov"][c, t].cpu().numpy(), cov[t]) < tol
+                for tau in range(t):
+                    assert np.max(np.abs(mom["cross"][c, t, tau].cpu().numpy() - cross[t, tau])) < tol * max(
+                        np.max(np.abs(cov[t])), np.max(np.abs(cov[tau])))
+            yw = yaws[offs[c]:offs[c + 1]]
+            np.testing.assert_allclose(mom["yaw_mean"][c].cpu().numpy(), yw.mean(axis=0), rtol=1e-12, atol=1e-13)
+            np.testing.assert_allclose(mom["yaw_var"][c].cpu().numpy(), yw.var(axis=0, ddof=1), rtol=1e-9)
+
+
+def test_sample_sums_per_cell_ego_and_linearity_over_shards(dev):
+    """Counts and power sums of the whole = sum over sample shards with a common pivot
+    (what the multi-GPU all-reduce relies on)."""
+    from ccmpc_b200 import ops
+    rng = np.random.default_rng(7)
+    T = 8
+    flat, offs = _ragged_cells(rng, T, [3000, 5000])
+    ego = np.asarray([170.0, -80.0]) + rng.normal(size=(2, T, 2)) * 2
+    pivot = T_(np.stack([flat[0], flat[3000]]), dev)
+    whole = ops.sample_sums(T_(flat, dev), T_(offs, dev, torch.int64), pivot, ego=T_(ego, dev))
+    parts = []
+    for lo, hi in ((0, 0.3), (0.3, 1.0)):
+        sel = [np.arange(offs[c] + int(lo * (offs[c + 1] - offs[c])), offs[c] + int(hi * (offs[c + 1] - offs[c])))
+               for c in range(2)]
+        sub = np.concatenate([flat[s] for s in sel])
+        so = np.asarray([0, len(sel[0]), len(sel[0]) + len(sel[1])], np.int64)
+        parts.append(ops.sample_sums(T_(sub, dev), T_(so, dev, torch.int64), pivot, ego=T_(ego, dev)))
+    tot = (parts[0] + parts[1]).cpu().numpy()
+    w = whole.cpu().numpy()
+    L = ops.sums_layout(T)
+    np.testing.assert_array_equal(tot[:, L["coll"]:L["any"] + 1], w[:, L["coll"]:L["any"] + 1])   # exact integers
+    assert tot[:, 0].tolist() == [3000, 5000]
+    np.testing.assert_allclose(tot, w, rtol=1e-11, atol=1e-7)
+
+
+def test_violation_counts_bit_exact(dev, golden):
+    from ccmpc_b200 import ops
+    from oracle import restate
+    g = golden("ref_pipeline")
+    T = int(g["T"])
+    samples, offsets, pivot, sums, eps = _pipeline(dev, g)
+    out = ops.minkowski_halfplanes(sums, pivot, T_(g["ref_traj"], dev), eps, prediction_horizon=T)
+    viol = ops.violation_counts(samples, offsets, out["nd"], out["idx_side"]).cpu().numpy()
+    nd = out["nd"].cpu().numpy()
+    side = np.where(out["idx_side"].cpu().numpy() & 2, -1, 1)
+    t_of = [t for t in range(T) for _ in range(t)]
+    for c in range(len(g["offsets"]) - 1):
+        pos = g["samples"][g["offsets"][c]:g["offsets"][c + 1]]
+        ref = restate.violation_counts(pos, nd[c, :, :2], nd[c, :, 2], side[c], t_of)
+        np.testing.assert_array_equal(viol[c], ref)
+    # shifting every line by +-6 sigma flips the count between 0 and N_k: a sanity check the
+    # predicate is not vacuous
+    assert viol.max() <= np.diff(g["offsets"]).max()
+
+
+# ------------------------------------------------------------------------- K5
+def test_vertices_match_reference_golden(dev, golden):
+    from ccmpc_b200 import npu
+    g = golden("ref_vertices")
+    v = npu.vertices_of_bboxes(g["centers"], g["theta"], g["lw"])
+    np.testing.assert_allclose(v, g["vertices"], rtol=0, atol=2e-13 * 200)       # coordinates ~ 2e2
+    vs = npu.vertices_of_bboxes(g["centers"][:7], float(g["theta"][0]), g["lw"])
+    np.testing.assert_allclose(vs, g["vertices_scalar_theta"], rtol=0, atol=4e-11)
+    per_box = npu.vertices_of_bboxes(g["centers"][:4], g["theta"][:4], np.array([[3.7, 1.79], [4.0, 2.0]] * 2))
+    np.testing.assert_allclose(per_box[0], g["vertices"][0], atol=4e-11)
+
+
+@pytest.mark.parametrize("T,sizes", [(8, [200, 1, 5000, 0, 4097]), (16, [33, 9000])])
+def test_l4_outer_matches_oracle(dev, T, sizes):
+    from ccmpc_b200 import ops, npu
+    from oracle import restate
+    rng = np.random.default_rng(5)
+    flat, offs = _ragged_cells(rng, T, sizes)
+    yaws = rng.uniform(-0.3, 0.3, size=flat.shape[:2]) + rng.uniform(-np.pi, np.pi)
+    samples, offsets, yw = T_(flat, dev), T_(offs, dev, torch.int64), T_(yaws, dev)
+    pivot = ops.cell_pivot(samples, offsets)
+    sums = ops.sample_sums(samples, offsets, pivot, yaws=yw)
+    mom = ops.moments_from_sums(sums, pivot, want_cross=False)
+    At, b0 = ops.l4_outer(samples, yw, offsets, mom["yaw_mean"], lw=restate.BBOX_DEFAULT)
+    At, b0 = At.cpu().numpy(), b0.cpu().numpy()
+    for c, n in enumerate(sizes):
+        if n == 0:
+            assert np.isnan(b0[c]).all()
+            continue
+        A_ref, b_ref, th = restate.l4_cell(flat[offs[c]:offs[c + 1]], yaws[offs[c]:offs[c + 1]])
+        assert relerr(At[c], A_ref) < 1e-11
+        assert relerr(b0[c], b_ref) < 1e-11
+    # scalar twin on explicit corners
+    c = 0
+    verts = restate.box_vertices(flat[:sizes[0], 2], yaws[:sizes[0], 2], np.asarray(restate.BBOX_DEFAULT))
+    A1, b1 = npu.compute_L4_outerapproximation(0.37, verts)
+    A2, b2 = restate.l4_outer(0.37, verts)
+    assert relerr(A1, A2) < 1e-14 and relerr(b1, b2) < 1e-13
+
+
+# ------------------------------------------------------------------------- K1
+PHILOX_KAT = [  # Random123 kat_vectors, philox4x32-10
+    ((0, 0, 0, 0), (0, 0), (0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8)),
+    ((0xffffffff,) * 4, (0xffffffff,) * 2, (0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd)),
+    ((0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344), (0xa4093822, 0x299f31d0),
+     (0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1)),
+]
+
+
+def test_philox_known_answers(dev):
+    from ccmpc_b200 import ops
+    ctr = torch.tensor(np.array([k[0] for k in PHILOX_KAT], dtype=np.uint32).view(np.int32), device=dev)
+    key = torch.tensor(np.array([k[1] for k in PHILOX_KAT], dtype=np.uint32).view(np.int32), device=dev)
+    out = ops.philox4x32(ctr, key).cpu().numpy().view(np.uint32)
+    np.testing.assert_array_equal(out, np.array([k[2] for k in PHILOX_KAT], dtype=np.uint32))
+
+
+def _scene_moments(seed, O, K, T):
+    from oracle import synth
+    sc = synth.make_scene(seed, O, K, T)
+    mean, cov, cross = sc.moments()
+    C = O * K
+    return sc, mean.reshape(C, T, 2), cov.reshape(C, T, 2, 2), cross.reshape(C, T, T, 2, 2)
+
+
+def test_rollout_with_supplied_noise_matches_oracle(dev):
+    from ccmpc_b200 import ops
+    from oracle import restate
+    sc, mean, cov, cross = _scene_moments(3, 2, 3, 9)
+    C, Tsh, n = 6, 8, 777
+    rng = np.random.default_rng(0)
+    Z = rng.standard_normal((C, n, Tsh, 2))
+    x0 = mean[:, 0] + rng.normal(size=(C, 2)) * 0.1
+    traj, _, status, x0_used = ops.mc_rollout(T_(mean, dev), T_(cov, dev), T_(cross, dev), T_(x0, dev), n, Tsh,
+                                              z=T_(Z, dev))
+    assert not status.any()
+    np.testing.assert_array_equal(x0_used.cpu().numpy(), x0)
+    traj = traj.cpu().numpy()
+    for c in range(C):
+        ref = restate.ideal_rollout(mean[c], cov[c], cross[c], Tsh, Z[c], x0[c])
+        assert relerr(traj[c], ref) < 1e-13
+
+
+def test_rollout_philox_statistics_and_shard_invariance(dev):
+    """Sampling parity is statistical (the reference draws from MT19937): the rollout's sample
+    moments must match the conditional-Gaussian chain's analytic moments within CLT bounds, and
+    the stream must not depend on how samples are sharded."""
+    from ccmpc_b200 import ops
+    sc, mean, cov, cross = _scene_moments(3, 1, 2, 9)
+    C, Tsh, n = 2, 8, 400_000
+    args = (T_(mean, dev), T_(cov, dev), T_(cross, dev))
+    traj, z, status, x0 = ops.mc_rollout(*args, None, n, Tsh, seed=42, want_z=True)
+    assert not status.any()
+    z = z.cpu().numpy()
+    assert abs(z.mean()) < 5 / np.sqrt(z.size) and abs(z.var() - 1) < 5 * np.sqrt(2 / z.size)
+    assert abs(np.mean(z ** 4) - 3) < 0.05 and np.abs(z).max() < 7
+    assert abs(np.corrcoef(z[0, :, 0, 0], z[0, :, 1, 0])[0, 1]) < 0.01
+    # same seed, two shards with sample_offset == one launch
+    a, _, _, _ = ops.mc_rollout(*args, x0, n // 2, Tsh, seed=42)
+    b, _, _, _ = ops.mc_rollout(*args, x0, n - n // 2, Tsh, seed=42, sample_offset=n // 2)
+    assert torch.equal(torch.cat([a, b], dim=1), traj)
+    # chain moments: x_{t+1} | x_t Gaussian with the reference's A_t, L_t starting from the point x0
+    x0 = x0.cpu().numpy()
+    tr = traj.cpu().numpy()
+    from oracle import restate
+    for c in range(C):
+        A, L = restate.rollout_params(mean[c], cov[c], cross[c], Tsh)
+        m, S = x0[c].copy(), np.zeros((2, 2))
+        for t in range(Tsh):
+            m = mean[c, t + 1] + A[t] @ (m - mean[c, t])
+            S = A[t] @ S @ A[t].T + L[t] @ L[t].T
+            xs = tr[c, :, t]
+            se = np.sqrt(np.diag(S) / n)
+            assert np.all(np.abs(xs.mean(axis=0) - m) < 5 * se + 1e-12)
+            assert relerr(np.cov(xs.T), S) < 0.02
+    # non-PD conditional covariance is reported, not silently sampled
+    bad = cov.copy(); bad[0, 3] = -bad[0, 3]
+    _, _, st, _ = ops.mc_rollout(T_(mean, dev), T_(bad, dev), T_(cross, dev), None, 16, Tsh)
+    assert st[0].item() in (ops.ST_SINGULAR, ops.ST_NO_TANGENT)
+
+
+# ------------------------------------------------------------------------ A12
+def test_episode_cost_matches_oracle(dev):
+    from ccmpc_b200 import cost
+    from oracle import restate
+    rng = np.random.default_rng(9)
+    for H in (2, 3, 14, 50):
+        X = [np.array([160 + rng.normal(), -80 + rng.normal(), 0.1, 5.0]) for _ in range(H)]
+        U = [rng.normal(size=2) for _ in range(H)]
+        c, cu = cost.cost_final(X, U)
+        rc, rcu = restate.episode_cost(X, U)
+        assert c == pytest.approx(rc, rel=1e-13) and cu == pytest.approx(rcu, rel=1e-13)
+    with pytest.raises(UnboundLocalError):
+        cost.cost_final([np.zeros(4)], [np.zeros(2)])
