@@ -369,9 +369,9 @@ extern "C" int ccmpc_mvoe_fit(const double* sigma1, const double* sigma2, double
                               double tol, int maxiter, int accel, double* beta, double* q, int32_t* iters,
                               uint8_t* status, void* stream) {
     CCMPC_REQUIRE(M >= 0, "ccmpc_mvoe_fit: M < 0");
-    CCMPC_REQUIRE(sigma1 && beta && q, "ccmpc_mvoe_fit: null sigma1/beta/q");
     CCMPC_REQUIRE(maxiter >= 0, "ccmpc_mvoe_fit: maxiter < 0");
     if (M == 0) return CCMPC_OK;
+    CCMPC_REQUIRE(sigma1 && beta && q, "ccmpc_mvoe_fit: null sigma1/beta/q");
     cudaStream_t st = (cudaStream_t)stream;
     if (sigma2) {
         mvoe_fit_kernel<false><<<fit_grid(M), FIT_THREADS, 0, st>>>(sigma1, sigma2, 0.0, M, tol, maxiter, accel,
@@ -388,9 +388,9 @@ extern "C" int ccmpc_mvoe_halfplane_sweep(const double* cov, const double* mu, c
                                           int maxiter, int accel, double* q, double* nd, int8_t* idx_side,
                                           uint8_t* status, void* stream) {
     CCMPC_REQUIRE(S >= 0 && O > 0 && T > 0 && K > 0, "ccmpc_mvoe_halfplane_sweep: bad dims");
-    CCMPC_REQUIRE(cov && mu && ref && q && nd && idx_side, "ccmpc_mvoe_halfplane_sweep: null pointer");
     const int64_t M = S * O * T * K;
     if (M == 0) return CCMPC_OK;
+    CCMPC_REQUIRE(cov && mu && ref && q && nd && idx_side, "ccmpc_mvoe_halfplane_sweep: null pointer");
     sweep_kernel<<<fit_grid(M), FIT_THREADS, 0, (cudaStream_t)stream>>>(cov, mu, ref, M, O, T, K, chi_scale,
                                                                         footprint_r2, tol, maxiter, accel, q, nd,
                                                                         idx_side, status);
@@ -400,8 +400,9 @@ extern "C" int ccmpc_mvoe_halfplane_sweep(const double* cov, const double* mu, c
 extern "C" int ccmpc_tangent(const double* mu, const double* sigma, const double* c, const double* m,
                              const double* a, const int32_t* const_idx, int64_t M, double* d12, double* dist,
                              double* d_star, int32_t* idx, void* stream) {
-    CCMPC_REQUIRE(M >= 0 && mu && sigma && c && m && a, "ccmpc_tangent: bad arguments");
+    CCMPC_REQUIRE(M >= 0, "ccmpc_tangent: M < 0");
     if (M == 0) return CCMPC_OK;
+    CCMPC_REQUIRE(mu && sigma && c && m && a, "ccmpc_tangent: null input");
     tangent_kernel<<<(unsigned)((M + 127) / 128), 128, 0, (cudaStream_t)stream>>>(mu, sigma, c, m, a, const_idx, M,
                                                                                  d12, dist, d_star, idx);
     return check_launch("tangent_kernel");
@@ -410,10 +411,11 @@ extern "C" int ccmpc_tangent(const double* mu, const double* sigma, const double
 extern "C" int ccmpc_scale_lower(const double* cov_infer, const double* cov_mu, const double* cov_t,
                                  const double* gamma, const double* eps, double target_p, int64_t M,
                                  double* scale, double* lower, void* stream) {
-    CCMPC_REQUIRE(M >= 0 && cov_infer && cov_mu && cov_t, "ccmpc_scale_lower: bad arguments");
+    CCMPC_REQUIRE(M >= 0, "ccmpc_scale_lower: M < 0");
+    if (M == 0) return CCMPC_OK;
+    CCMPC_REQUIRE(cov_infer && cov_mu && cov_t, "ccmpc_scale_lower: null input");
     CCMPC_REQUIRE(!scale || gamma, "ccmpc_scale_lower: scale needs gamma");
     CCMPC_REQUIRE(!lower || eps, "ccmpc_scale_lower: lower needs eps");
-    if (M == 0) return CCMPC_OK;
     scale_lower_kernel<<<(unsigned)((M + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
         cov_infer, cov_mu, cov_t, gamma, eps, target_p, M, scale, lower);
     return check_launch("scale_lower_kernel");
