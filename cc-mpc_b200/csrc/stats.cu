@@ -18,38 +18,250 @@
 namespace ccmpc {
 
 constexpr int ST_THREADS = 256;
-constexpr int ST_MAXP = 8;          // register-prefetched passes per chunk
-constexpr int ST_TILE_BYTES = 32768;
-constexpr int ST_CHUNKS_PER_UNIT = 16;
+constexpr int SS_WARPS = ST_THREADS / 32;
+constexpr int SS_DEPTH = 4;            // 4-sample groups in flight per warp (register prefetch ring)
+constexpr int SS_DEPTH_YAW = 3;        // ... when the yaw tensor is streamed as well (register budget)
+constexpr int SS_SLAB = 2048;          // samples per unit (= per CTA)
 
-struct StatsGeom {
-    int T, D, DP, nb, ntile, ns, rpp, ch, npass, slab;
-    __host__ explicit StatsGeom(int T_) {
-        T = T_;
-        D = 2 * T_;
-        DP = (D + 3) / 4 * 4;
-        nb = DP / 4;
-        ntile = nb * (nb + 1) / 2;
-        ns = ST_THREADS / ntile;
-        rpp = ST_THREADS / T;
-        int c = ST_MAXP * rpp;
-        int cap = ST_TILE_BYTES / (DP * 8);
-        if (c > cap) c = cap;
-        if (c > ns * 16) c = ns * 16;
-        if (c >= ns) c = c / ns * ns;
-        ch = c;
-        npass = (ch + rpp - 1) / rpp;
-        slab = ch * ST_CHUNKS_PER_UNIT;
-    }
-    __host__ size_t smem_bytes() const {
-        size_t tile = (size_t)ch * DP;
-        size_t red = (size_t)ns * ntile * 16;
-        size_t red2 = (size_t)ST_THREADS * 7;
-        size_t m = tile > red ? tile : red;
-        if (red2 > m) m = red2;
-        return m * 8 + (size_t)ch * 4 + (size_t)4 * T * 8 + 16;
-    }
+// ---------------------------------------------------------------------------
+// The 2T x 2T second-moment matrix is a Gram matrix  G = U^T U  over samples
+// (U = pivot-shifted coordinates): a dense fp64 contraction of 2T(2T+1)/2 = 528
+// unique FMAs per 256-byte sample row at T = 16.  tools/fp64_pipe_bench.cu shows
+// DFMA and mma.sync.m8n8k4.f64 (DMMA) share one pipe on B200 (33.7 / 37.1 TFLOP/s),
+// but the DMMA form needs ONE register operand per 8 FMAs instead of shared-memory
+// operand traffic, so the fragments are loaded straight from global memory:
+//
+//   lane = 4*q + r   (r = sample within the 4-sample group = MMA k index,
+//                     q = 0..7 = MMA m / n index)
+//   the lane loads columns NF*q .. NF*q+NF-1 of sample row r (NF = 2: T <= 8,
+//   NF = 4: T <= 16) - a warp reads 4 whole rows = one contiguous block;
+//   fragment j = column NF*q + j serves as BOTH the A fragment (row.col layout:
+//   A[m][k] -> lane 4m+k) and the B fragment (B[k][n] -> lane 4n+k) of
+//   tile (bi, bj):  C[m][n] += sum_k U[k][NF*m+bi] * U[k][NF*n+bj].
+//   NF(NF+1)/2 tiles (bi >= bj) cover every (i >= j) entry.
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void dmma8x8x4(double& c0, double& c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                 : "+d"(c0), "+d"(c1)
+                 : "d"(a), "d"(b));
+}
+
+struct StatsArgs {
+    const double* samples;
+    const int64_t* offsets;
+    const int32_t* cub;
+    const double* pivot;
+    const double* ego;
+    int64_t ego_cell_stride;
+    const double* yaws;
+    double* partials;
+    int64_t C;
+    double r2;
+    int T;
 };
+
+template <int NF>
+struct StatsSmem {
+    static constexpr int NT = NF * (NF + 1) / 2;   // 8x8 tiles (bi >= bj)
+    static constexpr int TP = 4 * NF;              // timesteps covered by a warp (padded)
+    static constexpr int O_S1 = NT * 64;           // [8 NF] column sums
+    static constexpr int O_COLL = O_S1 + 8 * NF;   // [TP] each: coll, pen, d2s, yaw, yaw2
+    static constexpr int O_PEN = O_COLL + TP;
+    static constexpr int O_D2S = O_PEN + TP;
+    static constexpr int O_YAW = O_D2S + TP;
+    static constexpr int O_YAW2 = O_YAW + TP;
+    static constexpr int O_ANY = O_YAW2 + TP;
+    static constexpr int PW = O_ANY + 2;           // doubles per warp
+    static constexpr size_t BYTES = (size_t)SS_WARPS * PW * sizeof(double);
+};
+
+template <int NF, bool YAW>
+__global__ void __launch_bounds__(ST_THREADS, 2) sample_sums_kernel(const StatsArgs a) {
+    constexpr int DEPTH = YAW ? SS_DEPTH_YAW : SS_DEPTH;
+    using SM = StatsSmem<NF>;
+    constexpr int NT = SM::NT;
+    constexpr int TS = NF / 2;                     // timesteps per lane
+    extern __shared__ __align__(16) double smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int r = lane & 3, q = lane >> 2;
+    const int T = a.T;
+    // ---- which unit am I -------------------------------------------------
+    const int n_units = a.cub[a.C];
+    const int u = blockIdx.x;
+    if (u >= n_units) return;
+    int64_t lo = 0, hi = a.C;            // largest c with cub[c] <= u
+    while (hi - lo > 1) {
+        int64_t mid = (lo + hi) >> 1;
+        if (a.cub[mid] <= u) lo = mid; else hi = mid;
+    }
+    const int64_t c = lo;                // cub[c] <= u < cub[c+1]: empty cells own no unit and are never hit
+    const int slab_idx = u - a.cub[c];
+    const int64_t cell_end = a.offsets[c + 1];
+    const int64_t begin = a.offsets[c] + (int64_t)slab_idx * SS_SLAB;
+    const int rows_unit = (int)min((int64_t)SS_SLAB, cell_end - begin);
+    const int ngroups = (rows_unit + 3) >> 2;
+
+    // ---- per-lane constants: its TS timesteps ------------------------------
+    const bool do_count = a.ego != nullptr;
+    constexpr bool do_yaw = YAW;
+    const double r2 = a.r2;
+    double pivx[TS], pivy[TS], ex[TS], ey[TS];
+    bool tv[TS];
+#pragma unroll
+    for (int i = 0; i < TS; ++i) {
+        const int t = TS * q + i;
+        tv[i] = t < T;
+        pivx[i] = tv[i] ? a.pivot[(c * T + t) * 2] : 0.0;
+        pivy[i] = tv[i] ? a.pivot[(c * T + t) * 2 + 1] : 0.0;
+        ex[i] = (tv[i] && do_count) ? a.ego[c * a.ego_cell_stride + 2 * t] : 0.0;
+        ey[i] = (tv[i] && do_count) ? a.ego[c * a.ego_cell_stride + 2 * t + 1] : 0.0;
+    }
+
+    double acc[NT][2];
+#pragma unroll
+    for (int i = 0; i < NT; ++i) acc[i][0] = acc[i][1] = 0.0;
+    double s1x[TS], s1y[TS], pen[TS], d2s[TS], yaw_s[TS], yaw_q[TS];
+    int coll[TS];
+#pragma unroll
+    for (int i = 0; i < TS; ++i) { s1x[i] = s1y[i] = pen[i] = d2s[i] = yaw_s[i] = yaw_q[i] = 0.0; coll[i] = 0; }
+    int any_cnt = 0;
+
+    const double2* g2 = reinterpret_cast<const double2*>(a.samples) + begin * T;
+    const double* gy = YAW ? a.yaws + begin * T : nullptr;
+    double2 buf[DEPTH][TS];
+    double ybuf[DEPTH][YAW ? TS : 1];
+
+    auto fetch = [&](int gg, double2 (&v)[TS], double (&yv)[YAW ? TS : 1]) {
+        const int row = 4 * gg + r;
+        const bool rv = row < rows_unit;
+#pragma unroll
+        for (int i = 0; i < TS; ++i) {
+            const bool ok = rv && tv[i];
+            const int64_t e = (int64_t)row * T + (TS * q + i);
+            v[i] = ok ? __ldcs(g2 + e) : make_double2(0.0, 0.0);
+            if (YAW) yv[i] = ok ? __ldcs(gy + e) : 0.0;
+        }
+    };
+
+#pragma unroll
+    for (int d = 0; d < DEPTH; ++d) fetch(warp + d * SS_WARPS, buf[d], ybuf[d]);
+
+    for (int g0 = warp; g0 < ngroups; g0 += SS_WARPS * DEPTH) {
+#pragma unroll
+        for (int d = 0; d < DEPTH; ++d) {
+            const int gg = g0 + d * SS_WARPS;
+            double2 cur[TS];
+            double ycur[TS];
+#pragma unroll
+            for (int i = 0; i < TS; ++i) { cur[i] = buf[d][i]; ycur[i] = YAW ? ybuf[d][i] : 0.0; }
+            fetch(gg + SS_WARPS * DEPTH, buf[d], ybuf[d]);          // next round's loads in flight
+            if (gg < ngroups) {                                         // warp-uniform
+                const bool rv = 4 * gg + r < rows_unit;
+                double f[NF];
+                bool hit_any = false;
+#pragma unroll
+                for (int i = 0; i < TS; ++i) {
+                    const bool ok = rv && tv[i];
+                    const double x = cur[i].x, y = cur[i].y;
+                    const double ux = ok ? x - pivx[i] : 0.0, uy = ok ? y - pivy[i] : 0.0;
+                    s1x[i] += ux;
+                    s1y[i] += uy;
+                    f[2 * i] = ux;
+                    f[2 * i + 1] = uy;
+                    if (do_count && ok) {
+                        // A9 predicate, fixed order, no FMA contraction
+                        const double dx = __dsub_rn(ex[i], x), dy = __dsub_rn(ey[i], y);
+                        const double d2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
+                        d2s[i] += d2;
+                        if (d2 < r2) {
+                            ++coll[i];
+                            pen[i] += r2 - d2;
+                            hit_any = true;
+                        }
+                    }
+                    if (do_yaw) { yaw_s[i] += ycur[i]; yaw_q[i] = fma(ycur[i], ycur[i], yaw_q[i]); }
+                }
+                if (do_count) {
+                    const unsigned bal = __ballot_sync(0xffffffffu, hit_any);
+                    if (bal) {
+#pragma unroll
+                        for (int rr = 0; rr < 4; ++rr) any_cnt += (bal & (0x11111111u << rr)) != 0;
+                    }
+                }
+                int ti = 0;
+#pragma unroll
+                for (int bi = 0; bi < NF; ++bi)
+#pragma unroll
+                    for (int bj = 0; bj <= bi; ++bj, ++ti) dmma8x8x4(acc[ti][0], acc[ti][1], f[bi], f[bj]);
+            }
+        }
+    }
+
+    // ---- warp epilogue: fixed-order shuffles over the 4 sample rows, then shared memory
+    double* wsm = smem + (size_t)warp * SM::PW;
+#pragma unroll
+    for (int ti = 0; ti < NT; ++ti)
+        *reinterpret_cast<double2*>(wsm + ti * 64 + q * 8 + 2 * r) = make_double2(acc[ti][0], acc[ti][1]);
+#pragma unroll
+    for (int i = 0; i < TS; ++i) {
+        double v[7] = {s1x[i], s1y[i], (double)coll[i], pen[i], d2s[i], yaw_s[i], yaw_q[i]};
+#pragma unroll
+        for (int k = 0; k < 7; ++k) {
+            v[k] += __shfl_xor_sync(0xffffffffu, v[k], 1);
+            v[k] += __shfl_xor_sync(0xffffffffu, v[k], 2);
+        }
+        if (r == 0) {
+            const int t = TS * q + i;
+            wsm[SM::O_S1 + 2 * t] = v[0];
+            wsm[SM::O_S1 + 2 * t + 1] = v[1];
+            wsm[SM::O_COLL + t] = v[2];
+            wsm[SM::O_PEN + t] = v[3];
+            wsm[SM::O_D2S + t] = v[4];
+            wsm[SM::O_YAW + t] = v[5];
+            wsm[SM::O_YAW2 + t] = v[6];
+        }
+    }
+    if (lane == 0) wsm[SM::O_ANY] = (double)any_cnt;
+    __syncthreads();
+
+    // ---- unit epilogue: add the warps in warp order into the partial vector
+    const SumsLayout L(T);
+    double* out = a.partials + (int64_t)u * L.len;
+    for (int e = tid; e < L.len; e += ST_THREADS) {
+        int src;
+        if (e == 0) {
+            out[0] = (double)rows_unit;
+            continue;
+        } else if (e < L.o_s2) {
+            src = SM::O_S1 + (e - L.o_s1);
+        } else if (e < L.o_coll) {
+            const int idx = e - L.o_s2;
+            int i = (int)((sqrtf(8.0f * (float)idx + 1.0f) - 1.0f) * 0.5f);
+            while (i * (i + 1) / 2 > idx) --i;
+            while ((i + 1) * (i + 2) / 2 <= idx) ++i;
+            const int j = idx - i * (i + 1) / 2;
+            int bi = i % NF, bj = j % NF, m = i / NF, n = j / NF;
+            if (bi < bj) { int t0 = bi; bi = bj; bj = t0; t0 = m; m = n; n = t0; }
+            src = (bi * (bi + 1) / 2 + bj) * 64 + m * 8 + n;
+        } else if (e < L.o_any) {
+            src = SM::O_COLL + (e - L.o_coll);
+        } else if (e == L.o_any) {
+            src = SM::O_ANY;
+        } else if (e < L.o_d2s) {
+            src = SM::O_PEN + (e - L.o_pen);
+        } else if (e < L.o_yaw) {
+            src = SM::O_D2S + (e - L.o_d2s);
+        } else if (e < L.o_yaw2) {
+            src = SM::O_YAW + (e - L.o_yaw);
+        } else {
+            src = SM::O_YAW2 + (e - L.o_yaw2);
+        }
+        double s = 0.0;
+#pragma unroll
+        for (int w = 0; w < SS_WARPS; ++w) s += smem[(size_t)w * SM::PW + src];
+        out[e] = s;
+    }
+}
 
 // cell_unit_begin[c] = number of units of cells < c  (exclusive scan of ceil(n_c / slab))
 __global__ void unit_scan_kernel(const int64_t* __restrict__ offsets, int64_t C, int slab,
@@ -91,204 +303,6 @@ __global__ void unit_scan_kernel(const int64_t* __restrict__ offsets, int64_t C,
         __syncthreads();
     }
     if (tid == 0) cub[C] = carry;
-}
-
-struct StatsArgs {
-    const double* samples;
-    const int64_t* offsets;
-    const int32_t* cub;
-    const double* pivot;
-    const double* ego;
-    int64_t ego_cell_stride;
-    const double* yaws;
-    double* partials;
-    int64_t C;
-    double r2;
-    int T, D, DP, nb, ntile, ns, rpp, ch, npass, slab;
-};
-
-__global__ void __launch_bounds__(ST_THREADS, 2) sample_sums_kernel(const StatsArgs a) {
-    extern __shared__ __align__(16) double smem[];
-    const int tid = threadIdx.x;
-    const int T = a.T, DP = a.DP;
-    // ---- which unit am I -------------------------------------------------
-    const int n_units = a.cub[a.C];
-    const int u = blockIdx.x;
-    if (u >= n_units) return;
-    int64_t lo = 0, hi = a.C;            // largest c with cub[c] <= u
-    while (hi - lo > 1) {
-        int64_t mid = (lo + hi) >> 1;
-        if (a.cub[mid] <= u) lo = mid; else hi = mid;
-    }
-    const int64_t c = lo;                // cub[c] <= u < cub[c+1]: empty cells own no unit and are never hit
-    const int slab_idx = u - a.cub[c];
-    const int64_t cell_begin = a.offsets[c], cell_end = a.offsets[c + 1];
-    const int64_t begin = cell_begin + (int64_t)slab_idx * a.slab;
-    const int rows_unit = (int)min((int64_t)a.slab, cell_end - begin);
-
-    // ---- shared memory carve-up -----------------------------------------
-    size_t tile_d = (size_t)a.ch * DP;
-    size_t red_d = (size_t)a.ns * a.ntile * 16;
-    size_t big = tile_d > red_d ? tile_d : red_d;
-    if ((size_t)ST_THREADS * 7 > big) big = (size_t)ST_THREADS * 7;
-    double* tile = smem;
-    double* s_piv = smem + big;                 // [2T]
-    double* s_ego = s_piv + 2 * T;              // [2T]
-    int* s_any = reinterpret_cast<int*>(s_ego + 2 * T);   // [ch]
-    __shared__ int s_anycnt;
-
-    for (int i = tid; i < (int)tile_d; i += ST_THREADS) tile[i] = 0.0;
-    for (int i = tid; i < a.ch; i += ST_THREADS) s_any[i] = 0;
-    if (tid < 2 * T) {
-        s_piv[tid] = a.pivot[c * 2 * T + tid];
-        s_ego[tid] = a.ego ? a.ego[c * a.ego_cell_stride + tid] : 0.0;
-    }
-    if (tid == 0) s_anycnt = 0;
-    __syncthreads();
-
-    // ---- roles -----------------------------------------------------------
-    const int rl = tid / T, t = tid - rl * T;
-    const bool stager = rl < a.rpp;
-    const int tl = tid % a.ntile, subset = tid / a.ntile;
-    const bool worker = subset < a.ns;
-    int rb = 0;
-    while ((rb + 1) * (rb + 2) / 2 <= tl) ++rb;
-    const int cb = tl - rb * (rb + 1) / 2;
-
-    const double pivx = s_piv[2 * t], pivy = s_piv[2 * t + 1];
-    const double ex = s_ego[2 * t], ey = s_ego[2 * t + 1];
-    const bool do_count = a.ego != nullptr;
-    const bool do_yaw = a.yaws != nullptr;
-    const double r2 = a.r2;
-
-    double acc[16];
-#pragma unroll
-    for (int i = 0; i < 16; ++i) acc[i] = 0.0;
-    double s1x = 0.0, s1y = 0.0, pen = 0.0, d2s = 0.0, yaw_sum = 0.0, yaw_sq = 0.0;
-    int coll = 0, any_cnt = 0;
-
-    double2 pre[ST_MAXP];
-    double ypre[ST_MAXP];
-    const double2* g2 = reinterpret_cast<const double2*>(a.samples);
-
-    auto prefetch = [&](int chunk0) {
-        const int rows = min(a.ch, rows_unit - chunk0);
-#pragma unroll
-        for (int p = 0; p < ST_MAXP; ++p) {
-            const int row = p * a.rpp + rl;
-            if (stager && p < a.npass && row < rows) {
-                const int64_t e = (begin + chunk0 + row) * T + t;
-                pre[p] = __ldcs(g2 + e);
-                if (do_yaw) ypre[p] = __ldcs(a.yaws + e);
-            }
-        }
-    };
-
-    prefetch(0);
-    for (int chunk0 = 0; chunk0 < rows_unit; chunk0 += a.ch) {
-        const int rows = min(a.ch, rows_unit - chunk0);
-        // ---- registers -> shared tile (pivot shift), predicate on the raw values
-#pragma unroll
-        for (int p = 0; p < ST_MAXP; ++p) {
-            const int row = p * a.rpp + rl;
-            if (stager && p < a.npass && row < rows) {
-                const double x = pre[p].x, y = pre[p].y;
-                const double ux = x - pivx, uy = y - pivy;
-                s1x += ux;
-                s1y += uy;
-                *reinterpret_cast<double2*>(tile + (size_t)row * DP + 2 * t) = make_double2(ux, uy);
-                if (do_count) {
-                    // A9 predicate, fixed order, no FMA contraction
-                    const double dx = __dsub_rn(ex, x), dy = __dsub_rn(ey, y);
-                    const double d2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
-                    d2s += d2;
-                    if (d2 < r2) {
-                        ++coll;
-                        pen += r2 - d2;
-                        s_any[row] = 1;
-                    }
-                }
-                if (do_yaw) { yaw_sum += ypre[p]; yaw_sq = fma(ypre[p], ypre[p], yaw_sq); }
-            }
-        }
-        __syncthreads();
-        if (chunk0 + a.ch < rows_unit) prefetch(chunk0 + a.ch);   // loads in flight during the rank-k update
-        // ---- any-time hits of this chunk
-        if (do_count) {
-            for (int i = tid; i < rows; i += ST_THREADS) {
-                any_cnt += s_any[i];
-                s_any[i] = 0;
-            }
-        }
-        // ---- rank-k update: 4x4 register tile per thread, samples strided over subsets
-        if (worker) {
-            const double* ap = tile + 4 * rb;
-            const double* bp = tile + 4 * cb;
-#pragma unroll 2
-            for (int s = subset; s < rows; s += a.ns) {
-                const double2 a01 = *reinterpret_cast<const double2*>(ap + (size_t)s * DP);
-                const double2 a23 = *reinterpret_cast<const double2*>(ap + (size_t)s * DP + 2);
-                const double2 b01 = *reinterpret_cast<const double2*>(bp + (size_t)s * DP);
-                const double2 b23 = *reinterpret_cast<const double2*>(bp + (size_t)s * DP + 2);
-                const double av[4] = {a01.x, a01.y, a23.x, a23.y};
-                const double bv[4] = {b01.x, b01.y, b23.x, b23.y};
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) acc[i * 4 + j] = fma(av[i], bv[j], acc[i * 4 + j]);
-            }
-        }
-        __syncthreads();
-    }
-
-    // ---- unit epilogue: fixed-order reductions into the partial vector ----
-    const SumsLayout L(T);
-    double* out = a.partials + (int64_t)u * L.len;
-    double* red = tile;
-    if (worker) {
-#pragma unroll
-        for (int i = 0; i < 16; ++i) red[((size_t)subset * a.ntile + tl) * 16 + i] = acc[i];
-    }
-    __syncthreads();
-    for (int e = tid; e < a.ntile * 16; e += ST_THREADS) {
-        const int tt = e >> 4, ij = e & 15;
-        int trb = 0;
-        while ((trb + 1) * (trb + 2) / 2 <= tt) ++trb;
-        const int tcb = tt - trb * (trb + 1) / 2;
-        const int i = 4 * trb + (ij >> 2), j = 4 * tcb + (ij & 3);
-        if (i < a.D && j < a.D && i >= j) {
-            double s = 0.0;
-            for (int k = 0; k < a.ns; ++k) s += red[((size_t)k * a.ntile + tt) * 16 + ij];
-            out[L.o_s2 + i * (i + 1) / 2 + j] = s;
-        }
-    }
-    __syncthreads();
-    red[tid * 7 + 0] = s1x;
-    red[tid * 7 + 1] = s1y;
-    red[tid * 7 + 2] = (double)coll;
-    red[tid * 7 + 3] = pen;
-    red[tid * 7 + 4] = d2s;
-    red[tid * 7 + 5] = yaw_sum;
-    red[tid * 7 + 6] = yaw_sq;
-    if (any_cnt) atomicAdd(&s_anycnt, any_cnt);
-    __syncthreads();
-    if (tid < T) {
-        double r[7] = {0, 0, 0, 0, 0, 0, 0};
-        for (int k = 0; k < a.rpp; ++k)
-#pragma unroll
-            for (int q = 0; q < 7; ++q) r[q] += red[(k * T + tid) * 7 + q];
-        out[L.o_s1 + 2 * tid] = r[0];
-        out[L.o_s1 + 2 * tid + 1] = r[1];
-        out[L.o_coll + tid] = r[2];
-        out[L.o_pen + tid] = r[3];
-        out[L.o_d2s + tid] = r[4];
-        out[L.o_yaw + tid] = r[5];
-        out[L.o_yaw2 + tid] = r[6];
-    }
-    if (tid == 0) {
-        out[0] = (double)rows_unit;
-        out[L.o_any] = (double)s_anycnt;
-    }
 }
 
 // sums[c] = sum over the cell's units, in unit order
@@ -425,9 +439,8 @@ static int64_t max_units(int64_t n_total, int64_t C, int slab) { return n_total 
 
 extern "C" size_t ccmpc_sample_sums_workspace_bytes(int64_t n_total, int64_t C, int T) {
     if (T < 1 || T > CCMPC_MAX_T || n_total < 0 || C < 0) return 0;
-    StatsGeom g(T);
     size_t cub = ((size_t)(C + 1) * sizeof(int32_t) + 255) / 256 * 256;
-    return cub + (size_t)max_units(n_total, C, g.slab) * SumsLayout(T).len * sizeof(double) + 256;
+    return cub + (size_t)max_units(n_total, C, SS_SLAB) * SumsLayout(T).len * sizeof(double) + 256;
 }
 
 extern "C" int ccmpc_sample_sums(const double* samples, const int64_t* offsets, int64_t n_total, int64_t C, int T,
@@ -446,22 +459,26 @@ extern "C" int ccmpc_sample_sums(const double* samples, const int64_t* offsets, 
         return CCMPC_E_WORKSPACE;
     }
     cudaStream_t st = (cudaStream_t)stream;
-    StatsGeom g(T);
     SumsLayout L(T);
     int32_t* cub = reinterpret_cast<int32_t*>(workspace);
     size_t cub_bytes = ((size_t)(C + 1) * sizeof(int32_t) + 255) / 256 * 256;
     double* partials = reinterpret_cast<double*>(reinterpret_cast<char*>(workspace) + cub_bytes);
-    unit_scan_kernel<<<1, 1024, 0, st>>>(offsets, C, g.slab, cub);
+    unit_scan_kernel<<<1, 1024, 0, st>>>(offsets, C, SS_SLAB, cub);
     int rc = check_launch("unit_scan_kernel");
     if (rc) return rc;
     StatsArgs a;
     a.samples = samples; a.offsets = offsets; a.cub = cub; a.pivot = pivot; a.ego = ego;
     a.ego_cell_stride = ego_cell_stride; a.yaws = yaws; a.partials = partials; a.C = C; a.r2 = R * R;
-    a.T = T; a.D = g.D; a.DP = g.DP; a.nb = g.nb; a.ntile = g.ntile; a.ns = g.ns; a.rpp = g.rpp; a.ch = g.ch;
-    a.npass = g.npass; a.slab = g.slab;
-    const int64_t mu = max_units(n_total, C, g.slab);
+    a.T = T;
+    const int64_t mu = max_units(n_total, C, SS_SLAB);
     CCMPC_REQUIRE(mu < (int64_t)1 << 31, "ccmpc_sample_sums: too many units");
-    sample_sums_kernel<<<(unsigned)mu, ST_THREADS, g.smem_bytes(), st>>>(a);
+    if (T <= 8) {
+        if (yaws) sample_sums_kernel<2, true><<<(unsigned)mu, ST_THREADS, StatsSmem<2>::BYTES, st>>>(a);
+        else sample_sums_kernel<2, false><<<(unsigned)mu, ST_THREADS, StatsSmem<2>::BYTES, st>>>(a);
+    } else {
+        if (yaws) sample_sums_kernel<4, true><<<(unsigned)mu, ST_THREADS, StatsSmem<4>::BYTES, st>>>(a);
+        else sample_sums_kernel<4, false><<<(unsigned)mu, ST_THREADS, StatsSmem<4>::BYTES, st>>>(a);
+    }
     rc = check_launch("sample_sums_kernel");
     if (rc) return rc;
     dim3 fg((unsigned)C, (unsigned)((L.len + 127) / 128));
