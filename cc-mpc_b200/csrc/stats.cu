@@ -19,8 +19,8 @@ namespace ccmpc {
 
 constexpr int ST_THREADS = 256;
 constexpr int SS_WARPS = ST_THREADS / 32;
-constexpr int SS_DEPTH = 4;            // 4-sample groups in flight per warp (register prefetch ring)
-constexpr int SS_DEPTH_YAW = 3;        // ... when the yaw tensor is streamed as well (register budget)
+constexpr int SS_DEPTH = 3;            // 4-sample groups in flight per warp (register prefetch ring)
+constexpr int SS_DEPTH_YAW = 2;        // ... when the yaw tensor is streamed as well (register budget)
 constexpr int SS_SLAB = 2048;          // samples per unit (= per CTA)
 
 // ---------------------------------------------------------------------------
@@ -75,17 +75,18 @@ struct StatsSmem {
     static constexpr size_t BYTES = (size_t)SS_WARPS * PW * sizeof(double);
 };
 
-template <int NF, bool YAW>
+template <int NF, bool YAW, bool COUNT, bool FULLT>
 __global__ void __launch_bounds__(ST_THREADS, 2) sample_sums_kernel(const StatsArgs a) {
     constexpr int DEPTH = YAW ? SS_DEPTH_YAW : SS_DEPTH;
+    constexpr int GPR = SS_WARPS * DEPTH;          // 4-sample groups per round of the CTA
     using SM = StatsSmem<NF>;
     constexpr int NT = SM::NT;
     constexpr int TS = NF / 2;                     // timesteps per lane
     extern __shared__ __align__(16) double smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int r = lane & 3, q = lane >> 2;
-    const int T = a.T;
-    // ---- which unit am I -------------------------------------------------
+    const int T = FULLT ? 4 * NF : a.T;
+    // ---- which unit am I (everything here is CTA-uniform) ------------------
     const int n_units = a.cub[a.C];
     const int u = blockIdx.x;
     if (u >= n_units) return;
@@ -100,21 +101,21 @@ __global__ void __launch_bounds__(ST_THREADS, 2) sample_sums_kernel(const StatsA
     const int64_t begin = a.offsets[c] + (int64_t)slab_idx * SS_SLAB;
     const int rows_unit = (int)min((int64_t)SS_SLAB, cell_end - begin);
     const int ngroups = (rows_unit + 3) >> 2;
+    const int rounds = (ngroups + GPR - 1) / GPR;          // uniform loop bounds: the DMMAs below sit in
+    const int full_rounds = (rows_unit >> 2) / GPR;        // provably convergent control flow
 
     // ---- per-lane constants: its TS timesteps ------------------------------
-    const bool do_count = a.ego != nullptr;
-    constexpr bool do_yaw = YAW;
     const double r2 = a.r2;
     double pivx[TS], pivy[TS], ex[TS], ey[TS];
     bool tv[TS];
 #pragma unroll
     for (int i = 0; i < TS; ++i) {
         const int t = TS * q + i;
-        tv[i] = t < T;
+        tv[i] = FULLT || t < T;
         pivx[i] = tv[i] ? a.pivot[(c * T + t) * 2] : 0.0;
         pivy[i] = tv[i] ? a.pivot[(c * T + t) * 2 + 1] : 0.0;
-        ex[i] = (tv[i] && do_count) ? a.ego[c * a.ego_cell_stride + 2 * t] : 0.0;
-        ey[i] = (tv[i] && do_count) ? a.ego[c * a.ego_cell_stride + 2 * t + 1] : 0.0;
+        ex[i] = (tv[i] && COUNT) ? a.ego[c * a.ego_cell_stride + 2 * t] : 0.0;
+        ey[i] = (tv[i] && COUNT) ? a.ego[c * a.ego_cell_stride + 2 * t + 1] : 0.0;
     }
 
     double acc[NT][2];
@@ -126,77 +127,112 @@ __global__ void __launch_bounds__(ST_THREADS, 2) sample_sums_kernel(const StatsA
     for (int i = 0; i < TS; ++i) { s1x[i] = s1y[i] = pen[i] = d2s[i] = yaw_s[i] = yaw_q[i] = 0.0; coll[i] = 0; }
     int any_cnt = 0;
 
-    const double2* g2 = reinterpret_cast<const double2*>(a.samples) + begin * T;
-    const double* gy = YAW ? a.yaws + begin * T : nullptr;
+    // lane's element (double2 index) inside the unit for group 0 of warp 0; groups advance by 4 T
+    const double2* g2 = reinterpret_cast<const double2*>(a.samples) + begin * T + (r * T + TS * q);
+    const double* gy = YAW ? a.yaws + begin * T + (r * T + TS * q) : nullptr;
+
+    // one 4-sample group: shift, S1, A9 predicate, Gram update.  `masked`: rows / timesteps may be absent
+    // (absent entries are fetched as the pivot itself, so u = 0 without a select).
+#define CCMPC_SS_PROCESS(cur, ycur, rv, MASKED)                                                             \
+    do {                                                                                                    \
+        double f[NF];                                                                                       \
+        bool hit_any = false;                                                                               \
+        _Pragma("unroll") for (int i = 0; i < TS; ++i) {                                                    \
+            const bool ok = (MASKED) ? ((rv) && tv[i]) : true;                                              \
+            const double x = (cur)[i].x, y = (cur)[i].y;                                                    \
+            const double ux = x - pivx[i], uy = y - pivy[i];                                                \
+            s1x[i] += ux;                                                                                   \
+            s1y[i] += uy;                                                                                   \
+            f[2 * i] = ux;                                                                                  \
+            f[2 * i + 1] = uy;                                                                              \
+            if (COUNT && ok) {                                                                              \
+                /* A9 predicate, fixed order, no FMA contraction */                                         \
+                const double dx = __dsub_rn(ex[i], x), dy = __dsub_rn(ey[i], y);                            \
+                const double d2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));                          \
+                d2s[i] += d2;                                                                               \
+                if (d2 < r2) {                                                                              \
+                    ++coll[i];                                                                              \
+                    pen[i] += r2 - d2;                                                                      \
+                    hit_any = true;                                                                         \
+                }                                                                                           \
+            }                                                                                               \
+            if (YAW) { yaw_s[i] += (ycur)[i]; yaw_q[i] = fma((ycur)[i], (ycur)[i], yaw_q[i]); }             \
+        }                                                                                                   \
+        if (COUNT) {                                                                                        \
+            const unsigned bal = __ballot_sync(0xffffffffu, hit_any);                                       \
+            if (bal) {                                                                                      \
+                _Pragma("unroll") for (int rr = 0; rr < 4; ++rr) any_cnt += (bal & (0x11111111u << rr)) != 0; \
+            }                                                                                               \
+        }                                                                                                   \
+        int ti = 0;                                                                                         \
+        _Pragma("unroll") for (int bi = 0; bi < NF; ++bi)                                                   \
+            _Pragma("unroll") for (int bj = 0; bj <= bi; ++bj, ++ti)                                        \
+                dmma8x8x4(acc[ti][0], acc[ti][1], f[bi], f[bj]);                                            \
+    } while (0)
+
     double2 buf[DEPTH][TS];
     double ybuf[DEPTH][YAW ? TS : 1];
-
-    auto fetch = [&](int gg, double2 (&v)[TS], double (&yv)[YAW ? TS : 1]) {
-        const int row = 4 * gg + r;
-        const bool rv = row < rows_unit;
-#pragma unroll
-        for (int i = 0; i < TS; ++i) {
-            const bool ok = rv && tv[i];
-            const int64_t e = (int64_t)row * T + (TS * q + i);
-            v[i] = ok ? __ldcs(g2 + e) : make_double2(0.0, 0.0);
-            if (YAW) yv[i] = ok ? __ldcs(gy + e) : 0.0;
-        }
-    };
-
-#pragma unroll
-    for (int d = 0; d < DEPTH; ++d) fetch(warp + d * SS_WARPS, buf[d], ybuf[d]);
-
-    for (int g0 = warp; g0 < ngroups; g0 += SS_WARPS * DEPTH) {
+    // ---- full rounds: no masks, next round's loads in flight during the Gram update
+    auto fetch_full = [&](int rd) {
 #pragma unroll
         for (int d = 0; d < DEPTH; ++d) {
-            const int gg = g0 + d * SS_WARPS;
-            double2 cur[TS];
-            double ycur[TS];
+            const int off = (((rd * DEPTH + d) * SS_WARPS + warp) * 4) * T;
 #pragma unroll
-            for (int i = 0; i < TS; ++i) { cur[i] = buf[d][i]; ycur[i] = YAW ? ybuf[d][i] : 0.0; }
-            fetch(gg + SS_WARPS * DEPTH, buf[d], ybuf[d]);          // next round's loads in flight
-            if (gg < ngroups) {                                         // warp-uniform
-                const bool rv = 4 * gg + r < rows_unit;
-                double f[NF];
-                bool hit_any = false;
+            for (int i = 0; i < TS; ++i) {
+                if (FULLT || tv[i]) {
+                    buf[d][i] = __ldcs(g2 + off + i);
+                    if (YAW) ybuf[d][i] = __ldcs(gy + off + i);
+                } else {
+                    buf[d][i] = make_double2(0.0, 0.0);
+                    if (YAW) ybuf[d][i] = 0.0;
+                }
+            }
+        }
+    };
+    if (full_rounds > 0) fetch_full(0);
+    for (int rd = 0; rd < full_rounds; ++rd) {
+#pragma unroll
+        for (int d = 0; d < DEPTH; ++d) {
+            double2 cur[TS];
+            double ycur[YAW ? TS : 1];
+#pragma unroll
+            for (int i = 0; i < TS; ++i) { cur[i] = buf[d][i]; if (YAW) ycur[i] = ybuf[d][i]; }
+            if (rd + 1 < full_rounds) {
+                const int off = ((((rd + 1) * DEPTH + d) * SS_WARPS + warp) * 4) * T;
 #pragma unroll
                 for (int i = 0; i < TS; ++i) {
-                    const bool ok = rv && tv[i];
-                    const double x = cur[i].x, y = cur[i].y;
-                    const double ux = ok ? x - pivx[i] : 0.0, uy = ok ? y - pivy[i] : 0.0;
-                    s1x[i] += ux;
-                    s1y[i] += uy;
-                    f[2 * i] = ux;
-                    f[2 * i + 1] = uy;
-                    if (do_count && ok) {
-                        // A9 predicate, fixed order, no FMA contraction
-                        const double dx = __dsub_rn(ex[i], x), dy = __dsub_rn(ey[i], y);
-                        const double d2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
-                        d2s[i] += d2;
-                        if (d2 < r2) {
-                            ++coll[i];
-                            pen[i] += r2 - d2;
-                            hit_any = true;
-                        }
-                    }
-                    if (do_yaw) { yaw_s[i] += ycur[i]; yaw_q[i] = fma(ycur[i], ycur[i], yaw_q[i]); }
-                }
-                if (do_count) {
-                    const unsigned bal = __ballot_sync(0xffffffffu, hit_any);
-                    if (bal) {
-#pragma unroll
-                        for (int rr = 0; rr < 4; ++rr) any_cnt += (bal & (0x11111111u << rr)) != 0;
+                    if (FULLT || tv[i]) {
+                        buf[d][i] = __ldcs(g2 + off + i);
+                        if (YAW) ybuf[d][i] = __ldcs(gy + off + i);
                     }
                 }
-                int ti = 0;
-#pragma unroll
-                for (int bi = 0; bi < NF; ++bi)
-#pragma unroll
-                    for (int bj = 0; bj <= bi; ++bj, ++ti) dmma8x8x4(acc[ti][0], acc[ti][1], f[bi], f[bj]);
             }
+            CCMPC_SS_PROCESS(cur, ycur, true, !FULLT);
+        }
+    }
+    // ---- tail rounds: masked rows (absent entries read as the pivot / zero yaw)
+    for (int rd = full_rounds; rd < rounds; ++rd) {
+#pragma unroll
+        for (int d = 0; d < DEPTH; ++d) {
+            const int gg = (rd * DEPTH + d) * SS_WARPS + warp;
+            const bool rv = 4 * gg + r < rows_unit;
+            const int off = gg * 4 * T;
+#pragma unroll
+            for (int i = 0; i < TS; ++i) {
+                const bool ok = rv && tv[i];
+                buf[d][i] = ok ? __ldcs(g2 + off + i) : make_double2(pivx[i], pivy[i]);
+                if (YAW) ybuf[d][i] = ok ? __ldcs(gy + off + i) : 0.0;
+            }
+        }
+#pragma unroll
+        for (int d = 0; d < DEPTH; ++d) {
+            const int gg = (rd * DEPTH + d) * SS_WARPS + warp;
+            const bool rv = 4 * gg + r < rows_unit;
+            CCMPC_SS_PROCESS(buf[d], ybuf[d], rv, true);
         }
     }
 
+#undef CCMPC_SS_PROCESS
     // ---- warp epilogue: fixed-order shuffles over the 4 sample rows, then shared memory
     double* wsm = smem + (size_t)warp * SM::PW;
 #pragma unroll
@@ -472,12 +508,24 @@ extern "C" int ccmpc_sample_sums(const double* samples, const int64_t* offsets, 
     a.T = T;
     const int64_t mu = max_units(n_total, C, SS_SLAB);
     CCMPC_REQUIRE(mu < (int64_t)1 << 31, "ccmpc_sample_sums: too many units");
-    if (T <= 8) {
-        if (yaws) sample_sums_kernel<2, true><<<(unsigned)mu, ST_THREADS, StatsSmem<2>::BYTES, st>>>(a);
-        else sample_sums_kernel<2, false><<<(unsigned)mu, ST_THREADS, StatsSmem<2>::BYTES, st>>>(a);
-    } else {
-        if (yaws) sample_sums_kernel<4, true><<<(unsigned)mu, ST_THREADS, StatsSmem<4>::BYTES, st>>>(a);
-        else sample_sums_kernel<4, false><<<(unsigned)mu, ST_THREADS, StatsSmem<4>::BYTES, st>>>(a);
+    {
+        const unsigned grid = (unsigned)mu;
+        const bool y = yaws != nullptr, cn = ego != nullptr;
+#define CCMPC_SS_LAUNCH(NF, Y, CN, FT)                                                                      \
+    sample_sums_kernel<NF, Y, CN, FT><<<grid, ST_THREADS, StatsSmem<NF>::BYTES, st>>>(a)
+#define CCMPC_SS_PICK(NF, FT)                                                                               \
+    do {                                                                                                    \
+        if (y && cn) CCMPC_SS_LAUNCH(NF, true, true, FT);                                                   \
+        else if (y) CCMPC_SS_LAUNCH(NF, true, false, FT);                                                   \
+        else if (cn) CCMPC_SS_LAUNCH(NF, false, true, FT);                                                  \
+        else CCMPC_SS_LAUNCH(NF, false, false, FT);                                                         \
+    } while (0)
+        if (T == 16) CCMPC_SS_PICK(4, true);
+        else if (T > 8) CCMPC_SS_PICK(4, false);
+        else if (T == 8) CCMPC_SS_PICK(2, true);
+        else CCMPC_SS_PICK(2, false);
+#undef CCMPC_SS_PICK
+#undef CCMPC_SS_LAUNCH
     }
     rc = check_launch("sample_sums_kernel");
     if (rc) return rc;
