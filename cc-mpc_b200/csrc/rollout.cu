@@ -42,30 +42,43 @@ __device__ __forceinline__ Philox philox4x32_10(uint32_t c0, uint32_t c1, uint32
     return Philox{{c0, c1, c2, c3}};
 }
 
-// Box-Muller on two 32-bit words: u1 in (0, 1], angle uniform in [-pi, pi).
-__device__ __forceinline__ void box_muller(uint32_t r0, uint32_t r1, float& z0, float& z1) {
-    const float u1 = fmaf(__uint2float_rn(r0), 2.3283064365386963e-10f, 1.1641532182693481e-10f);
-    const float rad = sqrtf(-2.0f * __logf(u1));
-    const float ang = __int2float_rn((int)r1) * 1.4629180792671596e-9f;   // pi / 2^31
-    float s, c;
-    __sincosf(ang, &s, &c);
-    z0 = rad * c;
-    z1 = rad * s;
+__device__ __forceinline__ float lg2_approx(float x) {
+    float y;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float sqrt_approx(float x) {
+    float y;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
 }
 
-struct StepParams {   // per (cell, t): 11 doubles
-    double mux, muy, mnx, mny, a00, a01, a10, a11, l00, l10, l11;
-};
+// Box-Muller on two 32-bit words: u1 in (0, 1] (>= 2^-33, never denormal), angle uniform in [-pi, pi).
+// MUFU-only transcendentals (lg2 / sqrt / sin / cos approximations, ~1e-6 relative): sampling noise, not parity.
+__device__ __forceinline__ void box_muller(uint32_t r0, uint32_t r1, float& z0, float& z1) {
+    const float u1 = fmaf(__uint2float_rn(r0), 2.3283064365386963e-10f, 1.1641532182693481e-10f);
+    const float rad = sqrt_approx(-1.3862943611198906f * lg2_approx(u1));    // sqrt(-2 ln u1)
+    const float ang = __int2float_rn((int)r1) * 1.4629180792671596e-9f;       // pi / 2^31
+    z0 = rad * __cosf(ang);
+    z1 = rad * __sinf(ang);
+}
 
+struct __align__(16) StepParams {   // per (cell, t): 11 doubles + pad -> six 16-byte shared-memory loads
+    double mux, muy, mnx, mny, a00, a01, a10, a11, l00, l10, l11, pad;
+};
+constexpr int SP_D = sizeof(StepParams) / sizeof(double);
+
+// TSH > 0: compile-time horizon (fully unrolled step loop, shift/mask index math); TSH = 0: runtime Tsh.
+template <int TSH, bool ZIN, bool ZOUT>
 __global__ void __launch_bounds__(RO_THREADS)
 rollout_kernel(const double* __restrict__ mean, const double* __restrict__ cov, const double* __restrict__ cross,
-               int Tm, const double* __restrict__ x0, int64_t n, int Tsh, uint32_t seed_lo, uint32_t seed_hi,
+               int Tm, const double* __restrict__ x0, int64_t n, int Tsh_rt, uint32_t seed_lo, uint32_t seed_hi,
                uint64_t sample_offset, const double* __restrict__ z_in, double* __restrict__ traj,
                double* __restrict__ z_out, uint8_t* __restrict__ status, double* __restrict__ x0_out) {
     extern __shared__ __align__(16) double smem[];
+    const int Tsh = TSH > 0 ? TSH : Tsh_rt;
     StepParams* sp = reinterpret_cast<StepParams*>(smem);                       // [Tsh]
-    const int par_d = (Tsh * 11 + 1) & ~1;
-    double2* stage = reinterpret_cast<double2*>(smem + par_d);                   // [128][stride2]
+    double2* stage = reinterpret_cast<double2*>(smem + Tsh * SP_D);              // [128][stride2]
     const int stride2 = Tsh | 1;
     const int tid = threadIdx.x;
     const int64_t c = blockIdx.y;
@@ -118,6 +131,7 @@ rollout_kernel(const double* __restrict__ mean, const double* __restrict__ cov, 
         const double r = k11 - p.l10 * p.l10;
         if (!(r > 0.0) && st == 0) st = CCMPC_ST_NO_TANGENT;
         p.l11 = sqrt(r);
+        p.pad = 0.0;
         sp[t] = p;
         if (status && blockIdx.x == 0 && st) status[c] = (uint8_t)st;
     }
@@ -129,43 +143,57 @@ rollout_kernel(const double* __restrict__ mean, const double* __restrict__ cov, 
     if (i < n) {
         double x = s_x0[0], y = s_x0[1];
         const uint64_t gi = sample_offset + (uint64_t)i;
-        const double2* zin2 = z_in ? reinterpret_cast<const double2*>(z_in) + (c * n + i) * Tsh : nullptr;
-        double2* zout2 = z_out ? reinterpret_cast<double2*>(z_out) + (c * n + i) * Tsh : nullptr;
-        float zb0 = 0.f, zb1 = 0.f;
-        for (int t = 0; t < Tsh; ++t) {
-            double zx, zy;
-            if (zin2) {
-                const double2 zz = zin2[t];
-                zx = zz.x; zy = zz.y;
-            } else {
-                if ((t & 1) == 0) {
-                    Philox r = philox4x32_10((uint32_t)gi, (uint32_t)(gi >> 32), (uint32_t)c, (uint32_t)(t >> 1),
-                                             seed_lo, seed_hi);
-                    float za, zb;
-                    box_muller(r.c[0], r.c[1], za, zb);
-                    box_muller(r.c[2], r.c[3], zb0, zb1);
-                    zx = (double)za; zy = (double)zb;
-                } else {
-                    zx = (double)zb0; zy = (double)zb1;
-                }
-            }
-            if (zout2) zout2[t] = make_double2(zx, zy);
+        const uint32_t gi_lo = (uint32_t)gi, gi_hi = (uint32_t)(gi >> 32);
+        const double2* zin2 = ZIN ? reinterpret_cast<const double2*>(z_in) + (c * n + i) * Tsh : nullptr;
+        double2* zout2 = ZOUT ? reinterpret_cast<double2*>(z_out) + (c * n + i) * Tsh : nullptr;
+        double2* my_stage = stage + tid * stride2;
+
+        auto step = [&](int t, double zx, double zy) {
+            if (ZOUT) zout2[t] = make_double2(zx, zy);
             const StepParams& p = sp[t];
             const double dx = x - p.mux, dy = y - p.muy;
             const double cmx = p.mnx + fma(dx, p.a00, dy * p.a01);
             const double cmy = p.mny + fma(dx, p.a10, dy * p.a11);
             x = cmx + zx * p.l00;
             y = cmy + fma(zx, p.l10, zy * p.l11);
-            stage[tid * stride2 + t] = make_double2(x, y);
+            my_stage[t] = make_double2(x, y);
+        };
+#pragma unroll
+        for (int t2 = 0; t2 < (TSH > 0 ? (TSH + 1) / 2 : (Tsh + 1) / 2); ++t2) {
+            const int t = 2 * t2;
+            if (ZIN) {
+                const double2 za = zin2[t];
+                step(t, za.x, za.y);
+                if (t + 1 < Tsh) {
+                    const double2 zb = zin2[t + 1];
+                    step(t + 1, zb.x, zb.y);
+                }
+            } else {
+                // one Philox block = 4 words = 2 Box-Muller pairs = the noise of steps t and t + 1
+                Philox r = philox4x32_10(gi_lo, gi_hi, (uint32_t)c, (uint32_t)t2, seed_lo, seed_hi);
+                float za, zb, zc, zd;
+                box_muller(r.c[0], r.c[1], za, zb);
+                box_muller(r.c[2], r.c[3], zc, zd);
+                step(t, (double)za, (double)zb);
+                if (t + 1 < Tsh) step(t + 1, (double)zc, (double)zd);
+            }
         }
     }
     __syncthreads();
     // contiguous store of the CTA's (rows, Tsh, 2) block
     double2* out2 = reinterpret_cast<double2*>(traj) + (c * n + i0) * Tsh;
-    const int total = rows * Tsh;
-    for (int e = tid; e < total; e += RO_THREADS) {
-        const int r = e / Tsh, t = e - r * Tsh;
-        __stcs(out2 + e, stage[r * stride2 + t]);
+    if (TSH > 0 && (RO_THREADS % TSH) == 0) {
+        constexpr int TT = TSH > 0 ? TSH : 1;
+        constexpr int RPP = RO_THREADS / TT;           // rows per pass
+        const int t = tid % TT, r0 = tid / TT;
+#pragma unroll 4
+        for (int r = r0; r < rows; r += RPP) __stcs(out2 + r * TT + t, stage[r * stride2 + t]);
+    } else {
+        const int total = rows * Tsh;
+        for (int e = tid; e < total; e += RO_THREADS) {
+            const int r = e / Tsh, t = e - r * Tsh;
+            __stcs(out2 + e, stage[r * stride2 + t]);
+        }
     }
 }
 
@@ -195,12 +223,24 @@ extern "C" int ccmpc_mc_rollout(const double* mean, const double* cov, const dou
         cudaError_t e = cudaMemsetAsync(status, 0, (size_t)C, st);
         if (e != cudaSuccess) { set_error("ccmpc_mc_rollout: memset: %s", cudaGetErrorString(e)); return CCMPC_E_LAUNCH; }
     }
-    const int par_d = (Tsh * 11 + 1) & ~1;
-    const size_t smem = (size_t)par_d * 8 + (size_t)RO_THREADS * (Tsh | 1) * 16;
+    const size_t smem = (size_t)Tsh * sizeof(StepParams) + (size_t)RO_THREADS * (Tsh | 1) * 16;
     dim3 grid((unsigned)((n + RO_THREADS - 1) / RO_THREADS), (unsigned)C);
-    rollout_kernel<<<grid, RO_THREADS, smem, st>>>(mean, cov, cross, Tm, x0, n, Tsh, (uint32_t)seed,
-                                                   (uint32_t)(seed >> 32), sample_offset, z, traj, z_out, status,
-                                                   x0_out);
+#define CCMPC_RO_LAUNCH(TSH, ZI, ZO)                                                                          \
+    rollout_kernel<TSH, ZI, ZO><<<grid, RO_THREADS, smem, st>>>(mean, cov, cross, Tm, x0, n, Tsh, (uint32_t)seed, \
+                                                                (uint32_t)(seed >> 32), sample_offset, z, traj,   \
+                                                                z_out, status, x0_out)
+#define CCMPC_RO_PICK(TSH)                                                                                    \
+    do {                                                                                                      \
+        if (z && z_out) CCMPC_RO_LAUNCH(TSH, true, true);                                                     \
+        else if (z) CCMPC_RO_LAUNCH(TSH, true, false);                                                        \
+        else if (z_out) CCMPC_RO_LAUNCH(TSH, false, true);                                                    \
+        else CCMPC_RO_LAUNCH(TSH, false, false);                                                              \
+    } while (0)
+    if (Tsh == 16) CCMPC_RO_PICK(16);
+    else if (Tsh == 8) CCMPC_RO_PICK(8);
+    else CCMPC_RO_PICK(0);
+#undef CCMPC_RO_PICK
+#undef CCMPC_RO_LAUNCH
     return check_launch("rollout_kernel");
 }
 
