@@ -88,7 +88,21 @@ __device__ __forceinline__ MvoeSpectrum mvoe_spectrum_iso(const Sym2& s1, double
     return sp;
 }
 
+// 1/sqrt(p) for p > 0 in the normal range: MUFU seed (2^-22) + two Newton steps (full fp64, ~1 ulp).
+// Non-positive / non-finite p yields NaN or inf, which the caller's convergence test rejects.
+__device__ __forceinline__ double rsqrt_newton(double p) {
+    double r;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(p));
+    double e = fma(-(p * r), r, 1.0);
+    r = fma(0.5 * r, e, r);
+    e = fma(-(p * r), r, 1.0);
+    r = fma(0.5 * r, e, r);
+    return r;
+}
+
 // Returns beta; iters = number of fixed-point evaluations (reference loop count).
+// One iterate is sqrt(a / b) with a = 2 + beta tr, b = tr + 2 beta dt, evaluated as a * rsqrt(a b):
+// no IEEE division / square-root slow paths in the dependent chain (~14 fp64 instructions per iteration).
 __device__ __forceinline__ double mvoe_beta(const MvoeSpectrum& sp, double tol, int maxiter, int accel,
                                             int& iters, int& status) {
     double beta = 1.0;
@@ -109,10 +123,12 @@ __device__ __forceinline__ double mvoe_beta(const MvoeSpectrum& sp, double tol, 
     bool converged = false;
     for (; it < maxiter;) {
         ++it;
-        double nb = sqrt(fma(beta, tr, 2.0) / fma(beta, dt2, tr));
+        const double a = fma(beta, tr, 2.0), b = fma(beta, dt2, tr);
+        const double nb = a * rsqrt_newton(a * b);
         converged = fabs(nb - beta) < tol;
         beta = nb;
         if (converged) break;
+        if (nb != nb) { it = maxiter; break; }      // NaN never converges: the reference spins to maxiter
     }
     iters = it;
     if (!converged && status == CCMPC_ST_OK) status = CCMPC_ST_NOT_CONVERGED;
@@ -172,6 +188,49 @@ __device__ __forceinline__ Tangent tangent_pick(double mux, double muy, const Sy
         if (t.dist1 < best) { best = t.dist1; t.idx = 1; }
     }
     t.d_star = t.idx == 0 ? t.d_plus : t.d_minus;
+    return t;
+}
+
+// choose_closest_tangent without the distances as outputs (makeconstraint.py:176-207): the two
+// candidates are compared through |n.a - d| only - dividing both by the same ||n|| > 0 is monotone, so
+// it can change the strict '<' scan only by rounding two numerators that are within a few ulp of each
+// other onto the same quotient; that case falls back to the divided form, keeping best_idx bit-exact.
+struct TangentStar {
+    double d_star;
+    int idx;     // -1: no tangent (n^T Sigma n <= 0)
+};
+
+__device__ __forceinline__ TangentStar tangent_star(double mux, double muy, const Sym2& S, double c, double m,
+                                                    double ax, double ay) {
+    TangentStar t;
+    const double n0 = -m;
+    double sx = fma(S.xx, n0, S.xy);
+    double sy = fma(S.xy, n0, S.yy);
+    double q = fma(n0, sx, sy);
+    if (!(q > 0.0)) {
+        t.idx = -1;
+        t.d_star = __longlong_as_double(0x7ff8000000000000LL);
+        return t;
+    }
+    const double proj = fma(n0, mux, muy);
+    const double half = c * sqrt(q);
+    const double d_plus = proj + half, d_minus = proj - half;
+    const double na = fma(n0, ax, ay);
+    const double e0 = fabs(na - d_plus), e1 = fabs(na - d_minus);
+    int idx;
+    if (fabs(e0 - e1) > 1e-14 * fmax(e0, e1)) {
+        idx = e1 < e0 ? 1 : 0;
+    } else {
+        const double nrm = sqrt(fma(m, m, 1.0));
+        const double dist0 = e0 / nrm, dist1 = e1 / nrm;
+        const double inf = __longlong_as_double(0x7ff0000000000000LL);
+        double best = inf;
+        idx = 0;
+        if (dist0 < best) { best = dist0; idx = 0; }
+        if (dist1 < best) { best = dist1; idx = 1; }
+    }
+    t.idx = idx;
+    t.d_star = idx == 0 ? d_plus : d_minus;
     return t;
 }
 

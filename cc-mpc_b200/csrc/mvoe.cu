@@ -101,9 +101,12 @@ sweep_kernel(const double* __restrict__ cov, const double* __restrict__ mu, cons
     const int tid = threadIdx.x;
     const int64_t ntiles = (M + FIT_THREADS - 1) / FIT_THREADS;
     const int64_t per_s = (int64_t)O * T * K;
+    const uint32_t per_s32 = (uint32_t)per_s;
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const int64_t base = tile * FIT_THREADS;
         const int cnt = (int)min((int64_t)FIT_THREADS, M - base);
+        const int64_t tile_s = base / per_s;                       // CTA-uniform 64-bit division, once per tile
+        const uint32_t tile_rem = (uint32_t)(base - tile_s * per_s);
         stage_in(cov + base * 3, s_a, cnt * 3, tid, FIT_THREADS);
         __syncthreads();
         Sym2 q{0.0, 0.0, 0.0};
@@ -119,13 +122,16 @@ sweep_kernel(const double* __restrict__ cov, const double* __restrict__ mu, cons
             double beta = mvoe_beta(sp, tol, maxiter, accel, iters, status);
             q = mvoe_q_iso(a, r2, beta);
             const double2 m2 = __ldg(reinterpret_cast<const double2*>(mu) + i);
-            const int64_t s = i / per_s;
-            const int t = (int)((i / K) % T);
-            const double2 r = __ldg(reinterpret_cast<const double2*>(ref) + (s * T + t));
+            // (scenario, timestep) of the cell: 32-bit arithmetic on the tile-local index
+            const uint32_t li = tile_rem + (uint32_t)tid;
+            const uint32_t ds = li / per_s32;
+            const uint32_t rem = li - ds * per_s32;
+            const int t = (int)((rem / (uint32_t)K) % (uint32_t)T);
+            const double2 r = __ldg(reinterpret_cast<const double2*>(ref) + ((tile_s + ds) * T + t));
             const double dy = r.y - m2.y;
             const double m = -(r.x - m2.x) / dy;          // v8ideal:923
             if (dy == 0.0 && status == 0) status = CCMPC_ST_DEGENERATE_SLOPE;
-            Tangent tg = tangent_pick(m2.x, m2.y, q, 1.0, m, r.x, r.y, -1);
+            TangentStar tg = tangent_star(m2.x, m2.y, q, 1.0, m, r.x, r.y);
             n0 = -m;
             d = tg.d_star;
             if (tg.idx < 0) {
@@ -264,7 +270,7 @@ __global__ void minkowski_kernel(const double* __restrict__ sums, const double* 
         const double dy = ry - my;
         const double m = -(rx - mx) / dy;
         if (dy == 0.0 && status == 0) status = CCMPC_ST_DEGENERATE_SLOPE;
-        Tangent tg = tangent_pick(mx, my, Q, 1.0, m, rx, ry, -1);
+        TangentStar tg = tangent_star(mx, my, Q, 1.0, m, rx, ry);
         const double n0 = -m, d = tg.d_star;
         int code = 0;
         double A0 = n0, A1 = 1.0, bb = d;
@@ -391,6 +397,7 @@ extern "C" int ccmpc_mvoe_halfplane_sweep(const double* cov, const double* mu, c
     const int64_t M = S * O * T * K;
     if (M == 0) return CCMPC_OK;
     CCMPC_REQUIRE(cov && mu && ref && q && nd && idx_side, "ccmpc_mvoe_halfplane_sweep: null pointer");
+    CCMPC_REQUIRE((int64_t)O * T * K < ((int64_t)1 << 31) - FIT_THREADS, "ccmpc_mvoe_halfplane_sweep: O*T*K too large");
     sweep_kernel<<<fit_grid(M), FIT_THREADS, 0, (cudaStream_t)stream>>>(cov, mu, ref, M, O, T, K, chi_scale,
                                                                         footprint_r2, tol, maxiter, accel, q, nd,
                                                                         idx_side, status);
