@@ -102,32 +102,56 @@ sweep_kernel(const double* __restrict__ cov, const double* __restrict__ mu, cons
     const int64_t ntiles = (M + FIT_THREADS - 1) / FIT_THREADS;
     const int64_t per_s = (int64_t)O * T * K;
     const uint32_t per_s32 = (uint32_t)per_s;
+    // the next tile's covariances travel in registers while the current tile is fitted
+    double2 pre0 = make_double2(0.0, 0.0), pre1 = pre0;
+    double pre_tail = 0.0;
+    auto fetch = [&](int64_t tile) {
+        if (tile >= ntiles) return;
+        const int64_t b = tile * FIT_THREADS;
+        const int n3 = (int)min((int64_t)FIT_THREADS, M - b) * 3;
+        const double2* g2 = reinterpret_cast<const double2*>(cov + b * 3);
+        if (tid < (n3 >> 1)) pre0 = __ldcs(g2 + tid);
+        if (tid + FIT_THREADS < (n3 >> 1)) pre1 = __ldcs(g2 + tid + FIT_THREADS);
+        if ((n3 & 1) && tid == 0) pre_tail = cov[b * 3 + n3 - 1];
+    };
+    fetch(blockIdx.x);
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const int64_t base = tile * FIT_THREADS;
         const int cnt = (int)min((int64_t)FIT_THREADS, M - base);
         const int64_t tile_s = base / per_s;                       // CTA-uniform 64-bit division, once per tile
         const uint32_t tile_rem = (uint32_t)(base - tile_s * per_s);
-        stage_in(cov + base * 3, s_a, cnt * 3, tid, FIT_THREADS);
+        {
+            const int n3 = cnt * 3;
+            double2* s2 = reinterpret_cast<double2*>(s_a);
+            if (tid < (n3 >> 1)) s2[tid] = pre0;
+            if (tid + FIT_THREADS < (n3 >> 1)) s2[tid + FIT_THREADS] = pre1;
+            if ((n3 & 1) && tid == 0) s_a[n3 - 1] = pre_tail;
+        }
+        // mean and reference point of this thread's cell: in flight during the fixed point
+        double2 m2 = make_double2(0.0, 0.0), r = m2;
+        if (tid < cnt) {
+            m2 = __ldcs(reinterpret_cast<const double2*>(mu) + (base + tid));
+            // (scenario, timestep) of the cell: 32-bit arithmetic on the tile-local index
+            const uint32_t li = tile_rem + (uint32_t)tid;
+            const uint32_t ds = li / per_s32;
+            const uint32_t rem = li - ds * per_s32;
+            const int t = (int)((rem / (uint32_t)K) % (uint32_t)T);
+            r = __ldg(reinterpret_cast<const double2*>(ref) + ((tile_s + ds) * T + t));
+        }
         __syncthreads();
+        Sym2 a{1.0, 0.0, 1.0};
+        if (tid < cnt) a = ld_sym3(s_a + tid * 3);
+        fetch(tile + gridDim.x);
         Sym2 q{0.0, 0.0, 0.0};
         double n0 = 0.0, d = 0.0;
         int status = 0, code = 0;
         if (tid < cnt) {
-            const int64_t i = base + tid;
-            Sym2 a = ld_sym3(s_a + tid * 3);
             a.xx *= chi_scale; a.xy *= chi_scale; a.yy *= chi_scale;
             MvoeSpectrum sp = mvoe_spectrum_iso(a, r2);
             status = sp.status;
             int iters;
             double beta = mvoe_beta(sp, tol, maxiter, accel, iters, status);
             q = mvoe_q_iso(a, r2, beta);
-            const double2 m2 = __ldg(reinterpret_cast<const double2*>(mu) + i);
-            // (scenario, timestep) of the cell: 32-bit arithmetic on the tile-local index
-            const uint32_t li = tile_rem + (uint32_t)tid;
-            const uint32_t ds = li / per_s32;
-            const uint32_t rem = li - ds * per_s32;
-            const int t = (int)((rem / (uint32_t)K) % (uint32_t)T);
-            const double2 r = __ldg(reinterpret_cast<const double2*>(ref) + ((tile_s + ds) * T + t));
             const double dy = r.y - m2.y;
             const double m = -(r.x - m2.x) / dy;          // v8ideal:923
             if (dy == 0.0 && status == 0) status = CCMPC_ST_DEGENERATE_SLOPE;
@@ -363,7 +387,7 @@ __global__ void affine_kernel(const double* __restrict__ sums, const double* __r
 
 static int fit_grid(int64_t M) {
     int64_t tiles = (M + FIT_THREADS - 1) / FIT_THREADS;
-    const int64_t cap = 148 * 8;   // 148 SMs x 8 resident 256-thread CTAs
+    const int64_t cap = 148 * 4;   // 148 SMs x 4 resident 256-thread CTAs (58 registers)
     return (int)(tiles < cap ? (tiles > 0 ? tiles : 1) : cap);
 }
 
