@@ -30,6 +30,7 @@ if ROOT not in sys.path:
 C3 = dict(O=8, K=4, T=16, n_per_cell=250_000, seed=3)            # 1M samples / obstacle, ph16
 C4 = dict(S=4096, O=8, T=16, K=25, seed=4)                      # batched MVOE sweep
 C2 = dict(O=4, K=25, T=8, N=5000, seed=2)                       # one MPC step
+C5 = dict(O=8, K=4, T=16, N=20_000, steps=200, seed=5)          # closed-loop replay
 METRIC = "mc_traj_steps_per_sec"
 UNIT = "traj-steps/s"
 BYTES_PER_TRAJ_STEP_SUMS = 16        # sample_sums: x, y fp64 read once
@@ -42,6 +43,16 @@ def _peaks():
             return float(json.load(f)["hbm_gbs"]), "measured"
     except Exception:
         return 6650.0, "fallback"
+
+
+def _traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` at the c3 shape, from the committed
+    ncu --set full capture (profiles/traffic.json names the .txt summary each figure comes from)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return json.load(f)[kernel]["bytes_per_launch"]
+    except Exception:
+        return None
 
 
 class ClockSampler:
@@ -110,42 +121,47 @@ def _cpu_mc_cell(args):
     return n * T
 
 
-def cpu_mc_throughput(n_per_cell, T, procs, cells):
+def cpu_mc_throughput(n_per_cell, T, procs, cells, pool=None):
     """traj-steps/s of the oracle over `cells` cells using `procs` worker processes."""
     jobs = [(1000 + i, n_per_cell, T) for i in range(cells)]
     t0 = time.perf_counter()
     if procs <= 1:
         done = sum(_cpu_mc_cell(j) for j in jobs)
+    elif pool is not None:
+        done = sum(pool.map(_cpu_mc_cell, jobs, chunksize=1))
     else:
         import multiprocessing as mp
-        with mp.get_context("fork").Pool(procs) as pool:
-            done = sum(pool.map(_cpu_mc_cell, jobs))
+        with mp.get_context("fork").Pool(procs) as p:
+            done = sum(p.map(_cpu_mc_cell, jobs, chunksize=1))
     dt = time.perf_counter() - t0
     return done / dt, dt
 
 
 def run_reference(args):
     """--impl reference: the reference's CPU path (oracle port; the reference is pure Python and its
-    v8ideal module does not import without carla/cvxpy) on all host cores."""
+    v8ideal module does not import without carla/cvxpy) on all host cores: one worker
+    process per core (the reference itself is single-threaded), each step = one c3-shaped cell slice per
+    worker through predict_ideal's loop body + A9 counts + save_moments."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
+    import multiprocessing as mp
+    os.environ.setdefault("OMP_NUM_THREADS", "1")       # one core per worker, no BLAS oversubscription
     cores = os.cpu_count() or 1
-    n = 20_000
+    n = 100_000
     T = C3["T"]
-    for _ in range(min(args.warmup, 1)):
-        cpu_mc_throughput(n, T, cores, cores)
-    vals, secs = [], []
     steps = max(1, min(args.steps, 5))
-    for _ in range(steps):
-        v, dt = cpu_mc_throughput(n, T, cores, cores)
-        vals.append(v)
-        secs.append(dt)
-    value = float(np.sum([n * T * cores] * steps) / np.sum(secs))
-    sample = f"{cores} cells x {n} samples x ph{T} per step (c3 shape, 1/{C3['n_per_cell'] // n} of a cell each)"
+    warm = min(args.warmup, 1)
+    with mp.get_context("fork").Pool(cores) as pool:
+        for _ in range(warm):
+            cpu_mc_throughput(n, T, cores, cores, pool)
+        secs = [cpu_mc_throughput(n, T, cores, cores, pool)[1] for _ in range(steps)]
+    value = float(n * T * cores * steps / np.sum(secs))
+    sample = (f"{cores} cells x {n} samples x ph{T} per step, one worker process per core "
+              f"(c3 shape, {n / C3['n_per_cell']:.2f} of a cell each)")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
-        "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * float(np.mean(secs)), "higher_is_better": True,
+        "warmup": warm, "ms_per_step": 1e3 * float(np.mean(secs)), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": _config(args.gpus),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
@@ -276,8 +292,13 @@ def run_ours(args):
     assert int(sums[0, 0].item()) == n * world, "sample count mismatch after all-reduce"
     assert counts.min() >= 0 and counts[:, :T].max() <= n * world
 
+    also = {}
+    if not args.skip_also:
+        also = bench_also(torch, ops, midlevel, synth, dev, args, world, rank, dist)
+
     if rank != 0:
         if world > 1:
+            dist.barrier()
             dist.destroy_process_group()
         return 0
 
@@ -287,14 +308,11 @@ def run_ours(args):
     ach = C * n * T * (BYTES_PER_TRAJ_STEP_SUMS if dom == "sample_sums_kernel" else BYTES_PER_TRAJ_STEP_ROLLOUT) \
         / (dom_ms * 1e-3) / 1e9
     roofline = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
-                "frac": ach / peak, "traffic": None,
+                "frac": ach / peak, "traffic": _traffic(dom) if n == C3["n_per_cell"] else None,
+                "algorithmic_bytes": C * n * T * 16,
                 "kernels_ms": {"rollout_kernel": roll_ms, "sample_sums(scan+sums+finalize)": sums_ms},
                 "other_kernel": {"name": "rollout_kernel" if dom == "sample_sums_kernel" else "sample_sums_kernel",
                                  "achieved": C * n * T * 16 / (min(sums_ms, roll_ms) * 1e-3) / 1e9}}
-
-    also = {}
-    if not args.skip_also:
-        also = bench_also(torch, ops, midlevel, synth, dev, args)
 
     cpu = None
     if not args.skip_cpu:
@@ -314,12 +332,15 @@ def run_ours(args):
     }
     print(json.dumps(line))
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
     return 0
 
 
-def bench_also(torch, ops, midlevel, synth, dev, args):
-    """The two other terms of BASELINE.json's metric, measured on rank 0's GPU."""
+def bench_also(torch, ops, midlevel, synth, dev, args, world=1, rank=0, dist=None):
+    """The two other terms of BASELINE.json's metric.  The c4 MVOE sweep runs on every rank (scenario batches
+    shard across GPUs with no exchange: each rank fits its own S = 4096 scenarios, weak scaling; time = max
+    over ranks); the single-GPU latency configs c2 / c5 run on rank 0 only."""
     out = {}
     ev = lambda: torch.cuda.Event(enable_timing=True)
     peak, _ = _peaks()
@@ -350,15 +371,24 @@ def bench_also(torch, ops, midlevel, synth, dev, args):
         b.record()
         torch.cuda.synchronize()
         ms = a.elapsed_time(b) / reps
-        M = S * O * T * K
+        if world > 1:
+            mt = torch.tensor([ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(mt, op=dist.ReduceOp.MAX)
+            ms = float(mt.item())
+        M = S * O * T * K * world
         bytes_per = 24 + 16 + 24 + 24 + 1 + 1
         out["mvoe_sweep_accel" if accel else "mvoe_sweep"] = {
             "metric": "mvoe_fits_per_sec", "value": M / (ms * 1e-3), "unit": "fits/s", "ms": ms, "fits": M,
-            "workload": f"c4: S={S} x O={O} x T={T} x K={K} footprint fit + tangent half-plane",
-            "roofline": {"bound": "hbm", "achieved": M * bytes_per / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
-                         "frac": M * bytes_per / (ms * 1e-3) / 1e9 / peak, "bytes_per_fit": bytes_per}}
+            "workload": f"c4: S={S} x O={O} x T={T} x K={K} footprint fit + tangent half-plane per GPU "
+                        f"(scenarios sharded x{world}, no exchange)", "n_gpus": world,
+            "iterate": "float32 warm start + fp64 map" if accel else "reference sequence from beta = 1",
+            "roofline": {"bound": "hbm", "achieved": M / world * bytes_per / (ms * 1e-3) / 1e9, "peak": peak,
+                         "unit": "GB/s", "frac": M / world * bytes_per / (ms * 1e-3) / 1e9 / peak,
+                         "bytes_per_fit": bytes_per, "per": "GPU"}}
     assert int(bufs[3].max().item()) == 0, "MVOE sweep reported a failed cell"
     del cov, mu, ref, bufs
+    if rank != 0:
+        return out
     # ---- c2: the full constraint build of one MPC step, host samples -> host rows --------------
     sc = synth.make_scene(C2["seed"], C2["O"], C2["K"], C2["T"])
     z, pos = synth.sample_scene(sc, C2["N"], C2["seed"])
@@ -389,6 +419,38 @@ def bench_also(torch, ops, midlevel, synth, dev, args):
         "workload": "c2: O=4, K=25, ph8, np5000: sums+counts -> Minkowski half-planes (2800 pairs, 5600 fits) -> "
                     "L4 polytopes -> violation counts; L2 flushed between iterations",
         "rows": int(step.C * step.P), "launches_per_step": step.launches_per_step}
+    del step
+    # ---- c5: receding-horizon replay, 200 MPC steps x 8 obstacles, ph16, np20000 (affine builder) ----
+    sc = synth.make_scene(C5["seed"], C5["O"], C5["K"], C5["T"])
+    z, pos = synth.sample_scene(sc, C5["N"], C5["seed"])
+    plan = midlevel.StepPlan.from_samples(z, pos, sc.pos_last, C5["K"], prediction_horizon=C5["T"], device=dev,
+                                          builder="affine")
+    hs = plan.host_samples.numpy()
+    ref0 = np.asarray(sc.ref_traj, dtype=np.float64)
+    slab = max(1, plan.N // 16)
+    lat = []
+    for i in range(10 + C5["steps"]):
+        # the scene advances: a rotating 1/16 of the prediction tensor and the reference move (untimed host work)
+        lo = (i % 16) * slab
+        hs[lo:lo + slab] += 0.01
+        ref_i = ref0 + 0.02 * i
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        res = plan.run(ref_traj=ref_i)
+        dt = (time.perf_counter() - t0) * 1e3
+        if i >= 10:
+            lat.append(dt)
+    assert not res["aff_status"].any()
+    out["replay_c5"] = {
+        "metric": "mpc_step_latency_ms", "unit": "ms", "higher_is_better": False, "steps": C5["steps"],
+        "p50_host_to_host": float(np.percentile(lat, 50)), "p95_host_to_host": float(np.percentile(lat, 95)),
+        "mean_host_to_host": float(np.mean(lat)),
+        "h2d_bytes_per_step": int(plan.host_samples.numel() * 8 + plan.host_ref.numel() * 8),
+        "d2h_bytes_per_step": int(plan.host_arena.numel()),
+        "workload": f"c5: {C5['steps']} receding-horizon MPC steps, O={C5['O']} x K={C5['K']} modes, ph{C5['T']}, "
+                    f"np{C5['N']}: pinned fp64 predictions H2D -> yaws -> sums/counts -> affine half-planes -> L4 -> "
+                    f"D2H (one CUDA graph per step); 41 MB sample tensor per step exceeds nothing but is re-sent "
+                    f"every step", "rows": int(plan.C * plan.T), "launches_per_step": plan.launches_per_step}
     return out
 
 

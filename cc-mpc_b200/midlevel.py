@@ -570,13 +570,23 @@ class StepPlan:
                ("mean", "f8", ("C", "T", 2)), ("cov", "f8", ("C", "T", 2, 2)), ("At", "f8", ("C", "T", 4, 2)),
                ("b0", "f8", ("C", "T", 4)), ("yaw_mean", "f8", ("C", "T")), ("yaw_var", "f8", ("C", "T")),
                ("counts", "i8", ("C", "T1")), ("viol", "i8", ("C", "P")), ("idx_side", "i1", ("C", "P")),
-               ("status", "u1", ("C", "P")))
+               ("status", "u1", ("C", "P")),
+               # affine (receding-horizon) builder, v8ideal:1476-1515
+               ("aff_nd", "f8", ("C", "T", 3)), ("aff_offset_rhs", "f8", ("C", "T", 2)),
+               ("aff_cov", "f8", ("C", "T", 3)), ("aff_idx_side", "i1", ("C", "T")), ("aff_status", "u1", ("C", "T")))
+    _MINK_ONLY = ("nd", "ab", "prob_lower", "viol", "idx_side", "status")
+    _AFF_ONLY = ("aff_nd", "aff_offset_rhs", "aff_cov", "aff_idx_side", "aff_status")
     _TORCH = {"f8": torch.float64, "i8": torch.int64, "i1": torch.int8, "u1": torch.uint8}
     _NP = {"f8": np.float64, "i8": np.int64, "i1": np.int8, "u1": np.uint8}
 
     def __init__(self, offsets_host, cell_obstacle, cell_mode, n_states, pos_last_cell, T: int,
                  prediction_horizon: int, eps_ura=None, device=None, bbox=BBOX_DEFAULT, R: float = ops.R_EV_OV,
-                 target_p: float = ops.TARGET_P, accel: bool = False, use_graph: bool = True):
+                 target_p: float = ops.TARGET_P, accel: bool = False, use_graph: bool = True,
+                 builder: str = "minkowski"):
+        if builder not in ("minkowski", "affine", "both"):
+            raise ValueError("builder must be 'minkowski' (shrinking horizon, v8ideal:881-947), "
+                             "'affine' (receding horizon, v8ideal:1476-1515) or 'both'")
+        self.builder = builder
         self.device = _device(device)
         self.offsets_host = np.asarray(offsets_host, dtype=np.int64)
         self.cell_obstacle, self.cell_mode = np.asarray(cell_obstacle), np.asarray(cell_mode)
@@ -605,6 +615,8 @@ class StepPlan:
         dims = {"C": self.C, "P": self.P, "T": self.T, "T1": self.T + 1}
         off, self._layout = 0, {}
         for name, ty, shp in self._FIELDS:
+            if (builder == "affine" and name in self._MINK_ONLY) or (builder == "minkowski" and name in self._AFF_ONLY):
+                continue
             shape = tuple(dims.get(s, s) for s in shp)
             nbytes = int(np.prod(shape)) * np.dtype(self._NP[ty]).itemsize
             self._layout[name] = (off, nbytes, ty, shape)
@@ -618,7 +630,11 @@ class StepPlan:
                          for n, (o, b, ty, shape) in self._layout.items()}
         self._mom = dict(mean=self.out["mean"], cov=self.out["cov"], cross=None, counts=self.out["counts"],
                          yaw_mean=self.out["yaw_mean"], yaw_var=self.out["yaw_var"])
-        self._mink = {k: self.out[k] for k in ("nd", "ab", "idx_side", "prob_lower", "status")}
+        self._mink = ({k: self.out[k] for k in ("nd", "ab", "idx_side", "prob_lower", "status")}
+                      if builder != "affine" else None)
+        self._aff = (dict(nd=self.out["aff_nd"], offset_rhs=self.out["aff_offset_rhs"],
+                          idx_side=self.out["aff_idx_side"], mean=self.out["mean"], cov=self.out["aff_cov"],
+                          status=self.out["aff_status"]) if builder != "minkowski" else None)
         self._ego_is_ref = True
         self._graph_full = self._graph_dev = None
         self.launches_per_step = None
@@ -658,11 +674,17 @@ class StepPlan:
         ops.sample_sums(self.samples, self.offsets, self.pivot, ego=self.ref, yaws=self.yaws, R=self.R,
                         workspace=self.ws, out=self.sums)
         ops.moments_from_sums(self.sums, self.pivot, out=self._mom)
-        ops.minkowski_halfplanes(self.sums, self.pivot, self.ref, self.eps_cell, self.prediction_horizon, R=self.R,
-                                 target_p=self.target_p, accel=self.accel, out=self._mink)
+        if self._mink is not None:
+            ops.minkowski_halfplanes(self.sums, self.pivot, self.ref, self.eps_cell, self.prediction_horizon,
+                                     R=self.R, target_p=self.target_p, accel=self.accel, out=self._mink)
+        if self._aff is not None:
+            ops.affine_halfplanes(self.sums, self.pivot, self.ref, self.eps_cell, self.prediction_horizon, R=self.R,
+                                  out=self._aff)
         ops.l4_outer(self.samples, self.yaws, self.offsets, self.out["yaw_mean"], lw_cell=self.lw_cell,
                      out=(self.out["At"], self.out["b0"]))
-        ops.violation_counts(self.samples, self.offsets, self.out["nd"], self.out["idx_side"], out=self.out["viol"])
+        if self._mink is not None:
+            ops.violation_counts(self.samples, self.offsets, self.out["nd"], self.out["idx_side"],
+                                 out=self.out["viol"])
 
     def _enqueue_full(self):
         self.samples.copy_(self.host_samples, non_blocking=True)

@@ -439,3 +439,55 @@ def test_episode_cost_matches_oracle(dev):
         assert c == pytest.approx(rc, rel=1e-13) and cu == pytest.approx(rcu, rel=1e-13)
     with pytest.raises(UnboundLocalError):
         cost.cost_final([np.zeros(4)], [np.zeros(2)])
+
+
+# --------------------------------------------------------- one MPC step as a CUDA graph
+@pytest.mark.parametrize("builder", ["minkowski", "affine", "both"])
+def test_step_plan_graph_matches_oracle_and_eager(dev, builder):
+    """StepPlan (H2D -> yaws -> sums/counts -> moments -> half-planes -> L4 -> D2H in one CUDA graph) against
+    the oracle loops (v8ideal:881-947 / :1476-1515 / :694-736) and against its own eager launch sequence,
+    replayed on two different sample sets (the graph must not bake inputs in)."""
+    from ccmpc_b200 import midlevel
+    from oracle import restate, synth
+    O, K, T, N = 2, 3, 8, 700
+    sc = synth.make_scene(21, O, K, T)
+    z, pos = synth.sample_scene(sc, N, 21)
+    plan = midlevel.StepPlan.from_samples(z, pos, sc.pos_last, K, prediction_horizon=T, device=dev, builder=builder)
+    eager = midlevel.StepPlan.from_samples(z, pos, sc.pos_last, K, prediction_horizon=T, device=dev,
+                                           builder=builder, use_graph=False)
+    eps = restate.eps_allocation(plan.n_states)
+    for rep in range(2):
+        hs = plan.host_samples.numpy().copy()
+        if rep == 1:                                  # second replay: shifted samples, shifted reference
+            hs = (hs + np.asarray([0.37, -0.21])).copy()
+        ref_traj = sc.ref_traj + (0.0 if rep == 0 else 0.15)
+        res = {k: v.copy() for k, v in plan.run(pos_host=hs, ref_traj=ref_traj).items()}
+        res_e = eager.run(pos_host=hs, ref_traj=ref_traj)
+        for k in res:
+            np.testing.assert_array_equal(res[k], res_e[k], err_msg=f"graph != eager for {k}")
+        for c in range(plan.C):
+            cell = hs[plan.offsets_host[c]:plan.offsets_host[c + 1]]
+            e = eps[plan.cell_obstacle[c], plan.cell_mode[c]]
+            if builder in ("minkowski", "both"):
+                ref = restate.minkowski_cell(cell, ref_traj, e, T)
+                np.testing.assert_array_equal(res["idx_side"][c] & 1, ref["idx"])
+                np.testing.assert_array_equal(np.where(res["idx_side"][c] & 2, -1, 1), ref["side"])
+                np.testing.assert_allclose(res["nd"][c][:, 2], ref["d"], rtol=1e-7)
+                np.testing.assert_allclose(res["ab"][c][:, :2], ref["A"], rtol=1e-7)
+                viol = restate.violation_counts(cell, res["nd"][c][:, :2], res["nd"][c][:, 2],
+                                                np.where(res["idx_side"][c] & 2, -1, 1),
+                                                [t for t in range(T) for _ in range(t)])
+                np.testing.assert_array_equal(res["viol"][c], viol)
+            if builder in ("affine", "both"):
+                ref = restate.affine_cell(cell, ref_traj, e, T)
+                np.testing.assert_array_equal(res["aff_idx_side"][c] & 1, ref["idx"])
+                np.testing.assert_array_equal(np.where(res["aff_idx_side"][c] & 2, -1, 1), ref["side"])
+                np.testing.assert_allclose(res["aff_nd"][c][:, 2], ref["d"], rtol=1e-7)
+                np.testing.assert_allclose(res["aff_offset_rhs"][c][:, 1], ref["rhs"], rtol=1e-7)
+            coll, any_, _, _ = restate.collision_counts(cell, ref_traj)
+            np.testing.assert_array_equal(res["counts"][c][:T], coll)
+            assert res["counts"][c][T] == any_
+            yaws = restate.yaws_from_positions(cell, sc.pos_last[plan.cell_obstacle[c]])
+            At, b0, _ = restate.l4_cell(cell, yaws)
+            np.testing.assert_allclose(res["At"][c], At, atol=1e-10)
+            np.testing.assert_allclose(res["b0"][c], b0, rtol=1e-10)
