@@ -37,6 +37,9 @@ SIGNATURES = {
     "ccmpc_mc_rollout": (c_int, [_P, _P, _P, c_int, _P, c_int64, c_int64, c_int, c_uint64, c_uint64, _P, _P, _P, _P, _P,
                                   _P]),
     "ccmpc_yaws_from_positions": (c_int, [_P, _P, c_int64, c_int64, c_int, _P, _P, _P]),
+    "ccmpc_group_workspace_bytes": (c_size_t, [c_int64, c_int64]),
+    "ccmpc_group_by_mode": (c_int, [_P, _P, _P, _P, c_int64, c_int64, c_int, c_int, c_double, c_double, c_double,
+                                     _P, _P, _P, _P, _P, _P, _P, _P, _P, c_size_t, _P]),
     "ccmpc_episode_cost": (c_int, [_P, _P, _P, c_int64, c_int, c_double, c_double, _P, _P, _P]),
     "ccmpc_philox4x32": (c_int, [_P, _P, c_int64, _P, _P]),
 }

@@ -326,6 +326,44 @@ def l4_outer(samples, yaws, offsets, yaw_mean, lw=(3.7, 1.79), lw_cell=None, out
     return At, b0
 
 
+def group_by_mode(predictions, z, latent_pmf, minpos=(0.0, 0.0), filter_pmf: float = 0.1, workspace=None,
+                  out: Optional[dict] = None):
+    """A2 on the device (v8ideal:486-494 + ovehicle.py:55-113).  ``predictions`` [V,N,T,2] float32 (minpos is
+    added after the upcast) or float64 (minpos already added), ``z`` [V,N] int32, ``latent_pmf`` [V,S] float64.
+    -> dict(samples [V*N,T,2] f64 grouped, offsets [V*S+1] i64 (cell = v*S + j), perm [V,N] i64,
+            n_states [V] i32, cell_latent [V*S] i32, cell_pmf [V*S], init_center [V*S,2], status [V] u8)."""
+    lib = _lib.load()
+    if predictions.dtype not in (torch.float32, F64):
+        raise TypeError("predictions must be float32 or float64")
+    _chk(predictions, predictions.dtype, "predictions", (2,))
+    _chk(z, torch.int32, "z"); _chk(latent_pmf, F64, "latent_pmf")
+    V, N, T = predictions.shape[0], predictions.shape[1], predictions.shape[2]
+    S = latent_pmf.shape[1]
+    if tuple(z.shape) != (V, N) or latent_pmf.shape[0] != V:
+        raise ValueError("z must be [V,N] and latent_pmf [V,S]")
+    dev = predictions.device
+    if out is None:
+        out = dict(samples=torch.empty((V * N, T, 2), dtype=F64, device=dev),
+                   offsets=torch.empty(V * S + 1, dtype=I64, device=dev),
+                   perm=torch.empty((V, N), dtype=I64, device=dev),
+                   n_states=torch.empty(V, dtype=torch.int32, device=dev),
+                   cell_latent=torch.empty(V * S, dtype=torch.int32, device=dev),
+                   cell_pmf=torch.empty(V * S, dtype=F64, device=dev),
+                   init_center=torch.empty((V * S, 2), dtype=F64, device=dev),
+                   status=torch.empty(V, dtype=U8, device=dev))
+    need = int(lib.ccmpc_group_workspace_bytes(V, N))
+    if workspace is None:
+        workspace = torch.empty(need, dtype=U8, device=dev)
+    f32 = predictions.dtype == torch.float32
+    _lib.check(lib.ccmpc_group_by_mode(_p(predictions) if f32 else None, None if f32 else _p(predictions), _p(z),
+                                       _p(latent_pmf), V, N, T, S, float(minpos[0]), float(minpos[1]),
+                                       float(filter_pmf), _p(out["samples"]), _p(out["offsets"]), _p(out["perm"]),
+                                       _p(out["n_states"]), _p(out.get("cell_latent")), _p(out.get("cell_pmf")),
+                                       _p(out.get("init_center")), _p(out.get("status")), _p(workspace),
+                                       workspace.numel(), _stream()), "ccmpc_group_by_mode")
+    return out
+
+
 def yaws_from_positions(samples, offsets, pos_last, out=None):
     """midlevel/ovehicle.py:72-76 on device: samples [N,T,2], offsets [C+1], pos_last [C,2] -> yaws [N,T]."""
     lib = _lib.load()

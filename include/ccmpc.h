@@ -227,6 +227,32 @@ int ccmpc_yaws_from_positions(const double* samples, const int64_t* offsets, int
                               int T, const double* pos_last, double* yaws, void* stream);
 
 /* ---------------------------------------------------------------------------
+ * A2  mode grouping on the device.  Replaces the per-sample Python append loop of
+ * v8ideal:486-494 (predictions + minpos -> float64, bucket by latent z in sample
+ * order) and OVehicle.from_trajectron (midlevel/ovehicle.py:55-113): keep latents
+ * with pmf > filter_pmf (ascending); centre_j = mean final position of latent j's own
+ * samples; every other latent (ascending) sends each sample to the nearest centre
+ * (distance_matrix + argmin, first minimum), appended after the cluster's rows;
+ * pmf_j = N_j / N.  Row order = stable sort by (cluster, origin latent).
+ *   exactly one of pred32 [V,N,T,2] float32 (Trajectron++ output, prediction.py:104;
+ *   minpos is added after the upcast as at v8ideal:486) / pred64 [V,N,T,2] float64
+ *   (minpos already added; minpos_* ignored); z [V,N] int32; latent_pmf [V,S], S <= 32.
+ *   out: samples [V*N,T,2] float64 grouped; offsets [V*S+1] int64 with cell = v*S + j
+ *   (cells j >= K_v are empty); perm [V,N] int64 = source sample of every grouped row
+ *   (vehicle-local); n_states [V] int32 = K_v; nullable: cell_latent [V*S] int32 (-1
+ *   unused), cell_pmf [V*S], init_center [V*S,2], status [V] uint8 (2: no latent above
+ *   filter_pmf - the reference fails in argmin over an empty centre list).
+ *   workspace: ccmpc_group_workspace_bytes(V, N).
+ */
+size_t ccmpc_group_workspace_bytes(int64_t V, int64_t N);
+int ccmpc_group_by_mode(const float* pred32, const double* pred64, const int32_t* z,
+                        const double* latent_pmf, int64_t V, int64_t N, int T, int S,
+                        double minpos_x, double minpos_y, double filter_pmf,
+                        double* samples, int64_t* offsets, int64_t* perm, int32_t* n_states,
+                        int32_t* cell_latent, double* cell_pmf, double* init_center, uint8_t* status,
+                        void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------
  * K1  Monte Carlo rollout.  Replaces MidlevelAgent.predict_ideal's loop body
  * (v8ideal:2662-2709) for C cells x n samples: per step t < Tsh
  *   A = C_{t+1,t} Sigma_t^-1 ; cond_cov = Sigma_{t+1} - A C^T ; L = chol(cond_cov)

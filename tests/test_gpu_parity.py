@@ -491,3 +491,56 @@ def test_step_plan_graph_matches_oracle_and_eager(dev, builder):
             At, b0, _ = restate.l4_cell(cell, yaws)
             np.testing.assert_allclose(res["At"][c], At, atol=1e-10)
             np.testing.assert_allclose(res["b0"][c], b0, rtol=1e-10)
+
+
+# --------------------------------------------------------- A2: mode grouping on the device
+def _group_inputs(rng, V, N, T, S, sparse):
+    """Per-vehicle latent probabilities with a few dominant modes (ovehicle.py:58 keeps pmf > 0.1)."""
+    pmf = np.zeros((V, S))
+    z = np.zeros((V, N), np.int32)
+    for v in range(V):
+        w = rng.dirichlet(np.full(S, 0.08 if sparse else 1.0))
+        pmf[v] = w
+        z[v] = rng.choice(S, size=N, p=w)
+    centres = rng.uniform(-30, 30, size=(V, S, 1, 2))
+    step = rng.normal(size=(V, S, 1, 2)) * 2
+    pred = np.zeros((V, N, T, 2), np.float32)
+    for v in range(V):
+        base = centres[v][z[v]] + np.arange(1, T + 1)[None, :, None] * step[v][z[v]]
+        pred[v] = (base + rng.normal(size=(N, T, 2)) * 0.7).astype(np.float32)
+    return pred, z, pmf
+
+
+@pytest.mark.parametrize("V,N,T,S,sparse,f32", [(3, 5000, 8, 25, True, True), (2, 1237, 16, 25, True, False),
+                                                (1, 40, 3, 7, False, True), (2, 3000, 8, 25, False, True)])
+def test_group_by_mode_matches_oracle(dev, V, N, T, S, sparse, f32):
+    """ccmpc_group_by_mode against the restated bucket + fold of v8ideal:486-494 / ovehicle.py:55-113:
+    identical row order (perm), cell sizes, retained latents; centres and pmf to rounding."""
+    from ccmpc_b200 import ops
+    from oracle import restate
+    rng = np.random.default_rng(1000 + N)
+    pred, z, pmf = _group_inputs(rng, V, N, T, S, sparse)
+    minpos = np.asarray([151.25, -93.5])
+    pred64 = pred.astype(np.float64) + minpos                    # v8ideal:486
+    src = T_(pred, dev, torch.float32) if f32 else T_(pred64, dev)
+    out = ops.group_by_mode(src, T_(z, dev, torch.int32), T_(pmf, dev), minpos=minpos if f32 else (0, 0))
+    h = {k: v.cpu().numpy() for k, v in out.items()}
+    for v in range(V):
+        keep = np.argwhere(pmf[v] > 0.1).ravel()
+        assert h["n_states"][v] == keep.size
+        if keep.size == 0:
+            assert h["status"][v] == 2
+            continue
+        pos_l, yaw_l, centers, pmf_o, mem_l = restate.group_by_mode(pred64[v], z[v], pmf[v], np.zeros(2), T)
+        for j in range(S):
+            c = v * S + j
+            b, e = h["offsets"][c], h["offsets"][c + 1]
+            if j >= keep.size:
+                assert b == e and h["cell_latent"][c] == -1
+                continue
+            assert h["cell_latent"][c] == keep[j]
+            np.testing.assert_array_equal(h["perm"][v][b - v * N:e - v * N], mem_l[j])       # same row order
+            np.testing.assert_array_equal(h["samples"][b:e], pos_l[j])                         # bit-exact rows
+            np.testing.assert_allclose(h["init_center"][c], centers[j], rtol=1e-13)
+            np.testing.assert_allclose(h["cell_pmf"][c], pmf_o[j], rtol=1e-15)
+    assert h["offsets"][-1] == V * N
