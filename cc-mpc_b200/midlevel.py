@@ -574,15 +574,17 @@ class StepPlan:
                # affine (receding-horizon) builder, v8ideal:1476-1515
                ("aff_nd", "f8", ("C", "T", 3)), ("aff_offset_rhs", "f8", ("C", "T", 2)),
                ("aff_cov", "f8", ("C", "T", 3)), ("aff_idx_side", "i1", ("C", "T")), ("aff_status", "u1", ("C", "T")))
+    _INGEST_FIELDS = (("g_offsets", "i8", ("C1",)), ("g_cell_pmf", "f8", ("C",)), ("g_init_center", "f8", ("C", 2)),
+                      ("g_n_states", "i4", ("V",)), ("g_cell_latent", "i4", ("C",)), ("g_status", "u1", ("V",)))
     _MINK_ONLY = ("nd", "ab", "prob_lower", "viol", "idx_side", "status")
     _AFF_ONLY = ("aff_nd", "aff_offset_rhs", "aff_cov", "aff_idx_side", "aff_status")
-    _TORCH = {"f8": torch.float64, "i8": torch.int64, "i1": torch.int8, "u1": torch.uint8}
-    _NP = {"f8": np.float64, "i8": np.int64, "i1": np.int8, "u1": np.uint8}
+    _TORCH = {"f8": torch.float64, "i8": torch.int64, "i4": torch.int32, "i1": torch.int8, "u1": torch.uint8}
+    _NP = {"f8": np.float64, "i8": np.int64, "i4": np.int32, "i1": np.int8, "u1": np.uint8}
 
     def __init__(self, offsets_host, cell_obstacle, cell_mode, n_states, pos_last_cell, T: int,
                  prediction_horizon: int, eps_ura=None, device=None, bbox=BBOX_DEFAULT, R: float = ops.R_EV_OV,
                  target_p: float = ops.TARGET_P, accel: bool = False, use_graph: bool = True,
-                 builder: str = "minkowski"):
+                 builder: str = "minkowski", ingest: Optional[dict] = None):
         if builder not in ("minkowski", "affine", "both"):
             raise ValueError("builder must be 'minkowski' (shrinking horizon, v8ideal:881-947), "
                              "'affine' (receding horizon, v8ideal:1476-1515) or 'both'")
@@ -603,7 +605,21 @@ class StepPlan:
         self.offsets = _h2d(self.offsets_host, dev)
         self.pos_last = _h2d(np.asarray(pos_last_cell, dtype=np.float64).reshape(self.C, 2), dev)
         self.lw_cell = _h2d(np.broadcast_to(np.asarray(bbox, dtype=np.float64), (self.C, 2)).copy(), dev)
-        self.host_samples = torch.empty((self.N, self.T, 2), dtype=torch.float64).pin_memory()
+        # ingest mode (from_predictions): raw float32 predictions + latents in, grouping done on the device
+        self.ingest = ingest
+        if ingest is not None:
+            V, Nv, S = int(ingest["V"]), int(ingest["N"]), int(ingest["S"])
+            self.host_pred = torch.zeros((V, Nv, self.T, 2), dtype=torch.float32).pin_memory()
+            self.host_z = torch.zeros((V, Nv), dtype=torch.int32).pin_memory()
+            self.host_pmf = torch.zeros((V, S), dtype=torch.float64).pin_memory()
+            self.pred = torch.empty((V, Nv, self.T, 2), dtype=torch.float32, device=dev)
+            self.z = torch.empty((V, Nv), dtype=torch.int32, device=dev)
+            self.pmf = torch.empty((V, S), dtype=torch.float64, device=dev)
+            self.perm_dev = torch.empty((V, Nv), dtype=torch.int64, device=dev)
+            self.group_ws = torch.empty(int(ops._lib.load().ccmpc_group_workspace_bytes(V, Nv)), dtype=torch.uint8,
+                                        device=dev)
+        self.host_samples = (torch.empty((self.N, self.T, 2), dtype=torch.float64).pin_memory()
+                             if ingest is None else None)
         self.host_ref = torch.empty((self.T, 2), dtype=torch.float64).pin_memory()
         self.samples = torch.empty((self.N, self.T, 2), dtype=torch.float64, device=dev)
         self.ref = torch.empty((self.T, 2), dtype=torch.float64, device=dev)
@@ -612,9 +628,10 @@ class StepPlan:
         self.sums = torch.empty((self.C, ops.sums_len(self.T)), dtype=torch.float64, device=dev)
         self.ws = ops.sample_sums_workspace(self.N, self.C, self.T, dev)
         # ---- one output arena on the device, one pinned mirror on the host
-        dims = {"C": self.C, "P": self.P, "T": self.T, "T1": self.T + 1}
+        dims = {"C": self.C, "P": self.P, "T": self.T, "T1": self.T + 1, "C1": self.C + 1,
+                "V": int(ingest["V"]) if ingest is not None else 0}
         off, self._layout = 0, {}
-        for name, ty, shp in self._FIELDS:
+        for name, ty, shp in self._FIELDS + (self._INGEST_FIELDS if ingest is not None else ()):
             if (builder == "affine" and name in self._MINK_ONLY) or (builder == "minkowski" and name in self._AFF_ONLY):
                 continue
             shape = tuple(dims.get(s, s) for s in shp)
@@ -635,6 +652,12 @@ class StepPlan:
         self._aff = (dict(nd=self.out["aff_nd"], offset_rhs=self.out["aff_offset_rhs"],
                           idx_side=self.out["aff_idx_side"], mean=self.out["mean"], cov=self.out["aff_cov"],
                           status=self.out["aff_status"]) if builder != "minkowski" else None)
+        if ingest is not None:
+            self.offsets = self.out["g_offsets"]          # written by the grouping kernel every step
+            self._group_out = dict(samples=self.samples, offsets=self.out["g_offsets"], perm=self.perm_dev,
+                                   n_states=self.out["g_n_states"], cell_latent=self.out["g_cell_latent"],
+                                   cell_pmf=self.out["g_cell_pmf"], init_center=self.out["g_init_center"],
+                                   status=self.out["g_status"])
         self._ego_is_ref = True
         self._graph_full = self._graph_dev = None
         self.launches_per_step = None
@@ -667,6 +690,38 @@ class StepPlan:
         plan.cell_latent = np.asarray([np.unique(z[o])[k] for o, k in zip(co, ck)])
         return plan
 
+    @classmethod
+    def from_predictions(cls, V: int, N: int, T: int, pos_last, prediction_horizon: int, S: int = 25,
+                         minpos=(0.0, 0.0), filter_pmf: float = 0.1, device=None, **kw) -> "StepPlan":
+        """Ingest mode: the planner hands over what ``generate_vehicle_latents`` returns (prediction.py:103-104) -
+        ``predictions (V, N, T, 2)`` float32, ``z (V, N)``, ``latent_probs (V, S)`` - and the bucket-by-latent /
+        rare-latent fold of v8ideal:486-494 + ovehicle.py:55-113 runs on the device inside the same CUDA graph.
+        Fixed cell layout: cell = v * S + j, cells j >= K_v empty (their rows are NaN, ``g_n_states`` says K_v).
+        Fill ``host_pred`` / ``host_z`` / ``host_pmf`` (pinned) or pass them to :meth:`run_predictions`."""
+        C = V * S
+        offs = np.zeros(C + 1, dtype=np.int64)
+        offs[-1] = V * N
+        co = np.repeat(np.arange(V), S)
+        ck = np.tile(np.arange(S), V)
+        kw.setdefault("eps_ura", np.full((V, S), EPS_TOTAL / V))            # eps_ura[o, k] = eps / O (v8ideal:2920-2926)
+        plan = cls(offs, co, ck, [S] * V, np.asarray(pos_last, dtype=np.float64).reshape(V, 2)[co], T,
+                   prediction_horizon, device=device,
+                   ingest=dict(V=V, N=N, S=S, minpos=tuple(float(m) for m in minpos), filter_pmf=float(filter_pmf)),
+                   **kw)
+        return plan
+
+    def run_predictions(self, predictions=None, z=None, latent_probs=None, ref_traj=None) -> dict:
+        """Ingest-mode step: host predictions in -> host rows out (one graph launch + one sync)."""
+        if self.ingest is None:
+            raise RuntimeError("run_predictions needs a plan built by StepPlan.from_predictions")
+        if predictions is not None:
+            self.host_pred.copy_(torch.as_tensor(np.asarray(predictions, dtype=np.float32)).reshape(self.host_pred.shape))
+        if z is not None:
+            self.host_z.copy_(torch.as_tensor(np.asarray(z).astype(np.int32)).reshape(self.host_z.shape))
+        if latent_probs is not None:
+            self.host_pmf.copy_(torch.as_tensor(np.asarray(latent_probs, dtype=np.float64)).reshape(self.host_pmf.shape))
+        return self.run(ref_traj=ref_traj)
+
     # -------------------------------------------------------------- launches
     def _enqueue_device(self):
         ops.yaws_from_positions(self.samples, self.offsets, self.pos_last, out=self.yaws)
@@ -686,16 +741,29 @@ class StepPlan:
             ops.violation_counts(self.samples, self.offsets, self.out["nd"], self.out["idx_side"],
                                  out=self.out["viol"])
 
+    def _enqueue_ingest(self):
+        """Device grouping of the raw predictions (v8ideal:486-494 + ovehicle.py:55-113) into the CSR layout."""
+        ops.group_by_mode(self.pred, self.z, self.pmf, minpos=self.ingest["minpos"],
+                          filter_pmf=self.ingest.get("filter_pmf", 0.1), workspace=self.group_ws, out=self._group_out)
+
     def _enqueue_full(self):
-        self.samples.copy_(self.host_samples, non_blocking=True)
-        self.ref.copy_(self.host_ref, non_blocking=True)
+        if self.ingest is not None:
+            self.pred.copy_(self.host_pred, non_blocking=True)
+            self.z.copy_(self.host_z, non_blocking=True)
+            self.pmf.copy_(self.host_pmf, non_blocking=True)
+            self.ref.copy_(self.host_ref, non_blocking=True)
+            self._enqueue_ingest()
+        else:
+            self.samples.copy_(self.host_samples, non_blocking=True)
+            self.ref.copy_(self.host_ref, non_blocking=True)
         self._enqueue_device()
         self.host_arena.copy_(self.arena, non_blocking=True)
 
     def _capture(self):
         from . import _lib
         lib = _lib.load()
-        self.samples.copy_(self.host_samples)
+        if self.ingest is None:
+            self.samples.copy_(self.host_samples)
         self.ref.copy_(self.host_ref)
         side = torch.cuda.Stream(device=self.device)
         side.wait_stream(torch.cuda.current_stream())

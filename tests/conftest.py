@@ -14,6 +14,8 @@ GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+    # the oracle calls scipy.spatial.distance_matrix because the reference does (ovehicle.py:94)
+    config.addinivalue_line("filterwarnings", "ignore:.*is deprecated in favor of.*:DeprecationWarning")
 
 
 @pytest.fixture(scope="session")

@@ -544,3 +544,42 @@ def test_group_by_mode_matches_oracle(dev, V, N, T, S, sparse, f32):
             np.testing.assert_allclose(h["init_center"][c], centers[j], rtol=1e-13)
             np.testing.assert_allclose(h["cell_pmf"][c], pmf_o[j], rtol=1e-15)
     assert h["offsets"][-1] == V * N
+
+
+def test_step_plan_ingest_matches_host_grouped_plan(dev):
+    """StepPlan.from_predictions (float32 predictions + z + latent pmf in, grouping on the device inside the
+    graph) gives, for every retained (vehicle, mode), exactly the rows of a plan fed with the oracle's
+    host-side grouping (v8ideal:486-494 + ovehicle.py:55-113)."""
+    from ccmpc_b200 import midlevel
+    from oracle import restate, synth
+    rng = np.random.default_rng(77)
+    V, N, T, S = 3, 2500, 8, 25
+    pred, z, pmf = _group_inputs(rng, V, N, T, S, sparse=True)
+    minpos = np.asarray([160.0, -90.0])
+    pos_last = minpos + rng.normal(size=(V, 2)) * 3
+    ref_traj = synth.reference_trajectory(T)
+    plan = midlevel.StepPlan.from_predictions(V, N, T, pos_last, prediction_horizon=T, S=S, minpos=minpos,
+                                              device=dev, builder="both")
+    for rep in range(2):                                  # replay the graph on fresh inputs
+        if rep == 1:
+            pred, z, pmf = _group_inputs(rng, V, N, T, S, sparse=True)
+        res = plan.run_predictions(pred, z, pmf, ref_traj=ref_traj)
+        pred64 = pred.astype(np.float64) + minpos
+        for v in range(V):
+            keep = np.argwhere(pmf[v] > 0.1).ravel()
+            assert res["g_n_states"][v] == keep.size
+            if keep.size == 0:
+                continue
+            pos_l, _, _, pmf_o, _ = restate.group_by_mode(pred64[v], z[v], pmf[v], pos_last[v], T)
+            offs = np.concatenate([[0], np.cumsum([p.shape[0] for p in pos_l])])
+            href = midlevel.StepPlan(offs, [0] * keep.size, list(range(keep.size)), [keep.size],
+                                     np.tile(pos_last[v], (keep.size, 1)), T, T, device=dev, builder="both",
+                                     eps_ura=np.full((1, keep.size), 0.05 / V), use_graph=False)
+            want = href.run(pos_host=np.concatenate(pos_l), ref_traj=ref_traj)
+            for j in range(keep.size):
+                c = v * S + j
+                assert res["g_cell_latent"][c] == keep[j]
+                np.testing.assert_allclose(res["g_cell_pmf"][c], pmf_o[j], rtol=1e-15)
+                for k in ("nd", "ab", "idx_side", "status", "prob_lower", "mean", "cov", "At", "b0", "yaw_mean",
+                          "counts", "viol", "aff_nd", "aff_offset_rhs", "aff_idx_side"):
+                    np.testing.assert_array_equal(res[k][c], want[k][j], err_msg=f"{k} differs (v={v}, j={j})")
