@@ -451,6 +451,43 @@ def bench_also(torch, ops, midlevel, synth, dev, args, world=1, rank=0, dist=Non
                     f"np{C5['N']}: pinned fp64 predictions H2D -> yaws -> sums/counts -> affine half-planes -> L4 -> "
                     f"D2H (one CUDA graph per step); 41 MB sample tensor per step exceeds nothing but is re-sent "
                     f"every step", "rows": int(plan.C * plan.T), "launches_per_step": plan.launches_per_step}
+    del plan
+    # ---- c5 through the ingest boundary: what generate_vehicle_latents returns (float32 predictions, z,
+    #      latent pmf; prediction.py:103-104) goes to the device, bucket-by-latent + rare-latent fold
+    #      (v8ideal:486-494, ovehicle.py:55-113) run there, inside the same graph
+    S = 25
+    pred32 = np.ascontiguousarray((pos - synth.MINPOS).astype(np.float32))
+    pmf = np.zeros((C5["O"], S))
+    pmf[:, :C5["K"]] = sc.weights
+    plan = midlevel.StepPlan.from_predictions(C5["O"], C5["N"], C5["T"], sc.pos_last, prediction_horizon=C5["T"],
+                                              S=S, minpos=synth.MINPOS, device=dev, builder="affine")
+    plan.host_pred.copy_(torch.from_numpy(pred32))
+    plan.host_z.copy_(torch.from_numpy(z.astype(np.int32)))
+    plan.host_pmf.copy_(torch.from_numpy(pmf))
+    hp = plan.host_pred.numpy()
+    slab = max(1, C5["N"] // 16)
+    lat = []
+    for i in range(10 + C5["steps"]):
+        lo = (i % 16) * slab
+        hp[:, lo:lo + slab] += np.float32(0.01)
+        ref_i = ref0 + 0.02 * i
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        res = plan.run(ref_traj=ref_i)
+        dt = (time.perf_counter() - t0) * 1e3
+        if i >= 10:
+            lat.append(dt)
+    assert int(res["g_n_states"].sum()) == C5["O"] * C5["K"] and not res["g_status"].any()
+    out["replay_c5_ingest"] = {
+        "metric": "mpc_step_latency_ms", "unit": "ms", "higher_is_better": False, "steps": C5["steps"],
+        "p50_host_to_host": float(np.percentile(lat, 50)), "p95_host_to_host": float(np.percentile(lat, 95)),
+        "mean_host_to_host": float(np.mean(lat)),
+        "h2d_bytes_per_step": int(plan.host_pred.numel() * 4 + plan.host_z.numel() * 4 + plan.host_pmf.numel() * 8
+                                  + plan.host_ref.numel() * 8),
+        "d2h_bytes_per_step": int(plan.host_arena.numel()),
+        "workload": f"c5 from the predictor's outputs: float32 predictions ({C5['O']}, {C5['N']}, {C5['T']}, 2) + z + "
+                    f"latent pmf ({S} states) H2D -> device mode grouping -> yaws -> sums/counts -> affine half-planes "
+                    f"-> L4 -> D2H, one CUDA graph per step", "launches_per_step": plan.launches_per_step}
     return out
 
 
