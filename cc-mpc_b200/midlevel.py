@@ -325,6 +325,41 @@ class MidlevelConstraints:
         raise InSimulationException(f"no moments of frame {frame} (predict_ideal needs the step {self.frame_stride} "
                                     f"frames earlier, v8ideal:2626)")
 
+    # ------------------------------------------------------------ _cov side file
+    def cov_payload(self, built, shrinking: bool, params=None, agent_params=None, apply_robust: bool = True) -> dict:
+        """The ``data_save`` dict the planner pickles next to every solve (v8ideal:2979-3003), filled from the
+        9-tuple a builder of this class returned.  The caller adds the solver's own entries
+        (``solve_time``, ``process_time``, ``x_init``, ``cost``, ``goal``, ``U_star``, ``X_star``, ``timeout``,
+        ``infeasible``; v8ideal:3033-3058, :3102-3103) before :meth:`save_data`."""
+        _, _, _, _, OVconstraint, direct, ov_mean, ov_cov, meanNtangent = built
+        d = {"direct": direct, "MeanCov": True, "OVconstraint": OVconstraint, "ovStateMean_tau_1": ov_mean,
+             "ovStateCov_tau_1": ov_cov, "shrinking": shrinking}
+        if shrinking and apply_robust:
+            d["meanNtangent"] = meanNtangent                      # :2989-2991 (the Minkowski builder returns 0)
+        d["params"] = params
+        d["__params"] = agent_params
+        return d
+
+    def save_data(self, data_save: dict, params, ego_vehicle_id):
+        """v8ideal:2559-2567: ``out/data/agent{id}_frame{frame}_cov`` (read back by :meth:`load_data` ten frames
+        later and by ``dataForCost_ref.getData_singleEpisode`` / ``ccmpc_b200.cost``)."""
+        if not self.out_dir:
+            return None
+        path = os.path.join(self.out_dir, f"agent{ego_vehicle_id}_frame{int(params.frame)}_cov")
+        try:
+            os.makedirs(self.out_dir, exist_ok=True)
+            with open(path, "wb") as f:
+                pickle.dump(data_save, f)
+        except OSError:
+            return None                                           # the reference logs and continues (:2566-2567)
+        return path
+
+    def load_data(self, params, ego_vehicle_id):
+        """v8ideal:2547-2557: ``meanNtangent`` of the step ten frames earlier."""
+        path = os.path.join(self.out_dir or "", f"agent{ego_vehicle_id}_frame{int(params.frame) - self.frame_stride}_cov")
+        with open(path, "rb") as f:
+            return pickle.load(f)["meanNtangent"]
+
     # --------------------------------------------------------- predict_ideal
     def predict_ideal_cells(self, n_states: Sequence[int], T: int, moments: Moments, x0=None, z=None,
                             n_samples: Optional[int] = None, seed: Optional[int] = None,

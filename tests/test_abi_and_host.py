@@ -118,3 +118,25 @@ def test_count_allreduce_world2_gloo():
     for p in procs:
         p.join(timeout=60)
     assert sorted(res) == [(0, True), (1, True)]
+
+
+def test_cov_side_file_roundtrip(tmp_path):
+    """MidlevelConstraints.cov_payload / save_data write what dataForCost_ref.get_data (:49-68) and
+    montecarlo_cost_ref.py:11 (file-name regex) read; load_data returns meanNtangent of frame - 10 (v8ideal:2547-2557)."""
+    import types
+    from ccmpc_b200 import cost, midlevel
+    mc = midlevel.MidlevelConstraints.__new__(midlevel.MidlevelConstraints)      # no device needed for the file helpers
+    mc.out_dir, mc.frame_stride = str(tmp_path), 10
+    built = ("rows", None, None, None, True, [None], ([[1.0]], [[2.0]], [[0.1]]), ([[0.5]], [[0.6]], [[0.01]]), 0)
+    for i, frame in enumerate((100, 110, 120)):
+        d = mc.cov_payload(built, shrinking=True, params={"frame": frame})
+        assert d["MeanCov"] is True and d["meanNtangent"] == 0 and d["OVconstraint"] is True
+        d.update(solve_time=0.1 * (i + 1), process_time=0.2, x_init=np.zeros(4), cost=1.0, goal=np.zeros(2),
+                 U_star=np.full((8, 2), 0.1 * i), X_star=np.full((8, 4), float(i)), timeout=False, infeasible=False)
+        assert mc.save_data(d, types.SimpleNamespace(frame=frame), 7).endswith(f"agent7_frame{frame}_cov")
+    assert mc.load_data(types.SimpleNamespace(frame=110), 7) == 0
+    assert cost.scan_episodes(str(tmp_path)) == {7: (100, 120)}
+    ep = cost.getData_singleEpisode(7, 100, 3, root=str(tmp_path) + "/")
+    avrP, avrS, avrSOV, worst, X_star, U_star, goal, x_init, timeout = ep.get_data()
+    assert abs(avrS - 0.2) < 1e-12 and abs(worst - 0.3) < 1e-12 and timeout == [False] * 3
+    assert np.allclose(X_star[2], 2.0) and np.allclose(U_star[1], 0.1)
