@@ -359,7 +359,7 @@ def bench_also(torch, ops, midlevel, synth, dev, args, world=1, rank=0, dist=Non
     del sx, sy, rho
     chi = -2.0 * np.log(0.05 / O / T)
     bufs = None
-    for accel in (False, True):
+    for accel in (0, 1, 2):
         for _ in range(3):
             bufs = ops.mvoe_halfplane_sweep(cov, mu, ref, chi, accel=accel, out=bufs)
         torch.cuda.synchronize()
@@ -377,11 +377,12 @@ def bench_also(torch, ops, midlevel, synth, dev, args, world=1, rank=0, dist=Non
             ms = float(mt.item())
         M = S * O * T * K * world
         bytes_per = 24 + 16 + 24 + 24 + 1 + 1
-        out["mvoe_sweep_accel" if accel else "mvoe_sweep"] = {
+        out[("mvoe_sweep", "mvoe_sweep_accel", "mvoe_sweep_direct")[accel]] = {
             "metric": "mvoe_fits_per_sec", "value": M / (ms * 1e-3), "unit": "fits/s", "ms": ms, "fits": M,
             "workload": f"c4: S={S} x O={O} x T={T} x K={K} footprint fit + tangent half-plane per GPU "
                         f"(scenarios sharded x{world}, no exchange)", "n_gpus": world,
-            "iterate": "float32 warm start + fp64 map" if accel else "reference sequence from beta = 1",
+            "iterate": ("reference sequence from beta = 1", "float32 warm start + fp64 map",
+                        "Newton on the stationarity cubic, accepted by one reference-map step at tol 1e-8")[accel],
             "roofline": {"bound": "hbm", "achieved": M / world * bytes_per / (ms * 1e-3) / 1e9, "peak": peak,
                          "unit": "GB/s", "frac": M / world * bytes_per / (ms * 1e-3) / 1e9 / peak,
                          "bytes_per_fit": bytes_per, "per": "GPU"}}

@@ -113,7 +113,7 @@ __device__ __forceinline__ double mvoe_beta(const MvoeSpectrum& sp, double tol, 
     double beta = 1.0;
     const double tr = sp.tr, dt2 = 2.0 * sp.dt;
     int it = 0;
-    if (accel) {
+    if (accel == 1) {
         // float32 warm start: same map, stopped at a float-level tolerance.
         float b = 1.0f;
         const float trf = (float)tr, dtf = (float)dt2;
@@ -124,6 +124,42 @@ __device__ __forceinline__ double mvoe_beta(const MvoeSpectrum& sp, double tol, 
             if (close) break;
         }
         if (isfinite(b) && b > 0.0f) beta = (double)b;
+    }
+    if (accel == 2 && maxiter > 0) {
+        // Direct solve.  The fixed point of the map is the one positive root of
+        //   g(b) = 2 dt b^3 + tr b^2 - tr b - 2
+        // (square the map and clear the denominator; one sign change => one positive root, g convex for b > 0).
+        // Every lane runs the SAME instruction count: float32 seed dt^-1/4 (exact when lam_1 = lam_2), two
+        // float32 map steps (exact in both limits dt -> 0, inf), three float32 Newton steps, two fp64 Newton
+        // steps with a MUFU reciprocal (the correction only needs ~2^-20 relative accuracy), and then ONE
+        // evaluation of the reference map, accepted under the reference's own rule |F(b) - b| < tol.
+        // A lane that fails the rule falls through to the reference sequence from beta = 1.
+        const float trf = (float)tr, dtf = (float)dt2;
+        float b = rsqrtf(sqrtf(0.5f * dtf));
+#pragma unroll
+        for (int k = 0; k < 2; ++k) b = sqrtf(__fdividef(fmaf(b, trf, 2.0f), fmaf(b, dtf, trf)));
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            const float g = fmaf(fmaf(fmaf(dtf, b, trf), b, -trf), b, -2.0f);
+            const float gp = fmaf(fmaf(3.0f * dtf, b, 2.0f * trf), b, -trf);
+            const float nb = b - __fdividef(g, gp);
+            b = (gp > 0.0f && nb > 0.0f) ? nb : b;
+        }
+        double x = (double)b;
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const double g = fma(fma(fma(dt2, x, tr), x, -tr), x, -2.0);
+            const double gp = fma(fma(3.0 * dt2, x, 2.0 * tr), x, -tr);
+            double r;
+            asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(gp));
+            x = fma(-g, r, x);
+        }
+        const double a = fma(x, tr, 2.0), bb = fma(x, dt2, tr);
+        const double nb = a * rsqrt_newton<2>(a * bb);
+        if (fabs(nb - x) < tol) {
+            iters = 1;
+            return nb;
+        }
     }
     bool converged = false;
     for (; it < maxiter;) {

@@ -74,7 +74,7 @@ def mvoe_fit(sigma1, sigma2=None, footprint_r2: float = R_EV_OV ** 2, tol: float
     iters = _new(lead, I32, sigma1) if want_iters else None
     status = _new(lead, U8, sigma1)
     _lib.check(lib.ccmpc_mvoe_fit(_p(sigma1), _p(sigma2), float(footprint_r2), M, float(tol), int(maxiter),
-                                  int(bool(accel)), _p(beta), _p(q), _p(iters), _p(status), _stream()),
+                                  int(accel), _p(beta), _p(q), _p(iters), _p(status), _stream()),
                "ccmpc_mvoe_fit")
     return beta, q, iters, status
 
@@ -94,7 +94,7 @@ def mvoe_halfplane_sweep(cov, mu, ref, chi_scale: float, footprint_r2: float = R
                _new((S, O, T, K), I8, cov), _new((S, O, T, K), U8, cov))
     q, nd, idx_side, status = out
     _lib.check(lib.ccmpc_mvoe_halfplane_sweep(_p(cov), _p(mu), _p(ref), S, O, T, K, float(chi_scale),
-                                              float(footprint_r2), float(tol), int(maxiter), int(bool(accel)),
+                                              float(footprint_r2), float(tol), int(maxiter), int(accel),
                                               _p(q), _p(nd), _p(idx_side), _p(status), _stream()),
                "ccmpc_mvoe_halfplane_sweep")
     return q, nd, idx_side, status
@@ -252,7 +252,7 @@ def minkowski_halfplanes(sums, pivot, ref, eps_cell, prediction_horizon: int, R:
     g = out.get
     _lib.check(lib.ccmpc_minkowski_halfplanes(
         _p(sums), _p(pivot), _p(ref), stride, _p(eps_cell), C, T, int(prediction_horizon), float(R), float(target_p),
-        float(tol), int(maxiter), int(bool(accel)), _p(g("nd")), _p(g("ab")), _p(g("idx_side")), _p(g("q")),
+        float(tol), int(maxiter), int(accel), _p(g("nd")), _p(g("ab")), _p(g("idx_side")), _p(g("q")),
         _p(g("q1")), _p(g("betas")), _p(g("cov_infer")), _p(g("cov_mu")), _p(g("prob_pair")), _p(g("prob_lower")),
         _p(g("mean")), _p(g("status")), _stream()), "ccmpc_minkowski_halfplanes")
     return out

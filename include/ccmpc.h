@@ -66,6 +66,11 @@ uint64_t ccmpc_launch_count(void);
  *   accel = 0: the reference's iterate sequence from beta = 1 (same stopping
  *   rule, same iteration count).  accel = 1: float32 warm start, then the same
  *   fp64 fixed-point map until |delta| < tol (result within tol of accel = 0).
+ *   accel = 2: direct solve - Newton on the stationarity cubic
+ *   2 det b^3 + tr b^2 - tr b - 2 = 0 (tr, det of Sigma1^-1 Sigma2) with a fixed
+ *   instruction count per fit, accepted by ONE evaluation of the reference map
+ *   under the reference's rule |F(b) - b| < tol (iters = 1); a fit that fails the
+ *   rule is redone with accel = 0.  beta within ~tol of accel = 0 (1e-5 contract).
  */
 int ccmpc_mvoe_fit(const double* sigma1, const double* sigma2, double footprint_r2,
                    int64_t M, double tol, int maxiter, int accel,

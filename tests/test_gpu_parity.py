@@ -63,6 +63,12 @@ def test_mvoe_fit_matches_reference_golden(dev, golden):
     np.testing.assert_allclose(beta_a.cpu().numpy(), g["beta"], rtol=1e-6)
     assert relerr(full(q_a.cpu().numpy()), g["Q"]) < 1e-7
     assert it_a.float().mean() < iters.float().mean()
+    # direct solve (accel = 2): the root of the stationarity cubic, accepted under the reference's stopping rule
+    beta_d, q_d, it_d, st_d = ops.mvoe_fit(T_(sym3(g["Sigma1"]), dev), T_(sym3(g["Sigma2"]), dev), accel=2)
+    assert not st_d.any()
+    np.testing.assert_allclose(beta_d.cpu().numpy(), g["beta"], rtol=1e-7)   # north_star: 1e-5 relative
+    assert relerr(full(q_d.cpu().numpy()), g["Q"]) < 1e-7
+    assert int(it_d.max()) == 1, "every golden pair is solved without falling back to the iteration"
 
 
 def test_mvoe_fit_footprint_form_and_edge_cases(dev):
@@ -88,6 +94,46 @@ def test_mvoe_fit_footprint_form_and_edge_cases(dev):
     assert st.item() == ops.ST_SINGULAR
     _, _, it, st = ops.mvoe_fit(T_([[1.0, 0.2, 2.0]], dev), T_([[30.0, 0.0, 0.5]], dev), maxiter=2)
     assert st.item() == ops.ST_NOT_CONVERGED and it.item() == 2
+
+
+@pytest.mark.parametrize("accel", [0, 1, 2])
+def test_mvoe_halfplane_sweep_matches_oracle(dev, accel):
+    """c4 kernel (v8ideal:915-939 per cell) against the restated compute_mvoe + choose_closest_tangent, on a small
+    (S, O, T, K) block that is NOT a multiple of the 256-fit tile, with eigenvalue ratios up to 1e8 (drives the
+    direct solve into its fall-back), a singular covariance and a cell whose slope is undefined."""
+    from ccmpc_b200 import ops
+    from oracle import restate, synth
+    S, O, T, K = 3, 2, 5, 7
+    rng = np.random.default_rng(40 + accel)
+    cov = synth.random_spd(rng, (S, O, T, K))
+    wide = synth.random_spd(rng, (O, T, K), smin=1e-3, smax=30.0)
+    cov[1] = wide
+    cov[1, :, :, 0, 0] *= 1e4                       # sigma_x >> sigma_y: lam ratio up to ~1e8
+    cov[1, :, :, 0, 1] *= 1e2
+    mu = np.stack([rng.uniform(150, 200, (S, O, T, K)), rng.uniform(-100, -60, (S, O, T, K))], -1)
+    ref = np.broadcast_to(synth.reference_trajectory(T), (S, T, 2)).copy()
+    ref[..., 1] += 30.0
+    cov[2, 1, 4, 6] = [1.0, 1.0, 1.0]               # singular Sigma1
+    mu[2, 0, 3, 2, 1] = ref[2, 3, 1]                # ref_y == mu_y: slope -dx/0 (v8ideal:923)
+    chi = -2.0 * np.log(0.05 / O / T)
+    R2 = 3.4 ** 2
+    q, nd, idx_side, status = ops.mvoe_halfplane_sweep(T_(cov, dev), T_(mu, dev), T_(ref, dev), chi, accel=accel)
+    q, nd, idx_side, status = (a.cpu().numpy() for a in (q, nd, idx_side, status))
+    assert status[2, 1, 4, 6] == ops.ST_SINGULAR and status[2, 0, 3, 2] != 0
+    status[2, 1, 4, 6] = status[2, 0, 3, 2] = 0
+    assert not status.any()
+    for s, o, t, k in np.ndindex(S, O, T, K):
+        if (s, o, t, k) in ((2, 1, 4, 6), (2, 0, 3, 2)):
+            continue
+        b_ref, Q = restate.mvoe(synth.sym_to_full(cov[s, o, t, k]) * chi, np.eye(2) * R2)
+        # the reference stops at an ABSOLUTE |delta beta| < 1e-8, so Q = (1 + 1/beta) Sigma1 + ... is only
+        # defined to ~1e-8 / beta relative by its own rule; the reference sequence (accel = 0) lands on the same iterate
+        assert relerr(full(q[s, o, t, k]), Q) < (1e-7 if accel == 0 else max(1e-7, 3e-8 / min(b_ref, 1.0) ** 2))
+        m = -(ref[s, t, 0] - mu[s, o, t, k, 0]) / (ref[s, t, 1] - mu[s, o, t, k, 1])
+        n, d, idx = restate.closest_tangent(mu[s, o, t, k], Q, 1, m, ref[s, t])
+        assert np.allclose(nd[s, o, t, k, :2], n, rtol=1e-12) and abs(nd[s, o, t, k, 2] - d) <= 1e-7 * abs(d)
+        assert (idx_side[s, o, t, k] & 1) == idx                                       # bit-exact best_idx
+        assert bool(idx_side[s, o, t, k] & 2) == (not (n @ mu[s, o, t, k] <= d))       # side (v8ideal:926)
 
 
 # ----------------------------------------------------------------------------- K4
