@@ -45,6 +45,8 @@ __device__ __forceinline__ double diff_of_products(double a, double b, double c,
 
 __device__ __forceinline__ double det2(const Sym2& s) { return diff_of_products(s.xx, s.yy, s.xy, s.xy); }
 
+__device__ __forceinline__ double rcp_newton(double x);   // defined below (MUFU seed + 2 Newton steps)
+
 // ---------------------------------------------------------------------------
 // MVOE fixed point (makeconstraint.py:21-32).
 //
@@ -76,11 +78,12 @@ __device__ __forceinline__ MvoeSpectrum mvoe_spectrum(const Sym2& s1, const Sym2
 }
 
 // Footprint fit: Sigma2 = r2 * I.
+template <bool FAST = false>
 __device__ __forceinline__ MvoeSpectrum mvoe_spectrum_iso(const Sym2& s1, double r2) {
     MvoeSpectrum sp;
     double d1 = det2(s1);
     sp.status = (d1 == 0.0 || !isfinite(d1)) ? CCMPC_ST_SINGULAR : CCMPC_ST_OK;
-    double inv = 1.0 / d1;
+    double inv = FAST ? rcp_newton(d1) : 1.0 / d1;
     sp.tr = r2 * (s1.xx + s1.yy) * inv;
     sp.dt = r2 * r2 * inv;
     double disc = fma(sp.tr, sp.tr, -4.0 * sp.dt);
@@ -103,13 +106,79 @@ __device__ __forceinline__ double rsqrt_newton(double p) {
     return r;
 }
 
+// 1/x for finite normal x: MUFU seed + two Newton steps (~1 ulp, not correctly rounded; no IEEE slow path).
+// x = 0 gives inf * 0 = NaN after the first step, which callers flag through their status byte.
+__device__ __forceinline__ double rcp_newton(double x) {
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        const double e = fma(-x, r, 1.0);
+        r = fma(r, e, r);
+    }
+    return r;
+}
+
+__device__ __forceinline__ float rcp_approx_f32(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float rsqrt_approx_f32(float x) {
+    float r;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
+// Direct solve of the MVOE fixed point (ccmpc.h, accel = 2).  The fixed point of the map is the one
+// positive root of
+//   g(b) = 2 dt b^3 + tr b^2 - tr b - 2
+// (square the map and clear the denominator; one sign change => one positive root, g convex for b > 0).
+// Every lane runs the SAME instruction count: float32 seed dt^-1/4 (exact when lam_1 = lam_2), two
+// float32 map steps (exact in both limits dt -> 0, inf), three float32 Newton steps, two fp64 Newton
+// steps with a MUFU reciprocal (the correction only needs ~2^-20 relative accuracy), and then ONE
+// evaluation of the reference map, accepted under the reference's own rule |F(b) - b| < tol.
+// Returns F(b) and 1/F(b) (both ~1 ulp: a rsqrt(ab) and b rsqrt(ab)), or -1 when the rule fails
+// (the caller then runs the reference sequence from beta = 1).  MUFU-only float32: no IEEE slow paths.
+__device__ __forceinline__ double mvoe_beta_direct(double tr, double dt2, double tol, double& inv_beta) {
+    const float trf = (float)tr, dtf = (float)dt2;
+    float b = rsqrt_approx_f32(0.5f * dtf);
+    b = b * rsqrt_approx_f32(b);                   // sqrt(rsqrt(dt)) = dt^-1/4
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        const float num = fmaf(b, trf, 2.0f), den = fmaf(b, dtf, trf);
+        b = num * rsqrt_approx_f32(num * den);
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float g = fmaf(fmaf(fmaf(dtf, b, trf), b, -trf), b, -2.0f);
+        const float gp = fmaf(fmaf(3.0f * dtf, b, 2.0f * trf), b, -trf);
+        const float nb = fmaf(-g, rcp_approx_f32(gp), b);
+        b = (gp > 0.0f && nb > 0.0f) ? nb : b;
+    }
+    double x = (double)b;
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        const double g = fma(fma(fma(dt2, x, tr), x, -tr), x, -2.0);
+        const double gp = fma(fma(3.0 * dt2, x, 2.0 * tr), x, -tr);
+        double r;
+        asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(gp));
+        x = fma(-g, r, x);
+    }
+    const double a = fma(x, tr, 2.0), bb = fma(x, dt2, tr);
+    const double r = rsqrt_newton<2>(a * bb);
+    const double nb = a * r;
+    inv_beta = bb * r;
+    return (fabs(nb - x) < tol) ? nb : -1.0;
+}
+
 // Returns beta; iters = number of fixed-point evaluations (reference loop count).
 // One iterate is sqrt(a / b) with a = 2 + beta tr, b = tr + 2 beta dt, evaluated as a * rsqrt(a b):
 // no IEEE division / square-root slow paths in the dependent chain (~11 fp64 instructions per iteration).
 // rsqrt carries ~1e-13 relative error per iterate; the map is a contraction, so the error does not
 // accumulate and stays five orders below the reference's own stopping tolerance (1e-8).
 __device__ __forceinline__ double mvoe_beta(const MvoeSpectrum& sp, double tol, int maxiter, int accel,
-                                            int& iters, int& status) {
+                                            int& iters, int& status, double* inv_beta = nullptr) {
     double beta = 1.0;
     const double tr = sp.tr, dt2 = 2.0 * sp.dt;
     int it = 0;
@@ -126,38 +195,11 @@ __device__ __forceinline__ double mvoe_beta(const MvoeSpectrum& sp, double tol, 
         if (isfinite(b) && b > 0.0f) beta = (double)b;
     }
     if (accel == 2 && maxiter > 0) {
-        // Direct solve.  The fixed point of the map is the one positive root of
-        //   g(b) = 2 dt b^3 + tr b^2 - tr b - 2
-        // (square the map and clear the denominator; one sign change => one positive root, g convex for b > 0).
-        // Every lane runs the SAME instruction count: float32 seed dt^-1/4 (exact when lam_1 = lam_2), two
-        // float32 map steps (exact in both limits dt -> 0, inf), three float32 Newton steps, two fp64 Newton
-        // steps with a MUFU reciprocal (the correction only needs ~2^-20 relative accuracy), and then ONE
-        // evaluation of the reference map, accepted under the reference's own rule |F(b) - b| < tol.
-        // A lane that fails the rule falls through to the reference sequence from beta = 1.
-        const float trf = (float)tr, dtf = (float)dt2;
-        float b = rsqrtf(sqrtf(0.5f * dtf));
-#pragma unroll
-        for (int k = 0; k < 2; ++k) b = sqrtf(__fdividef(fmaf(b, trf, 2.0f), fmaf(b, dtf, trf)));
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-            const float g = fmaf(fmaf(fmaf(dtf, b, trf), b, -trf), b, -2.0f);
-            const float gp = fmaf(fmaf(3.0f * dtf, b, 2.0f * trf), b, -trf);
-            const float nb = b - __fdividef(g, gp);
-            b = (gp > 0.0f && nb > 0.0f) ? nb : b;
-        }
-        double x = (double)b;
-#pragma unroll
-        for (int k = 0; k < 2; ++k) {
-            const double g = fma(fma(fma(dt2, x, tr), x, -tr), x, -2.0);
-            const double gp = fma(fma(3.0 * dt2, x, 2.0 * tr), x, -tr);
-            double r;
-            asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(gp));
-            x = fma(-g, r, x);
-        }
-        const double a = fma(x, tr, 2.0), bb = fma(x, dt2, tr);
-        const double nb = a * rsqrt_newton<2>(a * bb);
-        if (fabs(nb - x) < tol) {
+        double inv;
+        const double nb = mvoe_beta_direct(tr, dt2, tol, inv);
+        if (nb > 0.0) {
             iters = 1;
+            if (inv_beta) *inv_beta = inv;
             return nb;
         }
     }
@@ -173,6 +215,7 @@ __device__ __forceinline__ double mvoe_beta(const MvoeSpectrum& sp, double tol, 
     }
     iters = it;
     if (!converged && status == CCMPC_ST_OK) status = CCMPC_ST_NOT_CONVERGED;
+    if (inv_beta) *inv_beta = 1.0 / beta;
     return beta;
 }
 
@@ -184,6 +227,12 @@ __device__ __forceinline__ Sym2 mvoe_q(const Sym2& s1, const Sym2& s2, double be
 
 __device__ __forceinline__ Sym2 mvoe_q_iso(const Sym2& s1, double r2, double beta) {
     double a = 1.0 + 1.0 / beta, b = (1.0 + beta) * r2;
+    return Sym2{fma(a, s1.xx, b), a * s1.xy, fma(a, s1.yy, b)};
+}
+
+// same with 1/beta supplied by the solver (mvoe_beta's inv_beta)
+__device__ __forceinline__ Sym2 mvoe_q_iso_inv(const Sym2& s1, double r2, double beta, double inv_beta) {
+    double a = 1.0 + inv_beta, b = (1.0 + beta) * r2;
     return Sym2{fma(a, s1.xx, b), a * s1.xy, fma(a, s1.yy, b)};
 }
 
@@ -241,6 +290,7 @@ struct TangentStar {
     int idx;     // -1: no tangent (n^T Sigma n <= 0)
 };
 
+template <bool FAST = false>
 __device__ __forceinline__ TangentStar tangent_star(double mux, double muy, const Sym2& S, double c, double m,
                                                     double ax, double ay) {
     TangentStar t;
@@ -254,7 +304,7 @@ __device__ __forceinline__ TangentStar tangent_star(double mux, double muy, cons
         return t;
     }
     const double proj = fma(n0, mux, muy);
-    const double half = c * sqrt(q);
+    const double half = c * (FAST ? q * rsqrt_newton<2>(q) : sqrt(q));   // FAST: ~1 ulp, no IEEE sqrt slow path
     const double d_plus = proj + half, d_minus = proj - half;
     const double na = fma(n0, ax, ay);
     const double e0 = fabs(na - d_plus), e1 = fabs(na - d_minus);

@@ -90,52 +90,87 @@ mvoe_fit_kernel(const double* __restrict__ sigma1, const double* __restrict__ si
 // K3+K4 sweep over (scenario, obstacle, timestep, mode): footprint fit + tangent.
 // Bytes per cell: 24 (cov) + 16 (mu) in; 24 (Q) + 24 (n0,n1,d) + 1 out
 // (+ 16 per (scenario, t) for ref, amortised over O*K cells).
+// The kernel is instruction-issue bound once the fixed point is solved directly
+// (ncu: profiles/r01_ncu_full_sweep_direct.txt), so everything around the fit is
+// kept off the slow paths: index arithmetic by multiply-high (FastDiv), the
+// tile's scenario tracked incrementally, full tiles staged with two fixed
+// 16-byte accesses per thread, reciprocal / square root as MUFU seed + Newton.
 // ---------------------------------------------------------------------------
+struct FastDiv {   // q = n / d for n < 2^31 (Granlund-Montgomery round-up form): q = (umulhi(mul, n) + n) >> sh
+    uint32_t d, mul, sh;
+    __device__ __forceinline__ uint32_t div(uint32_t n) const { return (__umulhi(mul, n) + n) >> sh; }
+};
+
+static FastDiv make_fastdiv(uint32_t d) {
+    FastDiv f;
+    uint32_t l = 0;
+    while ((1ull << l) < d) ++l;
+    f.d = d;
+    f.sh = l;
+    f.mul = (uint32_t)((((1ull << l) - d) << 32) / d + 1);
+    return f;
+}
+
 __global__ void __launch_bounds__(FIT_THREADS)
 sweep_kernel(const double* __restrict__ cov, const double* __restrict__ mu, const double* __restrict__ ref,
-             int64_t M, int O, int T, int K, double chi_scale, double r2, double tol, int maxiter, int accel,
-             double* __restrict__ q_out, double* __restrict__ nd_out, int8_t* __restrict__ idx_side,
+             int64_t M, FastDiv dPerS, FastDiv dK, FastDiv dT, double chi_scale, double r2, double tol, int maxiter,
+             int accel, double* __restrict__ q_out, double* __restrict__ nd_out, int8_t* __restrict__ idx_side,
              uint8_t* __restrict__ status_out) {
     __shared__ __align__(16) double s_a[FIT_THREADS * 3];
     __shared__ __align__(16) double s_n[FIT_THREADS * 3];
+    constexpr int HALF = FIT_THREADS / 2;            // a full tile is 384 double2: tid and tid + 256 (< 384)
     const int tid = threadIdx.x;
     const int64_t ntiles = (M + FIT_THREADS - 1) / FIT_THREADS;
-    const int64_t per_s = (int64_t)O * T * K;
-    const uint32_t per_s32 = (uint32_t)per_s;
+    const uint32_t per_s = dPerS.d, T = dT.d;
     // the next tile's covariances travel in registers while the current tile is fitted
     double2 pre0 = make_double2(0.0, 0.0), pre1 = pre0;
     double pre_tail = 0.0;
     auto fetch = [&](int64_t tile) {
         if (tile >= ntiles) return;
         const int64_t b = tile * FIT_THREADS;
-        const int n3 = (int)min((int64_t)FIT_THREADS, M - b) * 3;
         const double2* g2 = reinterpret_cast<const double2*>(cov + b * 3);
-        if (tid < (n3 >> 1)) pre0 = __ldcs(g2 + tid);
-        if (tid + FIT_THREADS < (n3 >> 1)) pre1 = __ldcs(g2 + tid + FIT_THREADS);
-        if ((n3 & 1) && tid == 0) pre_tail = cov[b * 3 + n3 - 1];
+        if (M - b >= FIT_THREADS) {
+            pre0 = __ldcs(g2 + tid);
+            if (tid < HALF) pre1 = __ldcs(g2 + tid + FIT_THREADS);
+        } else {
+            const int n3 = (int)(M - b) * 3;
+            if (tid < (n3 >> 1)) pre0 = __ldcs(g2 + tid);
+            if (tid + FIT_THREADS < (n3 >> 1)) pre1 = __ldcs(g2 + tid + FIT_THREADS);
+            if ((n3 & 1) && tid == 0) pre_tail = cov[b * 3 + n3 - 1];
+        }
     };
     fetch(blockIdx.x);
+    // (scenario, offset in scenario) of the tile's first cell, advanced by the grid stride without divisions
+    const int64_t stride = (int64_t)gridDim.x * FIT_THREADS;
+    const int64_t stride_s = stride / per_s;
+    const uint32_t stride_rem = (uint32_t)(stride - stride_s * per_s);
+    int64_t tile_s = ((int64_t)blockIdx.x * FIT_THREADS) / per_s;
+    uint32_t tile_rem = (uint32_t)((int64_t)blockIdx.x * FIT_THREADS - tile_s * per_s);
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const int64_t base = tile * FIT_THREADS;
-        const int cnt = (int)min((int64_t)FIT_THREADS, M - base);
-        const int64_t tile_s = base / per_s;                       // CTA-uniform 64-bit division, once per tile
-        const uint32_t tile_rem = (uint32_t)(base - tile_s * per_s);
+        const bool full = M - base >= FIT_THREADS;
+        const int cnt = full ? FIT_THREADS : (int)(M - base);
         {
-            const int n3 = cnt * 3;
             double2* s2 = reinterpret_cast<double2*>(s_a);
-            if (tid < (n3 >> 1)) s2[tid] = pre0;
-            if (tid + FIT_THREADS < (n3 >> 1)) s2[tid + FIT_THREADS] = pre1;
-            if ((n3 & 1) && tid == 0) s_a[n3 - 1] = pre_tail;
+            if (full) {
+                s2[tid] = pre0;
+                if (tid < HALF) s2[tid + FIT_THREADS] = pre1;
+            } else {
+                const int n3 = cnt * 3;
+                if (tid < (n3 >> 1)) s2[tid] = pre0;
+                if (tid + FIT_THREADS < (n3 >> 1)) s2[tid + FIT_THREADS] = pre1;
+                if ((n3 & 1) && tid == 0) s_a[n3 - 1] = pre_tail;
+            }
         }
-        // mean and reference point of this thread's cell: in flight during the fixed point
+        // mean and reference point of this thread's cell: in flight during the fit
         double2 m2 = make_double2(0.0, 0.0), r = m2;
         if (tid < cnt) {
             m2 = __ldcs(reinterpret_cast<const double2*>(mu) + (base + tid));
-            // (scenario, timestep) of the cell: 32-bit arithmetic on the tile-local index
-            const uint32_t li = tile_rem + (uint32_t)tid;
-            const uint32_t ds = li / per_s32;
-            const uint32_t rem = li - ds * per_s32;
-            const int t = (int)((rem / (uint32_t)K) % (uint32_t)T);
+            const uint32_t li = tile_rem + (uint32_t)tid;          // < per_s + 256 < 2^31
+            const uint32_t ds = dPerS.div(li);
+            const uint32_t rem = li - ds * per_s;
+            const uint32_t row = dK.div(rem);                      // (o, t) row of the scenario
+            const uint32_t t = row - dT.div(row) * T;
             r = __ldg(reinterpret_cast<const double2*>(ref) + ((tile_s + ds) * T + t));
         }
         __syncthreads();
@@ -147,15 +182,16 @@ sweep_kernel(const double* __restrict__ cov, const double* __restrict__ mu, cons
         int status = 0, code = 0;
         if (tid < cnt) {
             a.xx *= chi_scale; a.xy *= chi_scale; a.yy *= chi_scale;
-            MvoeSpectrum sp = mvoe_spectrum_iso(a, r2);
+            MvoeSpectrum sp = mvoe_spectrum_iso<true>(a, r2);
             status = sp.status;
             int iters;
-            double beta = mvoe_beta(sp, tol, maxiter, accel, iters, status);
-            q = mvoe_q_iso(a, r2, beta);
+            double inv_beta;
+            const double beta = mvoe_beta(sp, tol, maxiter, accel, iters, status, &inv_beta);
+            q = mvoe_q_iso_inv(a, r2, beta, inv_beta);
             const double dy = r.y - m2.y;
-            const double m = -(r.x - m2.x) / dy;          // v8ideal:923
+            const double m = -(r.x - m2.x) * rcp_newton(dy);        // v8ideal:923
             if (dy == 0.0 && status == 0) status = CCMPC_ST_DEGENERATE_SLOPE;
-            TangentStar tg = tangent_star(m2.x, m2.y, q, 1.0, m, r.x, r.y);
+            TangentStar tg = tangent_star<true>(m2.x, m2.y, q, 1.0, m, r.x, r.y);
             n0 = -m;
             d = tg.d_star;
             if (tg.idx < 0) {
@@ -176,9 +212,25 @@ sweep_kernel(const double* __restrict__ cov, const double* __restrict__ mu, cons
             if (status_out) status_out[base + tid] = (uint8_t)status;
         }
         __syncthreads();
-        stage_out(q_out + base * 3, s_a, cnt * 3, tid, FIT_THREADS);
-        stage_out(nd_out + base * 3, s_n, cnt * 3, tid, FIT_THREADS);
+        if (full) {
+            double2* gq = reinterpret_cast<double2*>(q_out + base * 3);
+            double2* gn = reinterpret_cast<double2*>(nd_out + base * 3);
+            const double2* sq = reinterpret_cast<const double2*>(s_a);
+            const double2* sn = reinterpret_cast<const double2*>(s_n);
+            __stcs(gq + tid, sq[tid]);
+            __stcs(gn + tid, sn[tid]);
+            if (tid < HALF) {
+                __stcs(gq + tid + FIT_THREADS, sq[tid + FIT_THREADS]);
+                __stcs(gn + tid + FIT_THREADS, sn[tid + FIT_THREADS]);
+            }
+        } else {
+            stage_out(q_out + base * 3, s_a, cnt * 3, tid, FIT_THREADS);
+            stage_out(nd_out + base * 3, s_n, cnt * 3, tid, FIT_THREADS);
+        }
         __syncthreads();
+        tile_s += stride_s;
+        tile_rem += stride_rem;
+        if (tile_rem >= per_s) { tile_rem -= per_s; ++tile_s; }
     }
 }
 
@@ -422,9 +474,9 @@ extern "C" int ccmpc_mvoe_halfplane_sweep(const double* cov, const double* mu, c
     if (M == 0) return CCMPC_OK;
     CCMPC_REQUIRE(cov && mu && ref && q && nd && idx_side, "ccmpc_mvoe_halfplane_sweep: null pointer");
     CCMPC_REQUIRE((int64_t)O * T * K < ((int64_t)1 << 31) - FIT_THREADS, "ccmpc_mvoe_halfplane_sweep: O*T*K too large");
-    sweep_kernel<<<fit_grid(M), FIT_THREADS, 0, (cudaStream_t)stream>>>(cov, mu, ref, M, O, T, K, chi_scale,
-                                                                        footprint_r2, tol, maxiter, accel, q, nd,
-                                                                        idx_side, status);
+    sweep_kernel<<<fit_grid(M), FIT_THREADS, 0, (cudaStream_t)stream>>>(
+        cov, mu, ref, M, make_fastdiv((uint32_t)((int64_t)O * T * K)), make_fastdiv((uint32_t)K),
+        make_fastdiv((uint32_t)T), chi_scale, footprint_r2, tol, maxiter, accel, q, nd, idx_side, status);
     return check_launch("sweep_kernel");
 }
 

@@ -1,0 +1,47 @@
+#!/usr/bin/env python
+"""Tiny drivers for `ncu --set full` captures (one kernel, a few launches, no timing).
+
+  python tools/prof_driver.py sweep [accel]     # c4 MVOE sweep, accel = 0 | 1 | 2
+  python tools/prof_driver.py fit   [accel]     # c4-sized stand-alone footprint fit
+Run WITHOUT ncu first (must exit 0), then under
+  ncu --set full --clock-control none --import-source on -k regex:<kernel> -s 2 -c 1 -o gpurun_out/<name> python tools/prof_driver.py ...
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from ccmpc_b200 import ops  # noqa: E402
+from oracle import synth  # noqa: E402  (generators only)
+
+
+def c4_inputs(dev, S=4096, O=8, T=16, K=25, seed=4):
+    g = torch.Generator(device=dev).manual_seed(seed)
+    u = lambda lo, hi: torch.rand((S, O, T, K), generator=g, device=dev, dtype=torch.float64) * (hi - lo) + lo
+    sx, sy, rho = u(0.1, 3.0), u(0.1, 3.0), u(-0.8, 0.8)
+    cov = torch.stack([sx * sx, rho * sx * sy, sy * sy], dim=-1).contiguous()
+    mu = torch.stack([u(150, 200), u(-100, -60)], dim=-1).contiguous()
+    ref = torch.from_numpy(np.broadcast_to(synth.reference_trajectory(T), (S, T, 2)).copy()).to(dev)
+    ref[..., 1] += 30.0
+    return cov, mu, ref, -2.0 * np.log(0.05 / O / T)
+
+
+def main():
+    what = sys.argv[1] if len(sys.argv) > 1 else "sweep"
+    accel = int(sys.argv[2]) if len(sys.argv) > 2 else 2
+    dev = torch.device("cuda:0")
+    cov, mu, ref, chi = c4_inputs(dev)
+    out = None
+    for _ in range(4):
+        if what == "sweep":
+            out = ops.mvoe_halfplane_sweep(cov, mu, ref, chi, accel=accel, out=out)
+        else:
+            ops.mvoe_fit(cov.reshape(-1, 3), None, footprint_r2=3.4 ** 2, accel=accel, want_iters=False)
+    torch.cuda.synchronize()
+    print("ok", what, accel)
+
+
+if __name__ == "__main__":
+    main()
