@@ -58,7 +58,7 @@ def _traffic(kernel):
 class ClockSampler:
     """SM clock + throttle reasons during the timed region (NVML; nvidia-smi fallback)."""
 
-    def __init__(self, index=0, period=0.05):
+    def __init__(self, index=0, period=0.002):
         self.index, self.period = index, period
         self.samples, self.reasons, self.max_mhz = [], set(), None
         self._stop = threading.Event()
@@ -167,7 +167,7 @@ def run_reference(args):
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line))
+    emit(line)
     return 0
 
 
@@ -330,7 +330,7 @@ def run_ours(args):
         "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks.summary(),
         "also": also,
     }
-    print(json.dumps(line))
+    emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -495,7 +495,7 @@ def bench_also(torch, ops, midlevel, synth, dev, args, world=1, rank=0, dist=Non
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=int(os.environ.get("WORLD_SIZE", "1")))
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--n-per-cell", type=int, default=C3["n_per_cell"])
@@ -504,9 +504,25 @@ def main():
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3
+    # stdout carries exactly ONE JSON line: libraries that write to fd 1 on their own (NCCL prints its
+    # version banner there at communicator creation) are pointed at stderr until the line is printed
+    global _STDOUT_FD
+    sys.stdout.flush()
+    _STDOUT_FD = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         return run_reference(args)
     return run_ours(args)
+
+
+_STDOUT_FD = None
+
+
+def emit(line: dict):
+    sys.stdout.flush()
+    if _STDOUT_FD is not None:
+        os.dup2(_STDOUT_FD, 1)
+    print(json.dumps(line), flush=True)
 
 
 if __name__ == "__main__":
