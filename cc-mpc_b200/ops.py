@@ -403,6 +403,42 @@ def mc_rollout(mean, cov, cross, x0, n: int, Tsh: int, seed: int = 0, sample_off
     return traj, z_out, status, x0_out
 
 
+def gmm2d_sample(latent_pmf, mus, log_sigmas, corrs, n: int, log_pis=None, seed: int = 0, sample_offset: int = 0,
+                 noise=None, out=None, seed_dev=None):
+    """Stage 1 on the device (prediction.py:76-104; GMM2D.rsample of the missing Trajectron++ submodule).
+    latent_pmf [V,Z] f64, mus / log_sigmas [V,Z,T,G,2] f32, corrs [V,Z,T,G] f32, log_pis [V,Z,T,G] f32 (None iff
+    G = 1); noise = (u_z [V,N], u_c [V,N,T], eps [V,N,T,2]) f32 for deterministic parity, else Philox.
+    seed_dev: optional int64 [1] device word added to ``seed`` at run time (fresh draws per CUDA-graph replay).
+    -> (z [V,N] int32, predictions [V,N,T,2] float32): the inputs of group_by_mode."""
+    lib = _lib.load()
+    F32 = torch.float32
+    _chk(latent_pmf, F64, "latent_pmf"); _chk(mus, F32, "mus", (2,)); _chk(log_sigmas, F32, "log_sigmas", (2,))
+    _chk(corrs, F32, "corrs"); _chk(log_pis, F32, "log_pis")
+    if mus.dim() != 5:
+        raise ValueError("mus must be [V,Z,T,G,2]")
+    V, Z, T, G = mus.shape[:4]
+    if tuple(latent_pmf.shape) != (V, Z) or tuple(log_sigmas.shape) != (V, Z, T, G, 2) or \
+            tuple(corrs.shape) != (V, Z, T, G) or (log_pis is not None and tuple(log_pis.shape) != (V, Z, T, G)):
+        raise ValueError("gmm2d_sample: shape mismatch")
+    if G > 1 and log_pis is None:
+        raise ValueError("gmm2d_sample: G > 1 needs log_pis")
+    u_z = u_c = eps = None
+    if noise is not None:
+        u_z, u_c, eps = noise
+        _chk(u_z, F32, "u_z"); _chk(u_c, F32, "u_c"); _chk(eps, F32, "eps", (2,))
+        if tuple(u_z.shape) != (V, n) or tuple(u_c.shape) != (V, n, T) or tuple(eps.shape) != (V, n, T, 2):
+            raise ValueError("gmm2d_sample: noise must be ([V,N], [V,N,T], [V,N,T,2])")
+    if out is None:
+        out = (torch.empty((V, n), dtype=torch.int32, device=mus.device),
+               torch.empty((V, n, T, 2), dtype=F32, device=mus.device))
+    z, pred = out
+    _lib.check(lib.ccmpc_gmm2d_sample(_p(latent_pmf), _p(log_pis), _p(mus), _p(log_sigmas), _p(corrs), V, int(n), Z,
+                                      T, G, int(seed) & (2 ** 64 - 1), _p(seed_dev), int(sample_offset), _p(u_z), _p(u_c),
+                                      _p(eps),
+                                      _p(z), _p(pred), _stream()), "ccmpc_gmm2d_sample")
+    return z, pred
+
+
 def philox4x32(ctr, key):
     """Philox-4x32-10 known-answer hook: ctr [M,4] int32 bits, key [M,2] -> [M,4]."""
     lib = _lib.load()

@@ -258,6 +258,30 @@ int ccmpc_group_by_mode(const float* pred32, const double* pred64, const int32_t
                         void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------
+ * Stage 1  GMM2D sampling of the predictor's output distribution.  Stands in, at the
+ * boundary of generate_vehicle_latents (midlevel/prediction.py:76-104), for the two sampling
+ * calls whose code is in the Trajectron++ submodule that is absent from the reference tree
+ * (fireofearth/Trajectron-plus-plus @ 0e44e82): model.latent.sample_p (:81-83) and the
+ * GMM2D.rsample() at the end of model.p_y_xz (:85-86).  Per (vehicle v, sample n):
+ *   z ~ Cat(latent_pmf[v]);  per timestep t: g ~ Cat(softmax(log_pis[v,z,t]));
+ *   y = mu + L eps, L = [[sx, 0], [rho sy, sy sqrt(1 - rho^2)]], s = exp(log_sigmas)   (float32)
+ *   latent_pmf [V,Z] float64; log_pis [V,Z,T,G] (NULL allowed when G = 1), mus [V,Z,T,G,2],
+ *   log_sigmas [V,Z,T,G,2], corrs [V,Z,T,G] float32.
+ *   Randomness: Philox-4x32-10, counter = (sample_offset + n, v, draw), key = seed, so the
+ *   stream does not depend on how samples are sharded (seed_dev, nullable: a device word added
+ *   to seed at run time, so a captured CUDA graph draws fresh samples each replay); or, for deterministic parity,
+ *   supplied u_z [V,N], u_c [V,N,T] uniforms in [0,1) and eps [V,N,T,2] normals (all or none).
+ *   out: z_out [V,N] int32 (nullable), predictions [V,N,T,2] float32 - exactly the inputs
+ *   of ccmpc_group_by_mode (prediction.py:103-104).
+ */
+int ccmpc_gmm2d_sample(const double* latent_pmf, const float* log_pis, const float* mus,
+                       const float* log_sigmas, const float* corrs,
+                       int64_t V, int64_t N, int Z, int T, int G,
+                       uint64_t seed, const uint64_t* seed_dev, uint64_t sample_offset,
+                       const float* u_z, const float* u_c, const float* eps,
+                       int32_t* z_out, float* predictions, void* stream);
+
+/* ---------------------------------------------------------------------------
  * K1  Monte Carlo rollout.  Replaces MidlevelAgent.predict_ideal's loop body
  * (v8ideal:2662-2709) for C cells x n samples: per step t < Tsh
  *   A = C_{t+1,t} Sigma_t^-1 ; cond_cov = Sigma_{t+1} - A C^T ; L = chol(cond_cov)

@@ -548,6 +548,47 @@ def group_by_mode(predict, z, latent_pmf, pos_last, T, filter_pmf=0.1):
 # --------------------------------------------------------------------------
 # dataForCost_ref.py - closed-loop cost
 # --------------------------------------------------------------------------
+def gmm2d_sample(latent_pmf, log_pis, mus, log_sigmas, corrs, u_z, u_c, eps):
+    """z ~ Cat(latent_pmf), then GMM2D.rsample per (vehicle, sample, timestep) with SUPPLIED randomness.
+
+    Stands at prediction.py:81-86 (`model.latent.sample_p`, `model.p_y_xz` -> `GMM2D.rsample`); that code is in
+    the Trajectron++ submodule which is NOT in /root/reference (fireofearth/Trajectron-plus-plus @ 0e44e82), so
+    this follows the PUBLISHED Trajectron++ GMM2D (model/components/gmm2d.py): log_pis normalised by
+    logsumexp, sigma = exp(log_sigma), L = [[sx, 0], [rho sy, sy sqrt(1 - rho^2)]], y = mu + L eps for the
+    component drawn from Cat(pis).  PARITY UNPINNED (no reference code or vector to check against).
+    latent_pmf (V,Z); log_pis (V,Z,T,G) or None; mus, log_sigmas (V,Z,T,G,2); corrs (V,Z,T,G);
+    u_z (V,N), u_c (V,N,T) uniforms in [0,1); eps (V,N,T,2) normals.  float32 arithmetic like the model.
+    -> z (V,N) int32, predictions (V,N,T,2) float32."""
+    f = np.float32
+    mus, log_sigmas, corrs = np.asarray(mus, f), np.asarray(log_sigmas, f), np.asarray(corrs, f)
+    V, Z, T, G = mus.shape[:4]
+    N = u_z.shape[1]
+    z = np.zeros((V, N), np.int32)
+    pred = np.zeros((V, N, T, 2), f)
+    for v in range(V):
+        w = np.maximum(np.asarray(latent_pmf[v], np.float64), 0.0)
+        cum = (np.cumsum(w) / w.sum()).astype(f)
+        zz = np.minimum((np.asarray(u_z[v], f)[:, None] >= cum[None, :]).sum(axis=1), Z - 1)   # first k: u < cum_k
+        # bins with zero width after the last positive one cannot be hit; the last bin catches round-off
+        z[v] = zz
+        for t in range(T):
+            if G > 1:
+                lp = np.asarray(log_pis[v, zz, t], f)                       # (N,G)
+                p = np.exp(lp - lp.max(axis=1, keepdims=True), dtype=f)
+                acc = np.cumsum(p, axis=1, dtype=f)
+                target = (np.asarray(u_c[v, :, t], f) * acc[:, -1]).astype(f)
+                g = np.minimum((target[:, None] >= acc[:, :-1]).sum(axis=1), G - 1)
+            else:
+                g = np.zeros(N, int)
+            mu = mus[v, zz, t, g]
+            sg = np.exp(log_sigmas[v, zz, t, g], dtype=f)
+            rho = corrs[v, zz, t, g]
+            e1, e2 = np.asarray(eps[v, :, t, 0], f), np.asarray(eps[v, :, t, 1], f)
+            pred[v, :, t, 0] = mu[:, 0] + sg[:, 0] * e1
+            pred[v, :, t, 1] = mu[:, 1] + sg[:, 1] * (rho * e1 + np.sqrt(np.maximum(f(1) - rho * rho, f(0))) * e2)
+    return z, pred
+
+
 def episode_cost(X_star, U_star, goal=GOAL):
     """dataForCost_ref.py:198-232.
 

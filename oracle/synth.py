@@ -182,3 +182,27 @@ def mvoe_sweep_inputs(seed, S, O, T, K):
 def ego_plan(scene: GmmScene):
     """Ego plan = the reference trajectory."""
     return scene.ref_traj.copy()
+
+
+def gmm2d_params(scene: GmmScene, Z=25, slots=None, local=True):
+    """The scene as the predictor would hand it over (prediction.py:76-86): per vehicle a latent pmf over Z
+    discrete states and, per (latent, timestep), ONE-component GMM2D parameters in float32 (Trajectron++ emits
+    float32; vehicles use GMM_components = 1).  The scene's K modes occupy latent slots ``slots`` (default: the
+    first K), every other latent has pmf 0.  ``local``: means in scene-local coordinates (minus MINPOS), the
+    way predictions arrive before v8ideal:486 adds minpos.
+    -> latent_pmf (O,Z) f64, mus (O,Z,T,1,2) f32, log_sigmas (O,Z,T,1,2) f32, corrs (O,Z,T,1) f32."""
+    O, K, T = scene.O, scene.K, scene.T
+    slots = np.arange(K) if slots is None else np.asarray(slots)
+    pmf = np.zeros((O, Z))
+    mus = np.zeros((O, Z, T, 1, 2), np.float32)
+    log_sigmas = np.zeros((O, Z, T, 1, 2), np.float32)
+    corrs = np.zeros((O, Z, T, 1), np.float32)
+    sx = scene.chol[..., 0, 0]
+    sy = np.sqrt(scene.chol[..., 1, 0] ** 2 + scene.chol[..., 1, 1] ** 2)
+    for j, sl in enumerate(slots):
+        pmf[:, sl] = scene.weights[:, j]
+        mus[:, sl, :, 0, :] = scene.mean[:, j] - (MINPOS if local else 0.0)
+        log_sigmas[:, sl, :, 0, 0] = np.log(sx[:, j])
+        log_sigmas[:, sl, :, 0, 1] = np.log(sy[:, j])
+        corrs[:, sl, :, 0] = scene.chol[:, j, :, 1, 0] / sy[:, j]
+    return pmf, mus, log_sigmas, corrs

@@ -629,3 +629,74 @@ def test_step_plan_ingest_matches_host_grouped_plan(dev):
                 for k in ("nd", "ab", "idx_side", "status", "prob_lower", "mean", "cov", "At", "b0", "yaw_mean",
                           "counts", "viol", "aff_nd", "aff_offset_rhs", "aff_idx_side"):
                     np.testing.assert_array_equal(res[k][c], want[k][j], err_msg=f"{k} differs (v={v}, j={j})")
+
+
+# --------------------------------------------------------- stage 1: GMM2D sampling on the device
+@pytest.mark.parametrize("V,N,Z,T,G", [(3, 4001, 25, 8, 1), (2, 2500, 6, 7, 3), (1, 1, 1, 1, 1)])
+def test_gmm2d_sample_supplied_noise_matches_oracle(dev, V, N, Z, T, G):
+    """Deterministic mode: same uniforms / normals in, same latents and (float32) positions out as the oracle's
+    restatement of the published GMM2D.rsample (prediction.py:81-86; submodule absent => parity unpinned)."""
+    from ccmpc_b200 import ops
+    from oracle import restate
+    rng = np.random.default_rng(100 + G)
+    pmf = rng.dirichlet(np.full(Z, 0.3), size=V)
+    if Z > 1:
+        pmf[:, Z // 2] = 0.0                                       # an impossible latent is never drawn
+    mus = rng.uniform(-50, 50, (V, Z, T, G, 2)).astype(np.float32)
+    ls = rng.uniform(-2, 1, (V, Z, T, G, 2)).astype(np.float32)
+    rho = rng.uniform(-0.95, 0.95, (V, Z, T, G)).astype(np.float32)
+    lp = rng.normal(size=(V, Z, T, G)).astype(np.float32) if G > 1 else None
+    u_z = rng.random((V, N), dtype=np.float32)
+    u_c = rng.random((V, N, T), dtype=np.float32)
+    eps = rng.standard_normal((V, N, T, 2)).astype(np.float32)
+    f = lambda a: None if a is None else torch.from_numpy(a).to(dev)
+    z, pred = ops.gmm2d_sample(T_(pmf, dev), f(mus), f(ls), f(rho), N, log_pis=f(lp), noise=(f(u_z), f(u_c), f(eps)))
+    z_ref, pred_ref = restate.gmm2d_sample(pmf, lp, mus, ls, rho, u_z, u_c, eps)
+    np.testing.assert_array_equal(z.cpu().numpy(), z_ref)
+    if Z > 1:
+        assert not (z_ref == Z // 2).any()
+    got = pred.cpu().numpy()
+    bad = np.abs(got - pred_ref) > 1e-5 * (1.0 + np.abs(pred_ref))
+    # a component boundary can fall on different sides by one float32 ulp of exp(): at most a couple of draws
+    assert bad.any(axis=-1).sum() <= (2 if G > 1 else 0)
+
+
+def test_gmm2d_sample_philox_statistics_and_shard_invariance(dev):
+    """Philox mode: latent frequencies follow the pmf, per-(latent, timestep) sample moments follow the GMM
+    parameters within CLT bounds, the stream is independent of sharding, and seed_dev shifts the key."""
+    from ccmpc_b200 import ops
+    from oracle import synth
+    O, K, T, Z, N = 2, 4, 8, 25, 400_000
+    sc = synth.make_scene(31, O, K, T, flat=False)
+    pmf, mus, ls, rho = synth.gmm2d_params(sc, Z=Z, slots=[3, 7, 11, 20])
+    f = lambda a: torch.from_numpy(a).to(dev)
+    args = (T_(pmf, dev), f(mus), f(ls), f(rho))
+    z, pred = ops.gmm2d_sample(*args, N, seed=5)
+    zc, pc = z.cpu().numpy(), pred.cpu().numpy().astype(np.float64)
+    for o in range(O):
+        freq = np.bincount(zc[o], minlength=Z) / N
+        assert np.all(np.abs(freq - pmf[o]) < 5 * np.sqrt(pmf[o] * (1 - pmf[o]) / N) + 1e-12)
+        for j, slot in enumerate([3, 7, 11, 20]):
+            sel = pc[o][zc[o] == slot]
+            if len(sel) < 5000:
+                continue
+            for t in (0, T - 1):
+                S = sc.cov()[o, j, t]
+                m = sc.mean[o, j, t] - synth.MINPOS
+                assert np.all(np.abs(sel[:, t].mean(axis=0) - m) < 5 * np.sqrt(np.diag(S) / len(sel)) + 1e-4)
+                assert relerr(np.cov(sel[:, t].T), S) < 0.05
+            # independent draws per timestep (GMM2D.rsample draws eps per (sample, t))
+            assert abs(np.corrcoef(sel[:, 0, 0], sel[:, 1, 0])[0, 1]) < 0.02
+    # shards
+    za, pa = ops.gmm2d_sample(*args, N // 2, seed=5)
+    zb, pb = ops.gmm2d_sample(*args, N - N // 2, seed=5, sample_offset=N // 2)
+    assert torch.equal(torch.cat([za, zb], dim=1), z) and torch.equal(torch.cat([pa, pb], dim=1), pred)
+    # the device seed word is added to the key
+    sd = torch.tensor([2], dtype=torch.int64, device=dev)
+    z2, p2 = ops.gmm2d_sample(*args, N, seed=3, seed_dev=sd)
+    assert torch.equal(z2, z) and torch.equal(p2, pred)
+    z3, _ = ops.gmm2d_sample(*args, N, seed=6)
+    assert not torch.equal(z3, z)
+    # the sampler's output is the ingest format of group_by_mode
+    g = ops.group_by_mode(pred, z, T_(pmf, dev), minpos=tuple(synth.MINPOS))
+    assert int(g["offsets"][-1]) == O * N and not g["status"].any()

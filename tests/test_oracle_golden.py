@@ -157,3 +157,34 @@ def test_episode_cost_quirk():
     exp_u = U[1] @ R1 @ U[1] + du @ R2 @ du      # only tau = H-2 survives the first loop
     assert costU == pytest.approx(exp_u)
     assert cost == pytest.approx(6 * ((166 - 167.174698) ** 2 + (-81 + 81.759842) ** 2) + exp_u)
+
+
+def test_oracle_gmm2d_sample_restatement_is_a_gmm():
+    """The GMM2D sampling restatement (prediction.py:81-86; Trajectron++ submodule absent => parity unpinned):
+    latent frequencies follow the pmf, a never-weighted latent is never drawn, and per-latent sample moments
+    equal mu and L L^T of the published parameterisation."""
+    from oracle import restate
+    rng = np.random.default_rng(0)
+    V, Z, T, G, N = 1, 5, 3, 2, 200_000
+    pmf = np.array([[0.5, 0.0, 0.3, 0.2, 0.0]])
+    mus = rng.uniform(-5, 5, (V, Z, T, G, 2)).astype(np.float32)
+    ls = rng.uniform(-1, 0.5, (V, Z, T, G, 2)).astype(np.float32)
+    rho = rng.uniform(-0.9, 0.9, (V, Z, T, G)).astype(np.float32)
+    lp = np.log(np.array([0.25, 0.75], np.float32)) * np.ones((V, Z, T, G), np.float32) + 3.0   # unnormalised
+    z, pred = restate.gmm2d_sample(pmf, lp, mus, ls, rho, rng.random((V, N), dtype=np.float32),
+                                   rng.random((V, N, T), dtype=np.float32),
+                                   rng.standard_normal((V, N, T, 2)).astype(np.float32))
+    freq = np.bincount(z[0], minlength=Z) / N
+    assert np.all(np.abs(freq - pmf[0]) < 0.005) and freq[1] == 0 and freq[4] == 0
+    sel = pred[0][z[0] == 0][:, 1].astype(np.float64)                 # latent 0, timestep 1: 2-component mixture
+    w = np.array([0.25, 0.75])
+    m = (w[:, None] * mus[0, 0, 1]).sum(axis=0)
+    assert np.all(np.abs(sel.mean(axis=0) - m) < 0.02)
+    S = np.zeros((2, 2))
+    for g in range(G):
+        sx, sy = np.exp(ls[0, 0, 1, g].astype(np.float64))
+        r = float(rho[0, 0, 1, g])
+        L = np.array([[sx, 0.0], [r * sy, sy * np.sqrt(1 - r * r)]])
+        d = mus[0, 0, 1, g].astype(np.float64) - m
+        S += w[g] * (L @ L.T + np.outer(d, d))
+    assert np.abs(np.cov(sel.T) - S).max() < 0.03 * np.abs(S).max() + 0.02
