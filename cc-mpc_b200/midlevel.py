@@ -642,6 +642,7 @@ class StepPlan:
         self.lw_cell = _h2d(np.broadcast_to(np.asarray(bbox, dtype=np.float64), (self.C, 2)).copy(), dev)
         # ingest mode (from_predictions): raw float32 predictions + latents in, grouping done on the device
         self.ingest = ingest
+        self.sampler = None
         if ingest is not None:
             V, Nv, S = int(ingest["V"]), int(ingest["N"]), int(ingest["S"])
             self.host_pred = torch.zeros((V, Nv, self.T, 2), dtype=torch.float32).pin_memory()
@@ -653,6 +654,18 @@ class StepPlan:
             self.perm_dev = torch.empty((V, Nv), dtype=torch.int64, device=dev)
             self.group_ws = torch.empty(int(ops._lib.load().ccmpc_group_workspace_bytes(V, Nv)), dtype=torch.uint8,
                                         device=dev)
+            # sampler mode (from_gmm): the predictor's GMM2D parameters in, samples drawn on the device
+            self.sampler = ingest.get("sampler")
+            if self.sampler is not None:
+                G = int(self.sampler["G"])
+                f32 = torch.float32
+                self.host_gmm = dict(mus=torch.zeros((V, S, self.T, G, 2), dtype=f32).pin_memory(),
+                                     log_sigmas=torch.zeros((V, S, self.T, G, 2), dtype=f32).pin_memory(),
+                                     corrs=torch.zeros((V, S, self.T, G), dtype=f32).pin_memory(),
+                                     log_pis=torch.zeros((V, S, self.T, G), dtype=f32).pin_memory() if G > 1 else None,
+                                     seed=torch.zeros(1, dtype=torch.int64).pin_memory())
+                self.gmm = {k: (None if v is None else torch.empty(v.shape, dtype=v.dtype, device=dev))
+                            for k, v in self.host_gmm.items()}
         self.host_samples = (torch.empty((self.N, self.T, 2), dtype=torch.float64).pin_memory()
                              if ingest is None else None)
         self.host_ref = torch.empty((self.T, 2), dtype=torch.float64).pin_memory()
@@ -727,7 +740,8 @@ class StepPlan:
 
     @classmethod
     def from_predictions(cls, V: int, N: int, T: int, pos_last, prediction_horizon: int, S: int = 25,
-                         minpos=(0.0, 0.0), filter_pmf: float = 0.1, device=None, **kw) -> "StepPlan":
+                         minpos=(0.0, 0.0), filter_pmf: float = 0.1, device=None, sampler: Optional[dict] = None,
+                         **kw) -> "StepPlan":
         """Ingest mode: the planner hands over what ``generate_vehicle_latents`` returns (prediction.py:103-104) -
         ``predictions (V, N, T, 2)`` float32, ``z (V, N)``, ``latent_probs (V, S)`` - and the bucket-by-latent /
         rare-latent fold of v8ideal:486-494 + ovehicle.py:55-113 runs on the device inside the same CUDA graph.
@@ -741,9 +755,38 @@ class StepPlan:
         kw.setdefault("eps_ura", np.full((V, S), EPS_TOTAL / V))            # eps_ura[o, k] = eps / O (v8ideal:2920-2926)
         plan = cls(offs, co, ck, [S] * V, np.asarray(pos_last, dtype=np.float64).reshape(V, 2)[co], T,
                    prediction_horizon, device=device,
-                   ingest=dict(V=V, N=N, S=S, minpos=tuple(float(m) for m in minpos), filter_pmf=float(filter_pmf)),
+                   ingest=dict(V=V, N=N, S=S, minpos=tuple(float(m) for m in minpos), filter_pmf=float(filter_pmf),
+                               sampler=sampler),
                    **kw)
         return plan
+
+    @classmethod
+    def from_gmm(cls, V: int, N: int, T: int, pos_last, prediction_horizon: int, Z: int = 25, G: int = 1,
+                 seed: int = 0, **kw) -> "StepPlan":
+        """Sampler mode: the planner hands over the predictor's OUTPUT DISTRIBUTION - latent pmf (V, Z) and GMM2D
+        parameters per (vehicle, latent, timestep, component) - instead of N sampled trajectories per vehicle.
+        ``model.latent.sample_p`` + ``GMM2D.rsample`` (prediction.py:81-86), the D2H copy of the samples
+        (:88-93) and the bucket-by-latent loop (v8ideal:486-494) all run on the device inside one CUDA graph;
+        the step's H2D traffic is the parameters (KBs) rather than the sample tensor (MBs)."""
+        return cls.from_predictions(V, N, T, pos_last, prediction_horizon, S=Z,
+                                    sampler=dict(G=int(G), seed=int(seed)), **kw)
+
+    def run_gmm(self, latent_probs=None, mus=None, log_sigmas=None, corrs=None, log_pis=None, ref_traj=None,
+                step_seed: Optional[int] = None) -> dict:
+        """Sampler-mode step: GMM2D parameters in -> host rows out (one graph launch + one sync).  ``step_seed``
+        is added to the plan's seed on the device, so every replay of the captured graph draws fresh samples."""
+        if self.sampler is None:
+            raise RuntimeError("run_gmm needs a plan built by StepPlan.from_gmm")
+        for name, val in (("mus", mus), ("log_sigmas", log_sigmas), ("corrs", corrs), ("log_pis", log_pis)):
+            if val is not None:
+                if self.host_gmm[name] is None:
+                    raise ValueError(f"{name} given but the plan was built with G = 1")
+                self.host_gmm[name].copy_(torch.as_tensor(np.asarray(val, dtype=np.float32)).reshape(self.host_gmm[name].shape))
+        if latent_probs is not None:
+            self.host_pmf.copy_(torch.as_tensor(np.asarray(latent_probs, dtype=np.float64)).reshape(self.host_pmf.shape))
+        if step_seed is not None:
+            self.host_gmm["seed"][0] = int(step_seed)
+        return self.run(ref_traj=ref_traj)
 
     def run_predictions(self, predictions=None, z=None, latent_probs=None, ref_traj=None) -> dict:
         """Ingest-mode step: host predictions in -> host rows out (one graph launch + one sync)."""
@@ -782,7 +825,18 @@ class StepPlan:
                           filter_pmf=self.ingest.get("filter_pmf", 0.1), workspace=self.group_ws, out=self._group_out)
 
     def _enqueue_full(self):
-        if self.ingest is not None:
+        if self.sampler is not None:
+            # stage 1 on the device: a few KB of GMM2D parameters in, samples never cross PCIe (prediction.py:81-93)
+            for k, h in self.host_gmm.items():
+                if h is not None:
+                    self.gmm[k].copy_(h, non_blocking=True)
+            self.pmf.copy_(self.host_pmf, non_blocking=True)
+            self.ref.copy_(self.host_ref, non_blocking=True)
+            ops.gmm2d_sample(self.pmf, self.gmm["mus"], self.gmm["log_sigmas"], self.gmm["corrs"], self.pred.shape[1],
+                             log_pis=self.gmm["log_pis"], seed=int(self.sampler.get("seed", 0)),
+                             seed_dev=self.gmm["seed"], out=(self.z, self.pred))
+            self._enqueue_ingest()
+        elif self.ingest is not None:
             self.pred.copy_(self.host_pred, non_blocking=True)
             self.z.copy_(self.host_z, non_blocking=True)
             self.pmf.copy_(self.host_pmf, non_blocking=True)

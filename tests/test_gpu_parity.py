@@ -700,3 +700,36 @@ def test_gmm2d_sample_philox_statistics_and_shard_invariance(dev):
     # the sampler's output is the ingest format of group_by_mode
     g = ops.group_by_mode(pred, z, T_(pmf, dev), minpos=tuple(synth.MINPOS))
     assert int(g["offsets"][-1]) == O * N and not g["status"].any()
+
+
+def test_step_plan_sampler_mode_matches_ingest_plan(dev):
+    """StepPlan.from_gmm (GMM2D parameters in, sampling + grouping + constraint build in one CUDA graph) gives
+    exactly the rows of StepPlan.from_predictions fed with the samples the sampler draws for the same key, and
+    a new step_seed gives new draws without re-capturing the graph."""
+    from ccmpc_b200 import midlevel, ops
+    from oracle import synth
+    O, K, T, Z, N = 3, 3, 8, 25, 3000
+    sc = synth.make_scene(55, O, K, T)
+    pmf, mus, ls, rho = synth.gmm2d_params(sc, Z=Z, slots=[2, 9, 17])
+    plan = midlevel.StepPlan.from_gmm(O, N, T, sc.pos_last, prediction_horizon=T, Z=Z, minpos=tuple(synth.MINPOS),
+                                      device=dev, builder="both", seed=100)
+    ing = midlevel.StepPlan.from_predictions(O, N, T, sc.pos_last, prediction_horizon=T, S=Z,
+                                             minpos=tuple(synth.MINPOS), device=dev, builder="both")
+    f = lambda a: torch.from_numpy(a).to(dev)
+    prev = None
+    for step in (0, 1):
+        res = {k: v.copy() for k, v in plan.run_gmm(pmf, mus, ls, rho, ref_traj=sc.ref_traj, step_seed=step).items()}
+        z, pred = ops.gmm2d_sample(T_(pmf, dev), f(mus), f(ls), f(rho), N, seed=100 + step)
+        want = ing.run_predictions(pred.cpu().numpy(), z.cpu().numpy(), pmf, ref_traj=sc.ref_traj)
+        assert list(res["g_n_states"]) == [K] * O
+        for k in res:
+            np.testing.assert_array_equal(res[k], want[k], err_msg=f"{k} differs at step {step}")
+        if prev is not None:
+            assert not np.array_equal(prev["counts"], res["counts"]) or not np.array_equal(prev["mean"], res["mean"])
+        prev = res
+    # the Monte Carlo means converge on the GMM means (3000 samples / 3 modes)
+    for o in range(O):
+        for j in range(K):
+            c = o * Z + j
+            se = 5 * np.sqrt(np.diagonal(sc.cov()[o, j], axis1=-2, axis2=-1) / (N / K / 2))
+            assert np.all(np.abs(res["mean"][c] - sc.mean[o, j]) < se + 1e-3)
