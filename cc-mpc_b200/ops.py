@@ -403,6 +403,46 @@ def mc_rollout(mean, cov, cross, x0, n: int, Tsh: int, seed: int = 0, sample_off
     return traj, z_out, status, x0_out
 
 
+def risk_layout(T: int) -> dict:
+    """Offsets into the risk vector of mc_risk: n, coll[T], any, pen[T], d2s[T]."""
+    return dict(n=0, coll=1, any=1 + T, pen=2 + T, d2s=2 + 2 * T, len=3 * T + 2)
+
+
+def mc_risk_workspace(C: int, n: int, Tsh: int, device) -> torch.Tensor:
+    nbytes = _lib.load().ccmpc_mc_risk_workspace_bytes(int(C), int(n), int(Tsh))
+    return torch.empty(max(int(nbytes), 16), dtype=torch.uint8, device=device)
+
+
+def mc_risk(mean, cov, cross, x0, n: int, Tsh: int, ego, R: float = R_EV_OV, seed: int = 0, sample_offset: int = 0,
+            workspace=None, out=None):
+    """Fused predict_ideal rollout (v8ideal:2662-2709) + A9 evaluation, no trajectory tensor.  Arguments as
+    mc_rollout plus ego [Tsh,2] | [C,Tsh,2].  -> risk [C, 3 Tsh + 2] (risk_layout), status [C] uint8, x0_used [C,2].
+    The samples are the ones mc_rollout would write for the same (seed, sample_offset)."""
+    lib = _lib.load()
+    _chk(mean, F64, "mean", (2,)); _chk(cov, F64, "cov", (2, 2)); _chk(cross, F64, "cross", (2, 2))
+    _chk(x0, F64, "x0", (2,)); _chk(ego, F64, "ego", (2,))
+    C, Tm = mean.shape[0], mean.shape[1]
+    if tuple(cov.shape) != (C, Tm, 2, 2) or tuple(cross.shape) != (C, Tm, Tm, 2, 2) or \
+            (x0 is not None and tuple(x0.shape) != (C, 2)):
+        raise ValueError("mc_risk: moment shapes do not agree")
+    if tuple(ego.shape) == (Tsh, 2):
+        stride = 0
+    elif tuple(ego.shape) == (C, Tsh, 2):
+        stride = 2 * Tsh
+    else:
+        raise ValueError("ego must be [Tsh,2] or [C,Tsh,2]")
+    if workspace is None:
+        workspace = mc_risk_workspace(C, n, Tsh, mean.device)
+    risk = out if out is not None else _new((C, 3 * Tsh + 2), F64, mean)
+    status = _new((C,), U8, mean)
+    x0_out = _new((C, 2), F64, mean)
+    _lib.check(lib.ccmpc_mc_risk(_p(mean), _p(cov), _p(cross), Tm, _p(x0), C, int(n), int(Tsh),
+                                 int(seed) & 0xFFFFFFFFFFFFFFFF, int(sample_offset), _p(ego), stride, float(R),
+                                 _p(risk), _p(status), _p(x0_out), _p(workspace), workspace.numel(), _stream()),
+               "ccmpc_mc_risk")
+    return risk, status, x0_out
+
+
 def gmm2d_sample(latent_pmf, mus, log_sigmas, corrs, n: int, log_pis=None, seed: int = 0, sample_offset: int = 0,
                  noise=None, out=None, seed_dev=None):
     """Stage 1 on the device (prediction.py:76-104; GMM2D.rsample of the missing Trajectron++ submodule).

@@ -312,6 +312,27 @@ int ccmpc_mc_rollout(const double* mean, const double* cov, const double* cross,
 int ccmpc_episode_cost(const double* x_last, const double* U, const int32_t* lengths, int64_t E, int Hmax,
                        double goal_x, double goal_y, double* cost, double* costU, void* stream);
 
+/* ---------------------------------------------------------------------------
+ * K1+K6 fused  Monte Carlo collision-risk estimate without a trajectory tensor: the
+ * predict_ideal chain of ccmpc_mc_rollout (v8ideal:2662-2709; same arguments, same Philox
+ * stream, so sample i of cell c is bit-identical) with the A9 predicate of
+ * ccmpc_sample_sums applied to every (sample, timestep) in registers.
+ *   ego [Tsh,2] (ego_cell_stride = 0) or [C,Tsh,2] (stride = 2 Tsh); R = EV + OV radius.
+ *   out risk [C, 3 Tsh + 2] doubles per cell:
+ *     [0] n  [1,1+T) coll[t]  [1+T] any  [2+T,2+2T) pen[t]  [2+2T,2+3T) d2s[t]
+ *   (meanings as in the packed sums layout; counts are exact integers, so one fp64
+ *   all-reduce(sum) over sample shards is exact for them).
+ *   status [C] uint8, x0_out [C,2] (nullable) as in ccmpc_mc_rollout.
+ *   workspace: ccmpc_mc_risk_workspace_bytes(C, n, Tsh) bytes.
+ */
+size_t ccmpc_mc_risk_workspace_bytes(int64_t C, int64_t n, int Tsh);
+int ccmpc_mc_risk(const double* mean, const double* cov, const double* cross, int Tm,
+                  const double* x0, int64_t C, int64_t n, int Tsh,
+                  uint64_t seed, uint64_t sample_offset,
+                  const double* ego, int64_t ego_cell_stride, double R,
+                  double* risk, uint8_t* status, double* x0_out,
+                  void* workspace, size_t workspace_bytes, void* stream);
+
 /* Philox-4x32-10 known-answer hook: out[i] = philox(ctr[i], key[i]) (4 words each). */
 int ccmpc_philox4x32(const uint32_t* ctr, const uint32_t* key, int64_t M, uint32_t* out, void* stream);
 

@@ -733,3 +733,44 @@ def test_step_plan_sampler_mode_matches_ingest_plan(dev):
             c = o * Z + j
             se = 5 * np.sqrt(np.diagonal(sc.cov()[o, j], axis1=-2, axis2=-1) / (N / K / 2))
             assert np.all(np.abs(res["mean"][c] - sc.mean[o, j]) < se + 1e-3)
+
+
+# --------------------------------------------------------- fused rollout + evaluation (no trajectory tensor)
+@pytest.mark.parametrize("Tsh,n", [(16, 100_003), (8, 5000), (5, 777), (16, 1)])
+def test_mc_risk_equals_rollout_then_sample_sums(dev, Tsh, n):
+    """ccmpc_mc_risk draws the SAME samples as ccmpc_mc_rollout (same Philox counters) and applies the same A9
+    predicate as ccmpc_sample_sums: collision counts bit-exact, soft-cost sums to round-off, and shards add up."""
+    from ccmpc_b200 import ops
+    from oracle import synth
+    sc, mean, cov, cross = _scene_moments(9, 2, 3, Tsh + 1)
+    C = 6
+    rng = np.random.default_rng(1)
+    # ego plans close to each cell's mean path so that hits are common
+    ego = mean[:, 1:Tsh + 1] + rng.normal(size=(C, Tsh, 2)) * 1.5
+    args = (T_(mean, dev), T_(cov, dev), T_(cross, dev))
+    traj, _, st, x0 = ops.mc_rollout(*args, None, n, Tsh, seed=77)
+    offsets = torch.arange(C + 1, dtype=torch.int64, device=dev) * n
+    pivot = T_(mean[:, 1:Tsh + 1], dev)
+    sums = ops.sample_sums(traj.view(C * n, Tsh, 2), offsets, pivot, ego=T_(ego, dev))
+    risk, st2, x0b = ops.mc_risk(*args, None, n, Tsh, T_(ego, dev), seed=77)
+    assert torch.equal(st, st2) and torch.equal(x0, x0b)
+    L, R = ops.sums_layout(Tsh), ops.risk_layout(Tsh)
+    s, r = sums.cpu().numpy(), risk.cpu().numpy()
+    np.testing.assert_array_equal(r[:, R["n"]], s[:, L["n"]])
+    np.testing.assert_array_equal(r[:, R["coll"]:R["coll"] + Tsh], s[:, L["coll"]:L["coll"] + Tsh])
+    np.testing.assert_array_equal(r[:, R["any"]], s[:, L["any"]])
+    assert r[:, R["coll"]:R["coll"] + Tsh].sum() > 0 or n == 1
+    np.testing.assert_allclose(r[:, R["pen"]:R["pen"] + Tsh], s[:, L["pen"]:L["pen"] + Tsh], rtol=1e-11, atol=1e-9)
+    np.testing.assert_allclose(r[:, R["d2s"]:R["d2s"] + Tsh], s[:, L["d2s"]:L["d2s"] + Tsh], rtol=1e-11)
+    # one shared ego plan [Tsh,2] and two sample shards
+    if n > 1:
+        e1 = T_(ego[0], dev)
+        whole, _, _ = ops.mc_risk(*args, x0, n, Tsh, e1, seed=77)
+        a, _, _ = ops.mc_risk(*args, x0, n // 3, Tsh, e1, seed=77)
+        b, _, _ = ops.mc_risk(*args, x0, n - n // 3, Tsh, e1, seed=77, sample_offset=n // 3)
+        w, ab = whole.cpu().numpy(), (a + b).cpu().numpy()
+        np.testing.assert_array_equal(ab[:, :R["pen"]], w[:, :R["pen"]])
+        np.testing.assert_allclose(ab, w, rtol=1e-11, atol=1e-9)
+    # empty batch
+    z0, _, _ = ops.mc_risk(*args, None, 0, Tsh, T_(ego, dev))
+    assert not z0.any()
