@@ -355,6 +355,47 @@ def bench_also(torch, ops, midlevel, synth, dev, args, world=1, rank=0, dist=Non
     out = {}
     ev = lambda: torch.cuda.Event(enable_timing=True)
     peak, _ = _peaks()
+    # ---- c3 without a trajectory tensor: fused rollout + A9 evaluation (risk estimate only, no moments) --------
+    O3, K3, T3, n3 = C3["O"], C3["K"], C3["T"], args.n_per_cell
+    C3c = O3 * K3
+    sc3 = synth.make_scene(C3["seed"], O3, K3, T3 + 1)
+    m3, c3, x3 = (torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in sc3.moments())
+    m3, c3, x3 = m3.reshape(C3c, T3 + 1, 2), c3.reshape(C3c, T3 + 1, 2, 2), x3.reshape(C3c, T3 + 1, T3 + 1, 2, 2)
+    ego3 = torch.from_numpy(synth.reference_trajectory(T3)).to(dev)
+    ws3 = ops.mc_risk_workspace(C3c, n3, T3, dev)
+    risk = torch.empty((C3c, 3 * T3 + 2), dtype=torch.float64, device=dev)
+
+    def risk_step(i):
+        ops.mc_risk(m3, c3, x3, None, n3, T3, ego3, seed=1234 + i, sample_offset=rank * n3, workspace=ws3, out=risk)
+        if world > 1:
+            dist.all_reduce(risk, op=dist.ReduceOp.SUM)
+
+    for i in range(3):
+        risk_step(i)
+    torch.cuda.synchronize()
+    a, b = ev(), ev()
+    reps = 10
+    a.record()
+    for i in range(reps):
+        risk_step(3 + i)
+    b.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b) / reps
+    if world > 1:
+        mt = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(mt, op=dist.ReduceOp.MAX)
+        ms = float(mt.item())
+    assert int(risk[0, 0].item()) == n3 * world
+    out["mc_risk_fused"] = {
+        "metric": "mc_traj_steps_per_sec", "value": C3c * n3 * T3 * world / (ms * 1e-3), "unit": "traj-steps/s",
+        "ms": ms, "n_gpus": world,
+        "workload": f"c3 risk estimate only: {C3c} cells x {n3} samples x ph{T3} per GPU, Philox rollout + A9 collision "
+                    f"/ cost evaluation fused in registers, no trajectory tensor, no moments"
+                    f"{', fp64 all-reduce of the risk vectors' if world > 1 else ''}",
+        "roofline": {"bound": "issue", "algorithmic_hbm_bytes": 0,
+                     "note": "0 algorithmic HBM bytes: bound by instruction issue (Philox + Box-Muller + fp64 chain); "
+                             "the materialising path moves 32 B per trajectory-step"}}
+    del m3, c3, x3, ws3, risk
     # ---- c4: batched MVOE footprint fit + tangent half-plane sweep ---------------------------
     S, O, T, K = C4["S"], C4["O"], C4["T"], C4["K"]
     rng = np.random.default_rng(C4["seed"])

@@ -13,17 +13,18 @@
 //     [0] n   [1, 1+T) coll[t]   [1+T] any   [2+T, 2+2T) pen[t]   [2+2T, 2+3T) d2s[t]
 // with the meanings of the packed sums layout (ccmpc.h).  Counts are integers held exactly in doubles: CTA
 // partials are added in a fixed order by risk_finalize_kernel, and one fp64 all-reduce over sample shards is
-// exact for them.  pen[t] is accumulated with shared-memory fp64 atomics on the (rare) hit path, so its last
-// bits depend on the order hits arrive; coll / any / n are exact and d2s is deterministic for a given grid.
+// exact for them; every sum is accumulated per thread and reduced in a fixed order, so the result is
+// deterministic for a given grid.
 #include "rollout.cuh"
 
 namespace ccmpc {
 
 constexpr int RK_THREADS = 128;
 constexpr int RK_WARPS = RK_THREADS / 32;
+constexpr int RK_CTAS_PER_SM = 5;     // 80 registers; per-thread accumulators live in shared memory (40 KB per CTA at ph16)
 
 template <int TSH>
-__global__ void __launch_bounds__(RK_THREADS, 4)
+__global__ void __launch_bounds__(RK_THREADS, RK_CTAS_PER_SM)
 risk_kernel(const double* __restrict__ mean, const double* __restrict__ cov, const double* __restrict__ cross, int Tm,
             const double* __restrict__ x0, int64_t n, int Tsh_rt, uint32_t seed_lo, uint32_t seed_hi,
             uint64_t sample_offset, const double* __restrict__ ego, int64_t ego_cell_stride, double r2,
@@ -35,24 +36,27 @@ risk_kernel(const double* __restrict__ mean, const double* __restrict__ cov, con
     StepParams* sp = reinterpret_cast<StepParams*>(smem);                 // [Tsh]
     double2* s_ego = reinterpret_cast<double2*>(smem + Tsh * SP_D);        // [Tsh]
     double* s_red = smem + Tsh * SP_D + 2 * Tsh;                           // [RK_WARPS][L]
-    double* s_pen = s_red + RK_WARPS * L;                                  // [Tsh] hit-path accumulators
     __shared__ double s_x0[2];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t c = blockIdx.y;
 
     rollout_setup<RK_THREADS>(mean, cov, cross, Tm, x0, c, Tsh, seed_lo, seed_hi, sp, s_x0, status, x0_out, tid);
-    if (tid < Tsh) {
-        s_ego[tid] = reinterpret_cast<const double2*>(ego + c * ego_cell_stride)[tid];
-        s_pen[tid] = 0.0;
-    }
+    if (tid < Tsh) s_ego[tid] = reinterpret_cast<const double2*>(ego + c * ego_cell_stride)[tid];
     __syncthreads();
 
-    // per-thread accumulators in registers: hit counts and sum d^2 per step; the penetration sum is only
-    // touched on a hit and lives in shared memory (fp64 red.shared), which keeps the kernel at 128 registers
-    uint32_t coll[TMAX];
-    double d2s[TMAX];
-#pragma unroll
-    for (int t = 0; t < TMAX; ++t) { coll[t] = 0; d2s[t] = 0.0; }
+    // per-thread accumulators in SHARED memory, [t][tid] (conflict-free): sum d^2 is one LDS + DADD + STS per
+    // step, hit counts and the penetration sum are only touched on a hit (a shared fp64 atomicAdd per hit was
+    // measured first: it is a CAS loop, 32-way serialised inside a warp, and cells the ego drives through ran 3x longer).  Keeping them out of the register
+    // file (48 registers at ph16) doubles the resident warps, which is what hides the Philox / MUFU / fp64-chain
+    // latencies of this issue-bound kernel.
+    double* s_d2s = s_red + RK_WARPS * L;                                  // [Tsh][RK_THREADS]
+    double* s_pen = s_d2s + Tsh * RK_THREADS;                              // [Tsh][RK_THREADS]
+    uint32_t* s_coll = reinterpret_cast<uint32_t*>(s_pen + Tsh * RK_THREADS);   // [Tsh][RK_THREADS]
+    for (int t = 0; t < Tsh; ++t) {
+        s_d2s[t * RK_THREADS + tid] = 0.0;
+        s_pen[t * RK_THREADS + tid] = 0.0;
+        s_coll[t * RK_THREADS + tid] = 0u;
+    }
     uint32_t any_cnt = 0, n_cnt = 0;
 
     for (int64_t i = (int64_t)blockIdx.x * RK_THREADS + tid; i < n; i += (int64_t)gridDim.x * RK_THREADS) {
@@ -71,14 +75,14 @@ risk_kernel(const double* __restrict__ mean, const double* __restrict__ cov, con
             const double2 e = s_ego[t];
             const double ex = __dsub_rn(e.x, x), ey = __dsub_rn(e.y, y);
             const double d2 = __dadd_rn(__dmul_rn(ex, ex), __dmul_rn(ey, ey));
-            d2s[t] += d2;
+            s_d2s[t * RK_THREADS + tid] += d2;
             if (d2 < r2) {
-                ++coll[t];
-                atomicAdd(&s_pen[t], r2 - d2);
+                ++s_coll[t * RK_THREADS + tid];
+                s_pen[t * RK_THREADS + tid] += r2 - d2;
                 hit_any = true;
             }
         };
-#pragma unroll
+#pragma unroll 2
         for (int t2 = 0; t2 < (TSH > 0 ? (TSH + 1) / 2 : CCMPC_MAX_T / 2); ++t2) {
             const int t = 2 * t2;
             if (TSH == 0 && t >= Tsh) break;
@@ -112,9 +116,9 @@ risk_kernel(const double* __restrict__ mean, const double* __restrict__ cov, con
 #pragma unroll
     for (int t = 0; t < TMAX; ++t) {
         if (TSH == 0 && t >= Tsh) break;
-        const uint32_t cc = wsum_u(coll[t]);
-        const double dd = wsum_d(d2s[t]);
-        if (lane == 0) { wr[1 + t] = (double)cc; wr[2 + Tsh + t] = 0.0; wr[2 + 2 * Tsh + t] = dd; }
+        const uint32_t cc = wsum_u(s_coll[t * RK_THREADS + tid]);
+        const double dd = wsum_d(s_d2s[t * RK_THREADS + tid]), pp = wsum_d(s_pen[t * RK_THREADS + tid]);
+        if (lane == 0) { wr[1 + t] = (double)cc; wr[2 + Tsh + t] = pp; wr[2 + 2 * Tsh + t] = dd; }
     }
     __syncthreads();
     double* out = partial + (c * gridDim.x + blockIdx.x) * L;
@@ -122,7 +126,6 @@ risk_kernel(const double* __restrict__ mean, const double* __restrict__ cov, con
         double v = 0.0;
 #pragma unroll
         for (int w = 0; w < RK_WARPS; ++w) v += s_red[w * L + e];
-        if (e >= 2 + Tsh && e < 2 + 2 * Tsh) v = s_pen[e - 2 - Tsh];
         out[e] = v;
     }
 }
@@ -138,9 +141,9 @@ __global__ void risk_finalize_kernel(const double* __restrict__ partial, int npa
 }
 
 static int risk_grid_x(int64_t n, int64_t C) {
-    // one wave: 148 SMs x 4 resident 128-thread CTAs (125 registers), split evenly over the cells, never more
-    // than the samples need
-    int64_t want = (148 * 4) / C;
+    // one wave: 148 SMs x RK_CTAS_PER_SM resident 128-thread CTAs, split evenly over the cells, never more than
+    // the samples need
+    int64_t want = (148 * RK_CTAS_PER_SM) / C;
     int64_t need = (n + RK_THREADS - 1) / RK_THREADS;
     int64_t g = want < need ? want : need;
     return (int)(g < 1 ? 1 : g);
@@ -180,7 +183,8 @@ extern "C" int ccmpc_mc_risk(const double* mean, const double* cov, const double
     }
     const int gx = risk_grid_x(n, C);
     dim3 grid((unsigned)gx, (unsigned)C);
-    const size_t smem = ((size_t)Tsh * SP_D + 3 * (size_t)Tsh + (size_t)RK_WARPS * L) * sizeof(double);
+    const size_t smem = ((size_t)Tsh * SP_D + 2 * (size_t)Tsh + (size_t)RK_WARPS * L) * sizeof(double) +
+                        (size_t)Tsh * RK_THREADS * (2 * sizeof(double) + sizeof(uint32_t));
     double* partial = reinterpret_cast<double*>(workspace);
 #define CCMPC_RK_LAUNCH(TSH)                                                                                   \
     risk_kernel<TSH><<<grid, RK_THREADS, smem, st>>>(mean, cov, cross, Tm, x0, n, Tsh, (uint32_t)seed,           \

@@ -32,6 +32,22 @@ def main():
     what = sys.argv[1] if len(sys.argv) > 1 else "sweep"
     accel = int(sys.argv[2]) if len(sys.argv) > 2 else 2
     dev = torch.device("cuda:0")
+    if what in ("risk", "rollout"):
+        O, K, T, n = 8, 4, 16, 250_000
+        C = O * K
+        sc = synth.make_scene(3, O, K, T + 1)
+        m, c, x = (torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in sc.moments())
+        m, c, x = m.reshape(C, T + 1, 2), c.reshape(C, T + 1, 2, 2), x.reshape(C, T + 1, T + 1, 2, 2)
+        ego = torch.from_numpy(synth.reference_trajectory(T)).to(dev)
+        traj = torch.empty((C, n, T, 2), dtype=torch.float64, device=dev) if what == "rollout" else None
+        for i in range(4):
+            if what == "risk":
+                ops.mc_risk(m, c, x, None, n, T, ego, seed=i)
+            else:
+                ops.mc_rollout(m, c, x, None, n, T, seed=i, out=traj)
+        torch.cuda.synchronize()
+        print("ok", what)
+        return
     cov, mu, ref, chi = c4_inputs(dev)
     out = None
     for _ in range(4):
