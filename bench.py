@@ -327,10 +327,10 @@ def run_ours(args):
 
     cpu = None
     if not args.skip_cpu:
-        ncpu = 100_000
-        v, dt = cpu_mc_throughput(ncpu, T, 1, 2)
+        ncpu, ncells = 125_000, 12                      # ~10 s of single-core work: a bounded sample of c3
+        v, dt = cpu_mc_throughput(ncpu, T, 1, ncells)
         cpu = {"value": v, "unit": UNIT, "cores": 1, "kind": "port",
-               "sample": f"2 cells x {ncpu} samples x ph{T} ({dt:.1f} s; oracle/restate.py: predict_ideal body + "
+               "sample": f"{ncells} cells x {ncpu} samples x ph{T} ({dt:.1f} s; oracle/restate.py: predict_ideal body + "
                          f"A9 counts + save_moments)"}
 
     line = {
