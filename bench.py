@@ -439,6 +439,38 @@ def bench_also(torch, ops, midlevel, synth, dev, args, world=1, rank=0, dist=Non
                          "unit": "GB/s", "frac": M / world * bytes_per / (ms * 1e-3) / 1e9 / peak,
                          "bytes_per_fit": bytes_per, "per": "GPU"}}
     assert int(bufs[3].max().item()) == 0, "MVOE sweep reported a failed cell"
+    # ---- A6 alone: compute_mvoe (makeconstraint:7-38) in its general two-matrix form on the same 13.1 M pairs
+    #      (Sigma1 = the mode covariances, Sigma2 = the same set rolled by one scenario)
+    s1 = cov.reshape(-1, 3)
+    s2 = torch.roll(cov, 1, dims=0).reshape(-1, 3).contiguous()
+    for accel in (0, 2):
+        for _ in range(3):
+            fit = ops.mvoe_fit(s1, s2, accel=accel, want_iters=False)
+        torch.cuda.synchronize()
+        a, b = ev(), ev()
+        a.record()
+        for _ in range(10):
+            fit = ops.mvoe_fit(s1, s2, accel=accel, want_iters=False)
+        b.record()
+        torch.cuda.synchronize()
+        ms = a.elapsed_time(b) / 10
+        if world > 1:
+            mt = torch.tensor([ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(mt, op=dist.ReduceOp.MAX)
+            ms = float(mt.item())
+        M = S * O * T * K * world
+        bytes_per = 48 + 24 + 8 + 1
+        out["mvoe_fit" if accel == 0 else "mvoe_fit_direct"] = {
+            "metric": "mvoe_fits_per_sec", "value": M / (ms * 1e-3), "unit": "fits/s", "ms": ms, "fits": M,
+            "workload": f"compute_mvoe(Sigma1, Sigma2) on {S * O * T * K} SPD pairs per GPU (two symmetric 2x2 in, "
+                        f"Q + beta + status out)", "n_gpus": world,
+            "iterate": ("reference sequence from beta = 1",
+                        "", "Newton on the stationarity cubic, accepted by one reference-map step at tol 1e-8")[accel],
+            "roofline": {"bound": "hbm", "achieved": M / world * bytes_per / (ms * 1e-3) / 1e9, "peak": peak,
+                         "unit": "GB/s", "frac": M / world * bytes_per / (ms * 1e-3) / 1e9 / peak,
+                         "bytes_per_fit": bytes_per, "per": "GPU"}}
+    assert int(fit[3].max().item()) == 0
+    del s1, s2, fit
     del cov, mu, ref, bufs
     if rank != 0:
         return out

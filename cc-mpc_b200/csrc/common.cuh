@@ -230,6 +230,11 @@ __device__ __forceinline__ Sym2 mvoe_q_iso(const Sym2& s1, double r2, double bet
     return Sym2{fma(a, s1.xx, b), a * s1.xy, fma(a, s1.yy, b)};
 }
 
+__device__ __forceinline__ Sym2 mvoe_q_inv(const Sym2& s1, const Sym2& s2, double beta, double inv_beta) {
+    double a = 1.0 + inv_beta, b = 1.0 + beta;
+    return Sym2{fma(a, s1.xx, b * s2.xx), fma(a, s1.xy, b * s2.xy), fma(a, s1.yy, b * s2.yy)};
+}
+
 // same with 1/beta supplied by the solver (mvoe_beta's inv_beta)
 __device__ __forceinline__ Sym2 mvoe_q_iso_inv(const Sym2& s1, double r2, double beta, double inv_beta) {
     double a = 1.0 + inv_beta, b = (1.0 + beta) * r2;

@@ -40,6 +40,46 @@ __device__ __forceinline__ void stage_out(double* __restrict__ g, const double* 
 // Algorithmic HBM bytes per fit: 24 (Sigma1) + 24 (Sigma2, 0 for the footprint
 // form) in, 24 (Q) + 8 (beta) out.
 // ---------------------------------------------------------------------------
+// full tile = FIT_THREADS sym3 records = 384 double2: thread tid moves elements tid and (tid < 128) tid + 256
+__device__ __forceinline__ void tile_load(const double* __restrict__ g, int cnt, int tid, double2& p0, double2& p1,
+                                          double& tail) {
+    const double2* g2 = reinterpret_cast<const double2*>(g);
+    if (cnt == FIT_THREADS) {
+        p0 = __ldcs(g2 + tid);
+        if (tid < FIT_THREADS / 2) p1 = __ldcs(g2 + tid + FIT_THREADS);
+    } else {
+        const int n3 = cnt * 3;
+        if (tid < (n3 >> 1)) p0 = __ldcs(g2 + tid);
+        if (tid + FIT_THREADS < (n3 >> 1)) p1 = __ldcs(g2 + tid + FIT_THREADS);
+        if ((n3 & 1) && tid == 0) tail = g[n3 - 1];
+    }
+}
+
+__device__ __forceinline__ void tile_to_smem(double* s, int cnt, int tid, const double2& p0, const double2& p1,
+                                             double tail) {
+    double2* s2 = reinterpret_cast<double2*>(s);
+    if (cnt == FIT_THREADS) {
+        s2[tid] = p0;
+        if (tid < FIT_THREADS / 2) s2[tid + FIT_THREADS] = p1;
+    } else {
+        const int n3 = cnt * 3;
+        if (tid < (n3 >> 1)) s2[tid] = p0;
+        if (tid + FIT_THREADS < (n3 >> 1)) s2[tid + FIT_THREADS] = p1;
+        if ((n3 & 1) && tid == 0) s[n3 - 1] = tail;
+    }
+}
+
+__device__ __forceinline__ void tile_store(double* __restrict__ g, const double* s, int cnt, int tid) {
+    if (cnt == FIT_THREADS) {
+        double2* g2 = reinterpret_cast<double2*>(g);
+        const double2* s2 = reinterpret_cast<const double2*>(s);
+        __stcs(g2 + tid, s2[tid]);
+        if (tid < FIT_THREADS / 2) __stcs(g2 + tid + FIT_THREADS, s2[tid + FIT_THREADS]);
+    } else {
+        stage_out(g, s, cnt * 3, tid, FIT_THREADS);
+    }
+}
+
 template <bool ISO>
 __global__ void __launch_bounds__(FIT_THREADS)
 mvoe_fit_kernel(const double* __restrict__ sigma1, const double* __restrict__ sigma2, double r2, int64_t M,
@@ -49,39 +89,55 @@ mvoe_fit_kernel(const double* __restrict__ sigma1, const double* __restrict__ si
     __shared__ __align__(16) double s_b[ISO ? 2 : FIT_THREADS * 3];
     const int tid = threadIdx.x;
     const int64_t ntiles = (M + FIT_THREADS - 1) / FIT_THREADS;
+    // the next tile's records travel in registers while the current tile is fitted
+    double2 a0 = make_double2(0.0, 0.0), a1 = a0, b0 = a0, b1 = a0;
+    double at = 0.0, bt = 0.0;
+    auto fetch = [&](int64_t tile) {
+        if (tile >= ntiles) return;
+        const int64_t base = tile * FIT_THREADS;
+        const int cnt = (int)min((int64_t)FIT_THREADS, M - base);
+        tile_load(sigma1 + base * 3, cnt, tid, a0, a1, at);
+        if (!ISO) tile_load(sigma2 + base * 3, cnt, tid, b0, b1, bt);
+    };
+    fetch(blockIdx.x);
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
         const int64_t base = tile * FIT_THREADS;
         const int cnt = (int)min((int64_t)FIT_THREADS, M - base);
-        stage_in(sigma1 + base * 3, s_a, cnt * 3, tid, FIT_THREADS);
-        if (!ISO) stage_in(sigma2 + base * 3, s_b, cnt * 3, tid, FIT_THREADS);
+        tile_to_smem(s_a, cnt, tid, a0, a1, at);
+        if (!ISO) tile_to_smem(s_b, cnt, tid, b0, b1, bt);
         __syncthreads();
+        Sym2 a{1.0, 0.0, 1.0}, b{1.0, 0.0, 1.0};
+        if (tid < cnt) {
+            a = ld_sym3(s_a + tid * 3);
+            if (!ISO) b = ld_sym3(s_b + tid * 3);
+        }
+        fetch(tile + gridDim.x);
         double beta = 0.0;
         int iters = 0, status = 0;
         Sym2 q{0.0, 0.0, 0.0};
         if (tid < cnt) {
-            Sym2 a = ld_sym3(s_a + tid * 3);
+            double inv_beta;
             if (ISO) {
                 MvoeSpectrum sp = mvoe_spectrum_iso(a, r2);
                 status = sp.status;
-                beta = mvoe_beta(sp, tol, maxiter, accel, iters, status);
-                q = mvoe_q_iso(a, r2, beta);
+                beta = mvoe_beta(sp, tol, maxiter, accel, iters, status, &inv_beta);
+                q = mvoe_q_iso_inv(a, r2, beta, inv_beta);
             } else {
-                Sym2 b = ld_sym3(s_b + tid * 3);
                 MvoeSpectrum sp = mvoe_spectrum(a, b);
                 status = sp.status;
-                beta = mvoe_beta(sp, tol, maxiter, accel, iters, status);
-                q = mvoe_q(a, b, beta);
+                beta = mvoe_beta(sp, tol, maxiter, accel, iters, status, &inv_beta);
+                q = mvoe_q_inv(a, b, beta, inv_beta);
             }
         }
         __syncthreads();
         if (tid < cnt) {
             st_sym3(s_a + tid * 3, q);
-            beta_out[base + tid] = beta;
+            __stcs(beta_out + base + tid, beta);
             if (iters_out) iters_out[base + tid] = iters;
             if (status_out) status_out[base + tid] = (uint8_t)status;
         }
         __syncthreads();
-        stage_out(q_out + base * 3, s_a, cnt * 3, tid, FIT_THREADS);
+        tile_store(q_out + base * 3, s_a, cnt, tid);
         __syncthreads();
     }
 }
