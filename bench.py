@@ -505,6 +505,31 @@ def bench_also(torch, ops, midlevel, synth, dev, args, world=1, rank=0, dist=Non
                     "L4 polytopes -> violation counts; L2 flushed between iterations",
         "rows": int(step.C * step.P), "launches_per_step": step.launches_per_step}
     del step
+    # c2 from the predictor's output distribution: 25 latent states per obstacle (flat pmf, all kept), GMM2D
+    # parameters H2D, sampling + grouping + the same Minkowski build on the device, rows D2H
+    gpmf, gmus, gls, grho = synth.gmm2d_params(sc, Z=C2["K"])
+    step = midlevel.StepPlan.from_gmm(C2["O"], C2["N"], C2["T"], sc.pos_last, prediction_horizon=C2["T"], Z=C2["K"],
+                                      minpos=synth.MINPOS, filter_pmf=0.0, device=dev, seed=C2["seed"])
+    for i in range(10):
+        res = step.run_gmm(gpmf, gmus, gls, grho, ref_traj=ref_traj, step_seed=i)
+    assert int(res["g_n_states"].sum()) == C2["O"] * C2["K"]
+    times_s = []
+    for i in range(100):
+        flush.fill_(1)
+        step.host_gmm["seed"][0] = 10 + i
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        res = step.run(ref_traj=ref_traj)
+        times_s.append((time.perf_counter() - t0) * 1e3)
+    ok = res["status"][res["g_offsets"][1:] > res["g_offsets"][:-1]]
+    out["constraint_build_c2_sampler"] = {
+        "metric": "mpc_step_constraint_build_p50_ms", "unit": "ms", "higher_is_better": False,
+        "p50_host_to_host": float(np.percentile(times_s, 50)), "p95_host_to_host": float(np.percentile(times_s, 95)),
+        "failed_rows": int((ok != 0).sum()),
+        "workload": "c2 from GMM2D parameters: O=4 x 25 latent states, ph8, np5000 drawn on the device (Philox) -> "
+                    "grouping -> sums+counts -> Minkowski half-planes -> L4 -> violation counts; L2 flushed",
+        "launches_per_step": step.launches_per_step}
+    del step
     # ---- c5: receding-horizon replay, 200 MPC steps x 8 obstacles, ph16, np20000 (affine builder) ----
     sc = synth.make_scene(C5["seed"], C5["O"], C5["K"], C5["T"])
     z, pos = synth.sample_scene(sc, C5["N"], C5["seed"])

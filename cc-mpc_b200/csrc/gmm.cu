@@ -49,12 +49,16 @@ gmm2d_sample_kernel(const double* __restrict__ latent_pmf, const float* __restri
                     int32_t* __restrict__ z_out, float* __restrict__ pred) {
     extern __shared__ float s_cum[];                          // [Z] cumulative latent pmf of this vehicle
     const int v = blockIdx.y;
+    // cumulative pmf: loads in parallel, the running sum in the oracle's sequential order (bit-identical bins)
+    double* s_w = reinterpret_cast<double*>(s_cum + ((Z + 1) & ~1));
+    for (int k = threadIdx.x; k < Z; k += GMM_THREADS) s_w[k] = fmax(latent_pmf[(int64_t)v * Z + k], 0.0);
+    __syncthreads();
     if (threadIdx.x == 0) {
         double tot = 0.0;
-        for (int k = 0; k < Z; ++k) tot += fmax(latent_pmf[(int64_t)v * Z + k], 0.0);
+        for (int k = 0; k < Z; ++k) tot += s_w[k];
         double acc = 0.0;
         for (int k = 0; k < Z; ++k) {
-            acc += fmax(latent_pmf[(int64_t)v * Z + k], 0.0);
+            acc += s_w[k];
             s_cum[k] = (float)(acc / tot);
         }
     }
@@ -62,8 +66,7 @@ gmm2d_sample_kernel(const double* __restrict__ latent_pmf, const float* __restri
     if (seed_dev) seed += *seed_dev;              // per-step key read on the device: a captured graph replays with new draws
     const uint32_t seed_lo = (uint32_t)seed, seed_hi = (uint32_t)(seed >> 32);
     const int TP = (T + 1) >> 1;
-    const int64_t i = (int64_t)blockIdx.x * GMM_THREADS + threadIdx.x;
-    if (i >= N * TP) return;
+    for (int64_t i = (int64_t)blockIdx.x * GMM_THREADS + threadIdx.x; i < N * TP; i += (int64_t)gridDim.x * GMM_THREADS) {
     const int64_t n = i / TP;
     const int tp = (int)(i - n * TP);
     const uint64_t gi = sample_offset + (uint64_t)n;
@@ -105,7 +108,7 @@ gmm2d_sample_kernel(const double* __restrict__ latent_pmf, const float* __restri
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
         const int t = t0 + j;
-        if (t >= T) break;
+        if (t >= T) continue;
         const int64_t row = (((int64_t)v * Z + z) * T + t) * G;
         int g = 0;
         if (G > 1) {
@@ -138,6 +141,7 @@ gmm2d_sample_kernel(const double* __restrict__ latent_pmf, const float* __restri
         dst[1] = out[1];
         if (t0 + 1 < T) { dst[2] = out[2]; dst[3] = out[3]; }
     }
+    }   // grid-stride loop
 }
 
 }  // namespace ccmpc
@@ -157,11 +161,12 @@ extern "C" int ccmpc_gmm2d_sample(const double* latent_pmf, const float* log_pis
     const bool any = u_z || u_c || eps, all = u_z && u_c && eps;
     CCMPC_REQUIRE(!any || all, "ccmpc_gmm2d_sample: supply u_z, u_c and eps together or none of them");
     const int TP = (T + 1) / 2;
-    const int64_t blocks = (N * TP + GMM_THREADS - 1) / GMM_THREADS;
-    CCMPC_REQUIRE(blocks < ((int64_t)1 << 31), "ccmpc_gmm2d_sample: N too large for one launch");
+    int64_t blocks = (N * TP + GMM_THREADS - 1) / GMM_THREADS;
+    const int64_t cap = (148 * 8 + V - 1) / V;        // ~8 resident CTAs per SM over all vehicles; grid-stride beyond
+    if (blocks > cap) blocks = cap;
     dim3 grid((unsigned)blocks, (unsigned)V);
     GmmNoise noise{u_z, u_c, eps};
-    const size_t smem = (size_t)Z * sizeof(float);
+    const size_t smem = (size_t)((Z + 1) & ~1) * sizeof(float) + (size_t)Z * sizeof(double);
     cudaStream_t st = (cudaStream_t)stream;
     if ((T & 1) == 0) {
         gmm2d_sample_kernel<true><<<grid, GMM_THREADS, smem, st>>>(latent_pmf, log_pis, mus, log_sigmas, corrs, N, Z,

@@ -3,6 +3,8 @@
 // Reference: collect/in_simulation/midlevel/ovehicle.py:72-76 (per-sample yaw from consecutive
 // predicted positions): yaw[n, 0] = atan2 of (p[n, 0] - last observed position),
 // yaw[n, t] = atan2 of (p[n, t] - p[n, t-1]).
+#include <cooperative_groups.h>
+
 #include "common.cuh"
 
 namespace ccmpc {
@@ -46,11 +48,12 @@ __global__ void yaws_kernel(const double* __restrict__ samples, const int64_t* _
 //   already holds (:96-104); pmf_j = N_j / N (:109-113).
 // The resulting row order is a STABLE sort of the samples by (cluster j, origin g) with g = 0 for the
 // cluster's own latent and g = 1 + latent otherwise: two LSD counting-sort passes over sample indices.
-// One CTA per vehicle; cell index = v * S + j (cells j >= K_v stay empty).
+// One 8-CTA cluster per vehicle; cell index = v * S + j (cells j >= K_v stay empty).
 // ---------------------------------------------------------------------------
 constexpr int GR_THREADS = 1024;
 constexpr int GR_WARPS = GR_THREADS / 32;
 constexpr int GR_MAXS = 32;          // latent states handled (Trajectron++ uses 25)
+constexpr int GR_CLUSTER = 8;        // CTAs per vehicle (portable cluster size)
 
 struct GroupArgs {
     const float* pred32;             // [V,N,T,2] float32 (+ minpos) or
@@ -80,62 +83,91 @@ __device__ __forceinline__ double2 final_position(const GroupArgs& a, int64_t v,
     return reinterpret_cast<const double2*>(a.pred64)[e];
 }
 
-// one stable counting-sort pass over the vehicle's N samples.  key(n) in [0, 32); in_idx == nullptr means
-// the identity order.  Writes out_idx (int32 or int64) in sorted order; returns bin starts in s_start[33].
+// One vehicle = one thread-block CLUSTER of GR_CLUSTER CTAs; CTA r owns the r-th contiguous chunk of the
+// vehicle's samples (and, in the second sort pass, of the intermediate order), so "stable" means: bins in
+// order, inside a bin CTAs in rank order, inside a CTA the original order.  The CTAs exchange their per-bin
+// counts and per-latent partial sums through distributed shared memory.
+namespace cg = cooperative_groups;
+
+// one stable counting-sort pass over positions [lo, hi) of the vehicle's current order.  key(n) in [0, 32);
+// in_idx == nullptr means the identity order.  Writes out_idx at GLOBAL sorted positions; every CTA ends with
+// the vehicle-wide bin starts in s_start[33].
 template <typename OutT, typename KeyFn>
-__device__ void stable_pass(int64_t N, const int32_t* in_idx, OutT* out_idx, KeyFn key_of, int* s_hist /*[33]*/,
+__device__ void stable_pass(cg::cluster_group& cl, int64_t lo, int64_t hi, const int32_t* in_idx, OutT* out_idx,
+                            KeyFn key_of, int* s_hist /*[32], DSMEM-visible*/, int* s_pos /*[32]*/,
                             int* s_warp /*[GR_WARPS][32]*/, int* s_start /*[33]*/) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid < 33) s_hist[tid] = 0;
+    const unsigned rank = cl.block_rank(), nranks = cl.num_blocks();
+    if (tid < 32) s_hist[tid] = 0;
     __syncthreads();
-    for (int64_t i = tid; i < N; i += GR_THREADS) atomicAdd(&s_hist[key_of(in_idx ? in_idx[i] : (int32_t)i)], 1);
+    for (int64_t i = lo + tid; i < hi; i += GR_THREADS) atomicAdd(&s_hist[key_of(in_idx ? in_idx[i] : (int32_t)i)], 1);
+    __syncthreads();
+    cl.sync();                                         // every CTA's histogram is complete and visible
+    if (tid < 32) {
+        int before = 0, total = 0;
+        for (unsigned r = 0; r < nranks; ++r) {
+            const int h = cl.map_shared_rank(s_hist, r)[tid];
+            if (r < rank) before += h;
+            total += h;
+        }
+        s_pos[tid] = before;                           // + bin start, below
+        s_warp[tid] = total;
+    }
     __syncthreads();
     if (tid == 0) {
         int run = 0;
-        for (int b = 0; b < 32; ++b) { s_start[b] = run; run += s_hist[b]; }
+        for (int b = 0; b < 32; ++b) { s_start[b] = run; run += s_warp[b]; }
         s_start[32] = run;
     }
     __syncthreads();
-    if (tid < 32) s_hist[tid] = s_start[tid];          // running write position of every bin
+    if (tid < 32) s_pos[tid] += s_start[tid];          // running write position of this CTA in every bin
     __syncthreads();
-    for (int64_t base = 0; base < N; base += GR_THREADS) {
+    for (int64_t base = lo; base < hi; base += GR_THREADS) {
         const int64_t i = base + tid;
-        const bool live = i < N;
+        const bool live = i < hi;
         const int32_t src = live ? (in_idx ? in_idx[i] : (int32_t)i) : 0;
         const int key = live ? key_of(src) : 32 + lane;                 // dead lanes never match a live key
         const unsigned peers = __match_any_sync(0xffffffffu, key);
-        const int rank = __popc(peers & ((1u << lane) - 1u));
+        const int rk = __popc(peers & ((1u << lane) - 1u));
         s_warp[warp * 32 + lane] = 0;
         __syncwarp();
-        if (live && rank == 0) s_warp[warp * 32 + key] = __popc(peers);
+        if (live && rk == 0) s_warp[warp * 32 + key] = __popc(peers);
         __syncthreads();
         if (tid < 32) {                                                  // bin tid: exclusive scan over warps
-            int run = s_hist[tid];
+            int run = s_pos[tid];
             for (int w = 0; w < GR_WARPS; ++w) {
                 const int cnt = s_warp[w * 32 + tid];
                 s_warp[w * 32 + tid] = run;
                 run += cnt;
             }
-            s_hist[tid] = run;
+            s_pos[tid] = run;
         }
         __syncthreads();
-        if (live) out_idx[s_warp[warp * 32 + key] + rank] = (OutT)src;
+        if (live) out_idx[s_warp[warp * 32 + key] + rk] = (OutT)src;
         __syncthreads();
     }
+    __threadfence();
+    cl.sync();                                         // out_idx complete cluster-wide; s_hist may be reused
 }
 
-__global__ void __launch_bounds__(GR_THREADS) group_kernel(const GroupArgs a) {
+__global__ void __cluster_dims__(GR_CLUSTER, 1, 1) __launch_bounds__(GR_THREADS) group_kernel(const GroupArgs a) {
     __shared__ int s_rank[GR_MAXS];              // latent -> retained rank j, or -1
     __shared__ int s_keep[GR_MAXS];              // j -> latent
     __shared__ int s_K;
     __shared__ double s_acc[GR_WARPS][GR_MAXS][2];
     __shared__ int s_cnt[GR_WARPS][GR_MAXS];
+    __shared__ double s_part[GR_MAXS][2];        // this CTA's per-latent sums (DSMEM-visible)
+    __shared__ int s_pcnt[GR_MAXS];
     __shared__ double s_cx[GR_MAXS], s_cy[GR_MAXS];
-    __shared__ int s_hist[33], s_start[33], s_warp[GR_WARPS * 32];
+    __shared__ int s_hist[32], s_pos[32], s_start[33], s_warp[GR_WARPS * 32];
+    cg::cluster_group cl = cg::this_cluster();
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int64_t v = blockIdx.x;
+    const unsigned rank = cl.block_rank(), nranks = cl.num_blocks();
+    const int64_t v = blockIdx.y;
     const int S = a.S;
     const int64_t N = a.N;
+    const int64_t chunk = (N + nranks - 1) / nranks;
+    const int64_t lo = min(N, (int64_t)rank * chunk), hi = min(N, lo + chunk);
     // ---- retained latents (ovehicle.py:58)
     if (tid == 0) {
         int K = 0;
@@ -154,12 +186,13 @@ __global__ void __launch_bounds__(GR_THREADS) group_kernel(const GroupArgs a) {
     __syncthreads();
     const int K = s_K;
     const int32_t* zv = a.z + v * N;
-    // ---- centres: mean final position of every retained latent's own samples (:80), fixed summation order
-    for (int64_t base = 0; base < N; base += GR_THREADS) {
+    // ---- centres: mean final position of every retained latent's own samples (:80); fixed summation order
+    //      (lanes by shuffle tree, warps in order, CTAs in rank order), identical in every CTA of the cluster
+    for (int64_t base = lo; base < hi; base += GR_THREADS) {
         const int64_t n = base + tid;
         int j = -1;
         double2 p = make_double2(0.0, 0.0);
-        if (n < N) {
+        if (n < hi) {
             const int zz = zv[n];
             j = (zz >= 0 && zz < S) ? s_rank[zz] : -1;
             if (j >= 0) p = final_position(a, v, n);
@@ -184,17 +217,30 @@ __global__ void __launch_bounds__(GR_THREADS) group_kernel(const GroupArgs a) {
         }
     }
     __syncthreads();
+    if (tid < GR_MAXS) {
+        double sx = 0.0, sy = 0.0;
+        int cnt = 0;
+        if (tid < K)
+            for (int w = 0; w < GR_WARPS; ++w) { sx += s_acc[w][tid][0]; sy += s_acc[w][tid][1]; cnt += s_cnt[w][tid]; }
+        s_part[tid][0] = sx; s_part[tid][1] = sy; s_pcnt[tid] = cnt;
+    }
+    __syncthreads();
+    cl.sync();
     if (tid < K) {
         double sx = 0.0, sy = 0.0;
         int cnt = 0;
-        for (int w = 0; w < GR_WARPS; ++w) { sx += s_acc[w][tid][0]; sy += s_acc[w][tid][1]; cnt += s_cnt[w][tid]; }
+        for (unsigned r = 0; r < nranks; ++r) {
+            const double* pr = cl.map_shared_rank(&s_part[0][0], r);
+            sx += pr[2 * tid]; sy += pr[2 * tid + 1];
+            cnt += cl.map_shared_rank(s_pcnt, r)[tid];
+        }
         s_cx[tid] = sx / (double)cnt;          // 0/0 = NaN for a retained latent without samples, as np.mean
         s_cy[tid] = sy / (double)cnt;
     }
     __syncthreads();
-    // ---- key of every sample: cluster j (major) and origin g (minor)
+    // ---- key of every sample of the chunk: cluster j (major) and origin g (minor)
     uint16_t* keys = a.keys + v * N;
-    for (int64_t n = tid; n < N; n += GR_THREADS) {
+    for (int64_t n = lo + tid; n < hi; n += GR_THREADS) {
         const int zz = zv[n];
         int j = (zz >= 0 && zz < S) ? s_rank[zz] : -1;
         int g = 0;
@@ -212,16 +258,17 @@ __global__ void __launch_bounds__(GR_THREADS) group_kernel(const GroupArgs a) {
         }
         keys[n] = (uint16_t)(j * 32 + g);
     }
-    __syncthreads();
+    __threadfence();
+    cl.sync();                                   // keys of every chunk written (pass 2 reads other CTAs' keys)
     // ---- stable sort by (j, g): minor key first
     int32_t* idx1 = a.idx1 + v * N;
     int64_t* perm = a.perm + v * N;
-    stable_pass<int32_t>(N, nullptr, idx1, [&](int32_t n) { return (int)(keys[n] & 31); }, s_hist, s_warp, s_start);
-    __syncthreads();
-    stable_pass<int64_t>(N, idx1, perm, [&](int32_t n) { return (int)(keys[n] >> 5); }, s_hist, s_warp, s_start);
-    __syncthreads();
-    // ---- per-cell outputs (s_start now holds the cluster starts)
-    if (tid < S) {
+    stable_pass<int32_t>(cl, lo, hi, nullptr, idx1, [&](int32_t n) { return (int)(keys[n] & 31); }, s_hist, s_pos,
+                         s_warp, s_start);
+    stable_pass<int64_t>(cl, lo, hi, idx1, perm, [&](int32_t n) { return (int)(keys[n] >> 5); }, s_hist, s_pos,
+                         s_warp, s_start);
+    // ---- per-cell outputs (s_start now holds the vehicle-wide cluster starts), written by CTA 0
+    if (rank == 0 && tid < S) {
         const int64_t c = v * S + tid;
         const int start = tid < 32 ? s_start[tid] : (int)N, stop = tid + 1 <= 32 ? s_start[tid + 1] : (int)N;
         a.offsets[c] = v * N + (tid < K ? start : N);
@@ -232,8 +279,8 @@ __global__ void __launch_bounds__(GR_THREADS) group_kernel(const GroupArgs a) {
             a.init_center[2 * c + 1] = tid < K ? s_cy[tid] : 0.0;
         }
     }
-    if (tid == 0) {
-        if (v == gridDim.x - 1) a.offsets[(v + 1) * S] = (v + 1) * N;
+    if (rank == 0 && tid == 0) {
+        if (v == gridDim.y - 1) a.offsets[(v + 1) * S] = (v + 1) * N;
         a.n_states[v] = K;
         if (a.status) a.status[v] = K > 0 ? 0 : CCMPC_ST_NO_TANGENT;
     }
@@ -306,7 +353,8 @@ extern "C" int ccmpc_group_by_mode(const float* pred32, const double* pred64, co
     a.keys = reinterpret_cast<uint16_t*>(reinterpret_cast<char*>(workspace) + (((size_t)V * N * 4 + 255) / 256) * 256);
     a.perm = perm; a.offsets = offsets; a.n_states = n_states; a.cell_latent = cell_latent; a.cell_pmf = cell_pmf;
     a.init_center = init_center; a.status = status;
-    group_kernel<<<(unsigned)V, GR_THREADS, 0, st>>>(a);
+    CCMPC_REQUIRE(V <= 65535, "ccmpc_group_by_mode: V > 65535");
+    group_kernel<<<dim3(GR_CLUSTER, (unsigned)V), GR_THREADS, 0, st>>>(a);
     int rc = check_launch("group_kernel");
     if (rc || N == 0) return rc;
     const int64_t tot = V * N * T;

@@ -50,6 +50,7 @@ l4_outer_kernel(const double* __restrict__ samples, const double* __restrict__ y
     const int rl = tid / T, t = tid - rl * T;
     const int64_t b = offsets[c], e = offsets[c + 1];
     const double ninf = __longlong_as_double(0xfff0000000000000LL);
+    if (blockIdx.y > 0 && b + (int64_t)blockIdx.y * rpp >= e) return;      // no row for this block (CTA-uniform)
     double m0 = ninf, m1 = ninf, m2 = ninf, m3 = ninf;
     double ct = 1.0, stt = 0.0;
     if (lw_cell) { l = lw_cell[2 * c]; w = lw_cell[2 * c + 1]; }
@@ -117,11 +118,14 @@ extern "C" int ccmpc_l4_outer(const double* samples, const double* yaws, const i
     // 0xFF bytes = the identity of atomic_max_double (see common.cuh)
     cudaError_t e = cudaMemsetAsync(b0, 0xFF, (size_t)C * T * 4 * sizeof(double), st);
     if (e != cudaSuccess) { set_error("ccmpc_l4_outer: memset: %s", cudaGetErrorString(e)); return CCMPC_E_LAUNCH; }
+    // Cell sizes live on the device (offsets), and ingest layouts leave most cells empty (cell = v * S + j), so
+    // grid.y is sized for the case that ONE cell holds every row, 8 rows per thread: blocks whose first row lies
+    // beyond their cell's end exit after reading two offsets, which is cheaper than the serial tail a small
+    // grid.y leaves in the few populated cells.
     const int rpp = L4_THREADS / T;
-    int64_t per_cell = n_total / C + 1;
-    int64_t y = (per_cell + (int64_t)rpp * 16 - 1) / ((int64_t)rpp * 16);
+    int64_t y = (n_total + (int64_t)rpp * 8 - 1) / ((int64_t)rpp * 8);
     if (y < 1) y = 1;
-    if (y > 1024) y = 1024;
+    if (y > 64) y = 64;
     dim3 grid((unsigned)C, (unsigned)y);
     l4_outer_kernel<<<grid, L4_THREADS, 0, st>>>(samples, yaws, offsets, T, yaw_mean, lw_cell, l, w, At, b0);
     return check_launch("l4_outer_kernel");

@@ -32,6 +32,17 @@ def main():
     what = sys.argv[1] if len(sys.argv) > 1 else "sweep"
     accel = int(sys.argv[2]) if len(sys.argv) > 2 else 2
     dev = torch.device("cuda:0")
+    if what == "c5s":
+        from ccmpc_b200 import midlevel
+        O, K, T, N, Z = 8, 4, 16, 20_000, 25
+        sc = synth.make_scene(5, O, K, T)
+        pmf, mus, ls, rho = synth.gmm2d_params(sc, Z=Z)
+        plan = midlevel.StepPlan.from_gmm(O, N, T, sc.pos_last, prediction_horizon=T, Z=Z, minpos=synth.MINPOS,
+                                          device=dev, builder="affine", seed=5, use_graph=False)
+        for i in range(3):
+            plan.run_gmm(pmf, mus, ls, rho, ref_traj=sc.ref_traj, step_seed=i)
+        print("ok c5s")
+        return
     if what in ("risk", "rollout"):
         O, K, T, n = 8, 4, 16, 250_000
         C = O * K
