@@ -67,7 +67,7 @@ gmm2d_sample_kernel(const double* __restrict__ latent_pmf, const float* __restri
     const uint32_t seed_lo = (uint32_t)seed, seed_hi = (uint32_t)(seed >> 32);
     const int TP = (T + 1) >> 1;
     for (int64_t i = (int64_t)blockIdx.x * GMM_THREADS + threadIdx.x; i < N * TP; i += (int64_t)gridDim.x * GMM_THREADS) {
-    const int64_t n = i / TP;
+    const int64_t n = (N * TP < ((int64_t)1 << 31)) ? (int64_t)((uint32_t)i / (uint32_t)TP) : i / TP;
     const int tp = (int)(i - n * TP);
     const uint64_t gi = sample_offset + (uint64_t)n;
     const uint32_t gi_lo = (uint32_t)gi, gi_hi = (uint32_t)(gi >> 32);

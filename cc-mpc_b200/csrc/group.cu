@@ -23,7 +23,8 @@ __global__ void yaws_kernel(const double* __restrict__ samples, const int64_t* _
                             int64_t N, int T, const double* __restrict__ pos_last, double* __restrict__ yaws) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= N * T) return;
-    const int64_t row = i / T;
+    // 32-bit division when the element count allows (a 64-bit divide is ~100 instructions)
+    const int64_t row = (N * T < ((int64_t)1 << 31)) ? (int64_t)((uint32_t)i / (uint32_t)T) : i / T;
     const int t = (int)(i - row * T);
     const double2* p2 = reinterpret_cast<const double2*>(samples);
     const double2 cur = p2[i];
@@ -292,9 +293,10 @@ __global__ void gather_rows_kernel(const float* __restrict__ pred32, const doubl
                                    double miny, double* __restrict__ samples) {
     const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= rows * T) return;
-    const int64_t row = e / T;
+    const bool small = rows * T < ((int64_t)1 << 31);
+    const int64_t row = small ? (int64_t)((uint32_t)e / (uint32_t)T) : e / T;
     const int t = (int)(e - row * T);
-    const int64_t v = row / N;
+    const int64_t v = small ? (int64_t)((uint32_t)row / (uint32_t)N) : row / N;
     const int64_t src = (v * N + perm[row]) * T + t;
     double2 o;
     if (pred32) {

@@ -1,5 +1,10 @@
-import sys, os, torch, numpy as np
-sys.path.insert(0, "/root/repo")
+"""compute_mvoe alone (ccmpc_mvoe_fit) on 13.1 M SPD pairs: both forms, both iterate modes, GB/s per variant."""
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from ccmpc_b200 import ops
 dev = torch.device("cuda:0")
 M = 4096 * 8 * 16 * 25
