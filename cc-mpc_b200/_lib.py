@@ -39,7 +39,7 @@ SIGNATURES = {
     "ccmpc_yaws_from_positions": (c_int, [_P, _P, c_int64, c_int64, c_int, _P, _P, _P]),
     "ccmpc_group_workspace_bytes": (c_size_t, [c_int64, c_int64]),
     "ccmpc_group_by_mode": (c_int, [_P, _P, _P, _P, c_int64, c_int64, c_int, c_int, c_double, c_double, c_double,
-                                     _P, _P, _P, _P, _P, _P, _P, _P, _P, c_size_t, _P]),
+                                     _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, c_size_t, _P]),
     "ccmpc_episode_cost": (c_int, [_P, _P, _P, c_int64, c_int, c_double, c_double, _P, _P, _P]),
     "ccmpc_philox4x32": (c_int, [_P, _P, c_int64, _P, _P]),
     "ccmpc_mc_risk_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int]),

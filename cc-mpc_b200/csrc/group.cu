@@ -290,7 +290,8 @@ __global__ void __cluster_dims__(GR_CLUSTER, 1, 1) __launch_bounds__(GR_THREADS)
 // samples[v*N + i] = (double) predictions[v, perm[v, i]] + minpos     (v8ideal:486 on the grouped order)
 __global__ void gather_rows_kernel(const float* __restrict__ pred32, const double* __restrict__ pred64,
                                    const int64_t* __restrict__ perm, int64_t rows, int64_t N, int T, double minx,
-                                   double miny, double* __restrict__ samples) {
+                                   double miny, double* __restrict__ samples,
+                                   const double* __restrict__ pos_last, double* __restrict__ yaws) {
     const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= rows * T) return;
     const bool small = rows * T < ((int64_t)1 << 31);
@@ -298,14 +299,21 @@ __global__ void gather_rows_kernel(const float* __restrict__ pred32, const doubl
     const int t = (int)(e - row * T);
     const int64_t v = small ? (int64_t)((uint32_t)row / (uint32_t)N) : row / N;
     const int64_t src = (v * N + perm[row]) * T + t;
-    double2 o;
-    if (pred32) {
-        const float2 f = reinterpret_cast<const float2*>(pred32)[src];
-        o = make_double2((double)f.x + minx, (double)f.y + miny);
-    } else {
-        o = reinterpret_cast<const double2*>(pred64)[src];
-    }
+    auto fetch = [&](int64_t i) {
+        if (pred32) {
+            const float2 f = reinterpret_cast<const float2*>(pred32)[i];
+            return make_double2((double)f.x + minx, (double)f.y + miny);
+        }
+        return reinterpret_cast<const double2*>(pred64)[i];
+    };
+    const double2 o = fetch(src);
     reinterpret_cast<double2*>(samples)[e] = o;
+    if (yaws) {
+        // ovehicle.py:72-76 on the row just gathered (same arithmetic as yaws_kernel): heading of the step
+        // from the previous position, the vehicle's last observed position for t = 0
+        const double2 prev = t == 0 ? make_double2(pos_last[2 * v], pos_last[2 * v + 1]) : fetch(src - 1);
+        yaws[e] = atan2(o.y - prev.y, o.x - prev.x);
+    }
 }
 
 }  // namespace ccmpc
@@ -333,8 +341,8 @@ extern "C" int ccmpc_group_by_mode(const float* pred32, const double* pred64, co
                                    const double* latent_pmf, int64_t V, int64_t N, int T, int S, double minpos_x,
                                    double minpos_y, double filter_pmf, double* samples, int64_t* offsets,
                                    int64_t* perm, int32_t* n_states, int32_t* cell_latent, double* cell_pmf,
-                                   double* init_center, uint8_t* status, void* workspace, size_t workspace_bytes,
-                                   void* stream) {
+                                   double* init_center, uint8_t* status, const double* pos_last, double* yaws,
+                                   void* workspace, size_t workspace_bytes, void* stream) {
     CCMPC_REQUIRE(T >= 1 && T <= CCMPC_MAX_T, "ccmpc_group_by_mode: need 1 <= T <= %d", CCMPC_MAX_T);
     CCMPC_REQUIRE(S >= 1 && S <= GR_MAXS, "ccmpc_group_by_mode: need 1 <= S <= %d latent states", GR_MAXS);
     CCMPC_REQUIRE(V >= 0 && N >= 0 && N < ((int64_t)1 << 31), "ccmpc_group_by_mode: bad V / N");
@@ -342,6 +350,7 @@ extern "C" int ccmpc_group_by_mode(const float* pred32, const double* pred64, co
                   "ccmpc_group_by_mode: pass exactly one of pred32 / pred64");
     if (V == 0) return CCMPC_OK;
     CCMPC_REQUIRE(z && latent_pmf && samples && offsets && perm && n_states, "ccmpc_group_by_mode: null pointer");
+    CCMPC_REQUIRE(!yaws || pos_last, "ccmpc_group_by_mode: yaws needs pos_last [V,2]");
     const size_t need = ccmpc_group_workspace_bytes(V, N);
     if (!workspace || workspace_bytes < need) {
         set_error("ccmpc_group_by_mode: workspace %zu < %zu bytes", workspace_bytes, need);
@@ -361,6 +370,6 @@ extern "C" int ccmpc_group_by_mode(const float* pred32, const double* pred64, co
     if (rc || N == 0) return rc;
     const int64_t tot = V * N * T;
     gather_rows_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(pred32, pred64, perm, V * N, N, T, minpos_x,
-                                                                     minpos_y, samples);
+                                                                     minpos_y, samples, pos_last, yaws);
     return check_launch("gather_rows_kernel");
 }

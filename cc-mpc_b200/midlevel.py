@@ -652,6 +652,7 @@ class StepPlan:
             self.z = torch.empty((V, Nv), dtype=torch.int32, device=dev)
             self.pmf = torch.empty((V, S), dtype=torch.float64, device=dev)
             self.perm_dev = torch.empty((V, Nv), dtype=torch.int64, device=dev)
+            self.pos_last_vehicle = self.pos_last.view(V, S, 2)[:, 0].contiguous()
             self.group_ws = torch.empty(int(ops._lib.load().ccmpc_group_workspace_bytes(V, Nv)), dtype=torch.uint8,
                                         device=dev)
             # sampler mode (from_gmm): the predictor's GMM2D parameters in, samples drawn on the device
@@ -705,7 +706,7 @@ class StepPlan:
             self._group_out = dict(samples=self.samples, offsets=self.out["g_offsets"], perm=self.perm_dev,
                                    n_states=self.out["g_n_states"], cell_latent=self.out["g_cell_latent"],
                                    cell_pmf=self.out["g_cell_pmf"], init_center=self.out["g_init_center"],
-                                   status=self.out["g_status"])
+                                   status=self.out["g_status"], yaws=self.yaws)
         self._ego_is_ref = True
         self._graph_full = self._graph_dev = None
         self.launches_per_step = None
@@ -801,8 +802,9 @@ class StepPlan:
         return self.run(ref_traj=ref_traj)
 
     # -------------------------------------------------------------- launches
-    def _enqueue_device(self):
-        ops.yaws_from_positions(self.samples, self.offsets, self.pos_last, out=self.yaws)
+    def _enqueue_device(self, yaws_done: bool = False):
+        if not yaws_done:                   # ingest mode: the grouping kernel already wrote the yaws of its rows
+            ops.yaws_from_positions(self.samples, self.offsets, self.pos_last, out=self.yaws)
         ops.cell_pivot(self.samples, self.offsets, out=self.pivot)
         ops.sample_sums(self.samples, self.offsets, self.pivot, ego=self.ref, yaws=self.yaws, R=self.R,
                         workspace=self.ws, out=self.sums)
@@ -822,7 +824,8 @@ class StepPlan:
     def _enqueue_ingest(self):
         """Device grouping of the raw predictions (v8ideal:486-494 + ovehicle.py:55-113) into the CSR layout."""
         ops.group_by_mode(self.pred, self.z, self.pmf, minpos=self.ingest["minpos"],
-                          filter_pmf=self.ingest.get("filter_pmf", 0.1), workspace=self.group_ws, out=self._group_out)
+                          filter_pmf=self.ingest.get("filter_pmf", 0.1), workspace=self.group_ws, out=self._group_out,
+                          pos_last=self.pos_last_vehicle)
 
     def _enqueue_full(self):
         if self.sampler is not None:
@@ -845,7 +848,7 @@ class StepPlan:
         else:
             self.samples.copy_(self.host_samples, non_blocking=True)
             self.ref.copy_(self.host_ref, non_blocking=True)
-        self._enqueue_device()
+        self._enqueue_device(yaws_done=self.ingest is not None)
         self.host_arena.copy_(self.arena, non_blocking=True)
 
     def _capture(self):

@@ -327,11 +327,13 @@ def l4_outer(samples, yaws, offsets, yaw_mean, lw=(3.7, 1.79), lw_cell=None, out
 
 
 def group_by_mode(predictions, z, latent_pmf, minpos=(0.0, 0.0), filter_pmf: float = 0.1, workspace=None,
-                  out: Optional[dict] = None):
+                  out: Optional[dict] = None, pos_last=None):
     """A2 on the device (v8ideal:486-494 + ovehicle.py:55-113).  ``predictions`` [V,N,T,2] float32 (minpos is
     added after the upcast) or float64 (minpos already added), ``z`` [V,N] int32, ``latent_pmf`` [V,S] float64.
     -> dict(samples [V*N,T,2] f64 grouped, offsets [V*S+1] i64 (cell = v*S + j), perm [V,N] i64,
-            n_states [V] i32, cell_latent [V*S] i32, cell_pmf [V*S], init_center [V*S,2], status [V] u8)."""
+            n_states [V] i32, cell_latent [V*S] i32, cell_pmf [V*S], init_center [V*S,2], status [V] u8).
+    ``pos_last`` [V,2] (last observed position per vehicle): also returns ``yaws`` [V*N,T] of the grouped rows
+    (ovehicle.py:72-76), computed inside the gather instead of by a separate yaws_from_positions pass."""
     lib = _lib.load()
     if predictions.dtype not in (torch.float32, F64):
         raise TypeError("predictions must be float32 or float64")
@@ -351,6 +353,12 @@ def group_by_mode(predictions, z, latent_pmf, minpos=(0.0, 0.0), filter_pmf: flo
                    cell_pmf=torch.empty(V * S, dtype=F64, device=dev),
                    init_center=torch.empty((V * S, 2), dtype=F64, device=dev),
                    status=torch.empty(V, dtype=U8, device=dev))
+        if pos_last is not None:
+            out["yaws"] = torch.empty((V * N, T), dtype=F64, device=dev)
+    _chk(pos_last, F64, "pos_last", (2,))
+    if pos_last is not None and tuple(pos_last.shape) != (V, 2):
+        raise ValueError("pos_last must be [V,2]")
+    yaws = out.get("yaws") if pos_last is not None else None
     need = int(lib.ccmpc_group_workspace_bytes(V, N))
     if workspace is None:
         workspace = torch.empty(need, dtype=U8, device=dev)
@@ -359,7 +367,8 @@ def group_by_mode(predictions, z, latent_pmf, minpos=(0.0, 0.0), filter_pmf: flo
                                        _p(latent_pmf), V, N, T, S, float(minpos[0]), float(minpos[1]),
                                        float(filter_pmf), _p(out["samples"]), _p(out["offsets"]), _p(out["perm"]),
                                        _p(out["n_states"]), _p(out.get("cell_latent")), _p(out.get("cell_pmf")),
-                                       _p(out.get("init_center")), _p(out.get("status")), _p(workspace),
+                                       _p(out.get("init_center")), _p(out.get("status")), _p(pos_last), _p(yaws),
+                                       _p(workspace),
                                        workspace.numel(), _stream()), "ccmpc_group_by_mode")
     return out
 

@@ -247,6 +247,9 @@ int ccmpc_yaws_from_positions(const double* samples, const int64_t* offsets, int
  *   (vehicle-local); n_states [V] int32 = K_v; nullable: cell_latent [V*S] int32 (-1
  *   unused), cell_pmf [V*S], init_center [V*S,2], status [V] uint8 (2: no latent above
  *   filter_pmf - the reference fails in argmin over an empty centre list).
+ *   yaws [V*N,T] (nullable; needs pos_last [V,2], the vehicles' last observed positions):
+ *   per-sample headings of the grouped rows (ovehicle.py:72-76), computed while the rows
+ *   are gathered - the same values ccmpc_yaws_from_positions returns for them.
  *   workspace: ccmpc_group_workspace_bytes(V, N).
  */
 size_t ccmpc_group_workspace_bytes(int64_t V, int64_t N);
@@ -255,6 +258,7 @@ int ccmpc_group_by_mode(const float* pred32, const double* pred64, const int32_t
                         double minpos_x, double minpos_y, double filter_pmf,
                         double* samples, int64_t* offsets, int64_t* perm, int32_t* n_states,
                         int32_t* cell_latent, double* cell_pmf, double* init_center, uint8_t* status,
+                        const double* pos_last, double* yaws,
                         void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------

@@ -774,3 +774,19 @@ def test_mc_risk_equals_rollout_then_sample_sums(dev, Tsh, n):
     # empty batch
     z0, _, _ = ops.mc_risk(*args, None, 0, Tsh, T_(ego, dev))
     assert not z0.any()
+
+
+def test_group_by_mode_fused_yaws_equal_yaws_from_positions(dev):
+    """The yaws written while the grouped rows are gathered are bit-identical to a separate
+    ccmpc_yaws_from_positions pass over the grouped tensor (ovehicle.py:72-76)."""
+    from ccmpc_b200 import ops
+    rng = np.random.default_rng(5)
+    V, N, T, S = 3, 4000, 8, 25
+    pred, z, pmf = _group_inputs(rng, V, N, T, S, sparse=True)
+    minpos = np.asarray([151.25, -93.5])
+    pos_last = minpos + rng.normal(size=(V, 2)) * 3
+    out = ops.group_by_mode(T_(pred, dev, torch.float32), T_(z, dev, torch.int32), T_(pmf, dev), minpos=minpos,
+                            pos_last=T_(pos_last, dev))
+    pos_last_cell = T_(np.repeat(pos_last, S, axis=0), dev)
+    want = ops.yaws_from_positions(out["samples"], out["offsets"], pos_last_cell)
+    assert torch.equal(out["yaws"], want)
