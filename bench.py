@@ -17,7 +17,6 @@ import argparse
 import json
 import os
 import sys
-import threading
 import time
 
 import numpy as np
@@ -55,59 +54,76 @@ def _traffic(kernel):
         return None
 
 
+_CLOCK_CHILD = r"""
+import sys, time
+import pynvml
+idx, period = int(sys.argv[1]), float(sys.argv[2])
+pynvml.nvmlInit()
+h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+print("max", pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM), flush=True)
+while True:
+    try:
+        r = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h)
+    except Exception:
+        r = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+    print(time.monotonic(), pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM), r, flush=True)
+    time.sleep(period)
+"""
+
+
 class ClockSampler:
-    """SM clock + throttle reasons during the timed region (NVML; nvidia-smi fallback)."""
+    """SM clock + throttle reasons during the timed region, sampled by a CHILD PROCESS (NVML).  An in-process
+    sampler thread measurably slowed the loop it was watching (GIL + driver contention with kernel launches:
+    0.99 -> 1.08 ms per step at 2 ranks), so the child polls on its own and stamps CLOCK_MONOTONIC; the parent
+    keeps the samples that fall between ``start()`` and ``stop()``.  Only rank 0 samples."""
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
-    def __init__(self, index=0, period=0.002):
-        self.index, self.period = index, period
+    def __init__(self, index=0, period=0.005, enabled=True):
+        self.index, self.period, self.enabled = index, period, enabled
         self.samples, self.reasons, self.max_mhz = [], set(), None
-        self._stop = threading.Event()
-        self._thr = None
-
-    def _init(self):
-        import pynvml
-        pynvml.nvmlInit()
-        self._nv = pynvml
-        self._h = pynvml.nvmlDeviceGetHandleByIndex(self.index)
-        self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM)
-        self._names = {
-            getattr(pynvml, "nvmlClocksEventReasonHwSlowdown", 0x8): "hw_slowdown",
-            getattr(pynvml, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
-            getattr(pynvml, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
-            getattr(pynvml, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
-        }
-
-    def _loop(self):
+        self._proc, self._t0, self._t1 = None, None, None
+        if not enabled:
+            return
         try:
-            pynvml, h = self._nv, self._h
-            while not self._stop.is_set():
-                self.samples.append(pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM))
-                try:
-                    r = pynvml.nvmlDeviceGetCurrentClocksEventReasons(h)
-                except Exception:
-                    r = pynvml.nvmlDeviceGetCurrentClocksThrottleReasons(h)
-                for bit, name in self._names.items():
-                    if r & bit:
-                        self.reasons.add(name)
-                self._stop.wait(self.period)
+            import subprocess
+            self._proc = subprocess.Popen([sys.executable, "-c", _CLOCK_CHILD, str(index), str(period)],
+                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            first = self._proc.stdout.readline().split()          # blocks until NVML is up in the child
+            self.max_mhz = int(first[1]) if len(first) == 2 and first[0] == "max" else None
+            if self.max_mhz is None:
+                raise RuntimeError("clock child did not start")
         except Exception as e:  # noqa: BLE001
             self.reasons.add(f"nvml_unavailable:{type(e).__name__}")
+            self._proc = None
 
     def __enter__(self):
-        # NVML is initialised BEFORE the timed region starts (nvmlInit alone takes tens of ms)
-        try:
-            self._init()
-        except Exception as e:  # noqa: BLE001
-            self.reasons.add(f"nvml_unavailable:{type(e).__name__}")
-            return self
-        self._thr = threading.Thread(target=self._loop, daemon=True)
-        self._thr.start()
+        self._t0 = time.monotonic()
         return self
 
     def __exit__(self, *a):
-        self._stop.set()
-        if self._thr is not None:
-            self._thr.join(timeout=2)
+        self._t1 = time.monotonic()
+        if self._proc is None:
+            return
+        time.sleep(2 * self.period)
+        self._proc.terminate()
+        try:
+            out, _ = self._proc.communicate(timeout=5)
+        except Exception:  # noqa: BLE001
+            self._proc.kill()
+            out = ""
+        for line in out.splitlines():
+            f = line.split()
+            if len(f) != 3:
+                continue
+            try:
+                t, mhz, r = float(f[0]), int(f[1]), int(f[2])
+            except ValueError:
+                continue
+            if self._t0 <= t <= self._t1:
+                self.samples.append(mhz)
+                for bit, name in self.REASONS.items():
+                    if r & bit:
+                        self.reasons.add(name)
 
     def summary(self):
         med = float(np.median(self.samples)) if self.samples else None
@@ -259,13 +275,14 @@ def run_ours(args):
             torch.cuda.current_stream().synchronize()
 
     # ---- device-resident timing --------------------------------------------------------------
+    sampler = ClockSampler(local, enabled=(rank == 0 and os.environ.get("CCMPC_BENCH_NO_CLOCKS") != "1"))
     for i in range(args.warmup):
         step(i)
     barrier()
     l0 = lib.ccmpc_launch_count()
     evs = [[ev(), ev(), ev()] for _ in range(args.steps)]
     t_start, t_stop = ev(), ev()
-    with ClockSampler(local) as clocks:
+    with sampler as clocks:
         t_start.record()
         for i in range(args.steps):
             step(args.warmup + i, evs[i])
