@@ -249,12 +249,17 @@ __global__ void __cluster_dims__(GR_CLUSTER, 1, 1) __launch_bounds__(GR_THREADS)
             g = 1 + (zz < 0 ? 0 : (zz >= S ? S - 1 : zz));
             const double2 p = final_position(a, v, n);
             // scipy.spatial.distance_matrix (p = 2) + np.argmin: first strict minimum (ovehicle.py:94-95)
+            // np.argmin propagates NaN: a retained latent WITHOUT own samples has a NaN centre (np.mean of an
+            // empty slice) and the first such centre wins
             double best = __longlong_as_double(0x7ff0000000000000LL);
+            bool nan_seen = false;
             j = 0;
             for (int k = 0; k < K; ++k) {
                 const double dx = fabs(__dsub_rn(p.x, s_cx[k])), dy = fabs(__dsub_rn(p.y, s_cy[k]));
                 const double dist = __dsqrt_rn(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
-                if (dist < best) { best = dist; j = k; }
+                if (nan_seen) continue;
+                if (dist != dist) { j = k; nan_seen = true; }
+                else if (dist < best) { best = dist; j = k; }
             }
         }
         keys[n] = (uint16_t)(j * 32 + g);

@@ -558,7 +558,8 @@ def _group_inputs(rng, V, N, T, S, sparse):
 
 
 @pytest.mark.parametrize("V,N,T,S,sparse,f32", [(3, 5000, 8, 25, True, True), (2, 1237, 16, 25, True, False),
-                                                (1, 40, 3, 7, False, True), (2, 3000, 8, 25, False, True)])
+                                                (1, 40, 3, 7, False, True), (2, 3000, 8, 25, False, True),
+                                                (2, 5, 4, 6, False, True), (1, 20001, 16, 25, True, True)])
 def test_group_by_mode_matches_oracle(dev, V, N, T, S, sparse, f32):
     """ccmpc_group_by_mode against the restated bucket + fold of v8ideal:486-494 / ovehicle.py:55-113:
     identical row order (perm), cell sizes, retained latents; centres and pmf to rounding."""
