@@ -21,7 +21,7 @@ constexpr int ST_THREADS = 256;
 constexpr int SS_WARPS = ST_THREADS / 32;
 constexpr int SS_DEPTH = 3;            // 4-sample groups in flight per warp (register prefetch ring)
 constexpr int SS_DEPTH_YAW = 2;        // ... when the yaw tensor is streamed as well (register budget)
-constexpr int SS_SLAB = 2048;          // samples per unit (= per CTA)
+constexpr int SS_SLAB = 2048;          // samples per unit (= per CTA) for large inputs; see pick_slab()
 
 // ---------------------------------------------------------------------------
 // The 2T x 2T second-moment matrix is a Gram matrix  G = U^T U  over samples
@@ -58,6 +58,7 @@ struct StatsArgs {
     int64_t C;
     double r2;
     int T;
+    int slab;
 };
 
 template <int NF>
@@ -98,8 +99,8 @@ __global__ void __launch_bounds__(ST_THREADS, 2) sample_sums_kernel(const StatsA
     const int64_t c = lo;                // cub[c] <= u < cub[c+1]: empty cells own no unit and are never hit
     const int slab_idx = u - a.cub[c];
     const int64_t cell_end = a.offsets[c + 1];
-    const int64_t begin = a.offsets[c] + (int64_t)slab_idx * SS_SLAB;
-    const int rows_unit = (int)min((int64_t)SS_SLAB, cell_end - begin);
+    const int64_t begin = a.offsets[c] + (int64_t)slab_idx * a.slab;
+    const int rows_unit = (int)min((int64_t)a.slab, cell_end - begin);
     const int ngroups = (rows_unit + 3) >> 2;
     const int rounds = (ngroups + GPR - 1) / GPR;          // uniform loop bounds: the DMMAs below sit in
     const int full_rounds = (rows_unit >> 2) / GPR;        // provably convergent control flow
@@ -473,10 +474,19 @@ extern "C" int64_t ccmpc_sums_len(int T) {
 
 static int64_t max_units(int64_t n_total, int64_t C, int slab) { return n_total / slab + C; }
 
+// Samples per CTA.  2048 amortises the CTA epilogue at Monte Carlo sizes; one MPC step (c2: 20 000 rows,
+// c5: 160 000 rows) would then fill only 10-80 of the 296 resident CTA slots, so the slab shrinks (power of
+// two, >= 256) until the grid covers the machine about once.
+static int pick_slab(int64_t n_total) {
+    int slab = SS_SLAB;
+    while (slab > 256 && n_total / slab < 148 * 2) slab >>= 1;
+    return slab;
+}
+
 extern "C" size_t ccmpc_sample_sums_workspace_bytes(int64_t n_total, int64_t C, int T) {
     if (T < 1 || T > CCMPC_MAX_T || n_total < 0 || C < 0) return 0;
     size_t cub = ((size_t)(C + 1) * sizeof(int32_t) + 255) / 256 * 256;
-    return cub + (size_t)max_units(n_total, C, SS_SLAB) * SumsLayout(T).len * sizeof(double) + 256;
+    return cub + (size_t)max_units(n_total, C, pick_slab(n_total)) * SumsLayout(T).len * sizeof(double) + 256;
 }
 
 extern "C" int ccmpc_sample_sums(const double* samples, const int64_t* offsets, int64_t n_total, int64_t C, int T,
@@ -499,14 +509,16 @@ extern "C" int ccmpc_sample_sums(const double* samples, const int64_t* offsets, 
     int32_t* cub = reinterpret_cast<int32_t*>(workspace);
     size_t cub_bytes = ((size_t)(C + 1) * sizeof(int32_t) + 255) / 256 * 256;
     double* partials = reinterpret_cast<double*>(reinterpret_cast<char*>(workspace) + cub_bytes);
-    unit_scan_kernel<<<1, 1024, 0, st>>>(offsets, C, SS_SLAB, cub);
+    const int slab = pick_slab(n_total);
+    unit_scan_kernel<<<1, 1024, 0, st>>>(offsets, C, slab, cub);
     int rc = check_launch("unit_scan_kernel");
     if (rc) return rc;
     StatsArgs a;
     a.samples = samples; a.offsets = offsets; a.cub = cub; a.pivot = pivot; a.ego = ego;
     a.ego_cell_stride = ego_cell_stride; a.yaws = yaws; a.partials = partials; a.C = C; a.r2 = R * R;
     a.T = T;
-    const int64_t mu = max_units(n_total, C, SS_SLAB);
+    a.slab = slab;
+    const int64_t mu = max_units(n_total, C, slab);
     CCMPC_REQUIRE(mu < (int64_t)1 << 31, "ccmpc_sample_sums: too many units");
     {
         const unsigned grid = (unsigned)mu;
