@@ -6,7 +6,8 @@
 //   collect/in_simulation/midlevel/v8ideal/__init__.py:627-640, :694-736   per (o, k, t) drivers
 // The reference materialises (N_k, 4, 2) corners per cell and timestep and
 // then takes max(At @ v) over samples and corners; l4_outer_kernel reads
-// (x, y, yaw) once and keeps only the four running maxima.
+// (x, y, yaw) once, evaluates the corner maximum in closed form and keeps only
+// the four running maxima.
 #include "common.cuh"
 
 namespace ccmpc {
@@ -55,22 +56,44 @@ l4_outer_kernel(const double* __restrict__ samples, const double* __restrict__ y
     double ct = 1.0, stt = 0.0;
     if (lw_cell) { l = lw_cell[2 * c]; w = lw_cell[2 * c + 1]; }
     if (rl < rpp) {
-        sincos(yaw_mean[c * T + t], &stt, &ct);
+        const double ym = yaw_mean[c * T + t];
+        sincos(ym, &stt, &ct);
         const double2* g2 = reinterpret_cast<const double2*>(samples);
-        for (int64_t row = b + (int64_t)blockIdx.y * rpp + rl; row < e; row += (int64_t)gridDim.y * rpp) {
-            const double2 p = __ldcs(g2 + row * T + t);
-            const double th = __ldcs(yaws + row * T + t);
-            double vx[4], vy[4];
-            box_corners(p.x, p.y, th, l, w, vx, vy);
+        const double hl = 0.5 * l, hw = 0.5 * w;
+        const int64_t stride = (int64_t)gridDim.y * rpp;
+        const int64_t row0 = b + (int64_t)blockIdx.y * rpp + rl;
+        // 4 rows in flight per thread: the loads of a batch are issued before the first sincos
+        for (int64_t rb = row0; rb < e; rb += 4 * stride) {
+            double2 pp[4];
+            double tt[4];
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
-                // rows of At = [I; -I] Rot(theta): [c, s], [-s, c], [-c, -s], [s, -c]   (util.py:190-193)
-                const double u = fma(ct, vx[k], stt * vy[k]);
-                const double v = fma(-stt, vx[k], ct * vy[k]);
-                m0 = fmax(m0, u);
-                m1 = fmax(m1, v);
-                m2 = fmax(m2, -u);
-                m3 = fmax(m3, -v);
+                const int64_t row = rb + k * stride;
+                const bool ok = row < e;
+                pp[k] = ok ? __ldcs(g2 + row * T + t) : make_double2(0.0, 0.0);
+                tt[k] = ok ? __ldcs(yaws + row * T + t) : 0.0;
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+            if (rb + k * stride >= e) break;
+            const double2 p = pp[k];
+            const double th = tt[k];
+            // The corners are centre +- (l/2) e1 +- (w/2) e2 with e1 = (cos th, sin th), e2 = (-sin th, cos th)
+            // (npu.py:343-347), and a row of At is a unit vector d, so max over the 4 corners of d.v is
+            //   d.centre + (l/2) |d.e1| + (w/2) |d.e2|,
+            // with d.e1 = cos(th - mean yaw), d.e2 = -sin(th - mean yaw) for the first row and the roles of
+            // sin / cos swapped for the second (util.py:190-199): one sincos of the yaw DIFFERENCE per sample
+            // instead of the four corners.
+            double sd, cd;
+            sincos(th - ym, &sd, &cd);
+            const double ca = fabs(cd), sa = fabs(sd);
+            const double eu = fma(hl, ca, hw * sa), ev = fma(hl, sa, hw * ca);
+            const double u = fma(ct, p.x, stt * p.y);
+            const double v = fma(-stt, p.x, ct * p.y);
+            m0 = fmax(m0, u + eu);
+            m1 = fmax(m1, v + ev);
+            m2 = fmax(m2, eu - u);
+            m3 = fmax(m3, ev - v);
             }
         }
     }
@@ -125,7 +148,7 @@ extern "C" int ccmpc_l4_outer(const double* samples, const double* yaws, const i
     const int rpp = L4_THREADS / T;
     int64_t y = (n_total + (int64_t)rpp * 8 - 1) / ((int64_t)rpp * 8);
     if (y < 1) y = 1;
-    if (y > 64) y = 64;
+    if (y > 32) y = 32;
     dim3 grid((unsigned)C, (unsigned)y);
     l4_outer_kernel<<<grid, L4_THREADS, 0, st>>>(samples, yaws, offsets, T, yaw_mean, lw_cell, l, w, At, b0);
     return check_launch("l4_outer_kernel");
