@@ -13,8 +13,8 @@
 // Parity is statistical (no reference code to run, torch draws from its own generator); a supplied-noise
 // mode makes the arithmetic itself checkable against the oracle (oracle/restate.py: gmm2d_sample).
 //
-// One thread per (sample, timestep pair): one Philox-4x32-10 block gives the four normals of the pair, the
-// 16-byte float4 store of consecutive threads is contiguous.  HBM: 8 B written per (sample, timestep).
+// One thread per (sample, one or two timestep pairs): one Philox-4x32-10 block gives the four normals of a
+// pair, the latent draw is shared by the thread's pairs, the float4 stores of consecutive threads are contiguous.  HBM: 8 B written per (sample, timestep).
 #include "common.cuh"
 #include "philox.cuh"
 
@@ -40,7 +40,7 @@ __device__ __forceinline__ int pick_latent(const float* __restrict__ s_cum, int 
     return z;
 }
 
-template <bool VEC>
+template <bool VEC, int PAIRS>
 __global__ void __launch_bounds__(GMM_THREADS)
 gmm2d_sample_kernel(const double* __restrict__ latent_pmf, const float* __restrict__ log_pis,
                     const float* __restrict__ mus, const float* __restrict__ log_sigmas,
@@ -66,9 +66,10 @@ gmm2d_sample_kernel(const double* __restrict__ latent_pmf, const float* __restri
     if (seed_dev) seed += *seed_dev;              // per-step key read on the device: a captured graph replays with new draws
     const uint32_t seed_lo = (uint32_t)seed, seed_hi = (uint32_t)(seed >> 32);
     const int TP = (T + 1) >> 1;
-    for (int64_t i = (int64_t)blockIdx.x * GMM_THREADS + threadIdx.x; i < N * TP; i += (int64_t)gridDim.x * GMM_THREADS) {
-    const int64_t n = (N * TP < ((int64_t)1 << 31)) ? (int64_t)((uint32_t)i / (uint32_t)TP) : i / TP;
-    const int tp = (int)(i - n * TP);
+    const int TQ = (TP + PAIRS - 1) / PAIRS;          // work items per sample: PAIRS timestep pairs each
+    for (int64_t i = (int64_t)blockIdx.x * GMM_THREADS + threadIdx.x; i < N * TQ; i += (int64_t)gridDim.x * GMM_THREADS) {
+    const int64_t n = (N * TQ < ((int64_t)1 << 31)) ? (int64_t)((uint32_t)i / (uint32_t)TQ) : i / TQ;
+    const int tq = (int)(i - n * TQ);
     const uint64_t gi = sample_offset + (uint64_t)n;
     const uint32_t gi_lo = (uint32_t)gi, gi_hi = (uint32_t)(gi >> 32);
     const int64_t vn = (int64_t)v * N + n;
@@ -82,8 +83,12 @@ gmm2d_sample_kernel(const double* __restrict__ latent_pmf, const float* __restri
         uz = u01(r.c[0]);
     }
     const int z = pick_latent(s_cum, Z, uz);
-    if (tp == 0 && z_out) z_out[vn] = z;
+    if (tq == 0 && z_out) z_out[vn] = z;
 
+#pragma unroll
+    for (int pp = 0; pp < PAIRS; ++pp) {
+    const int tp = tq * PAIRS + pp;
+    if (tp >= TP) continue;
     float e[4] = {0.f, 0.f, 0.f, 0.f}, uc[2] = {0.f, 0.f};
     const int t0 = 2 * tp;
     if (noise.eps) {
@@ -141,6 +146,7 @@ gmm2d_sample_kernel(const double* __restrict__ latent_pmf, const float* __restri
         dst[1] = out[1];
         if (t0 + 1 < T) { dst[2] = out[2]; dst[3] = out[3]; }
     }
+    }   // pairs of this work item
     }   // grid-stride loop
 }
 
@@ -161,21 +167,22 @@ extern "C" int ccmpc_gmm2d_sample(const double* latent_pmf, const float* log_pis
     const bool any = u_z || u_c || eps, all = u_z && u_c && eps;
     CCMPC_REQUIRE(!any || all, "ccmpc_gmm2d_sample: supply u_z, u_c and eps together or none of them");
     const int TP = (T + 1) / 2;
-    int64_t blocks = (N * TP + GMM_THREADS - 1) / GMM_THREADS;
+    const int pairs = (T % 4 == 0) ? 2 : 1;            // 4 timesteps (32 contiguous bytes) per thread when possible
+    const int TQ = (TP + pairs - 1) / pairs;
+    int64_t blocks = (N * TQ + GMM_THREADS - 1) / GMM_THREADS;
     const int64_t cap = (148 * 8 + V - 1) / V;        // ~8 resident CTAs per SM over all vehicles; grid-stride beyond
     if (blocks > cap) blocks = cap;
     dim3 grid((unsigned)blocks, (unsigned)V);
     GmmNoise noise{u_z, u_c, eps};
     const size_t smem = (size_t)((Z + 1) & ~1) * sizeof(float) + (size_t)Z * sizeof(double);
     cudaStream_t st = (cudaStream_t)stream;
-    if ((T & 1) == 0) {
-        gmm2d_sample_kernel<true><<<grid, GMM_THREADS, smem, st>>>(latent_pmf, log_pis, mus, log_sigmas, corrs, N, Z,
-                                                                  T, G, seed, seed_dev, sample_offset, noise,
-                                                                  z_out, predictions);
-    } else {
-        gmm2d_sample_kernel<false><<<grid, GMM_THREADS, smem, st>>>(latent_pmf, log_pis, mus, log_sigmas, corrs, N,
-                                                                   Z, T, G, seed, seed_dev, sample_offset, noise,
-                                                                   z_out, predictions);
-    }
+#define CCMPC_GMM_LAUNCH(VEC, PAIRS)                                                                          \
+    gmm2d_sample_kernel<VEC, PAIRS><<<grid, GMM_THREADS, smem, st>>>(latent_pmf, log_pis, mus, log_sigmas, corrs, N, \
+                                                                    Z, T, G, seed, seed_dev, sample_offset, noise,  \
+                                                                    z_out, predictions)
+    if (pairs == 2) CCMPC_GMM_LAUNCH(true, 2);
+    else if ((T & 1) == 0) CCMPC_GMM_LAUNCH(true, 1);
+    else CCMPC_GMM_LAUNCH(false, 1);
+#undef CCMPC_GMM_LAUNCH
     return check_launch("gmm2d_sample_kernel");
 }
