@@ -348,6 +348,15 @@ __device__ __forceinline__ double lower_bound_prob(const Sym2& ci, const Sym2& c
     return chi2_cdf_df2(r * r);
 }
 
+// same with Gamma = norm.ppf(1 - eps_t) supplied (it is a per-cell constant in the Minkowski loop)
+__device__ __forceinline__ double lower_bound_prob_gamma(const Sym2& ci, const Sym2& cm, const Sym2& ct, double Gamma) {
+    double base = sqrt(fro_norm(ct));
+    double alpha = sqrt(fro_norm(ci)) / base;
+    double beta = sqrt(fro_norm(cm)) / base;
+    double r = Gamma * (1.0 - alpha) / beta;
+    return chi2_cdf_df2(r * r);
+}
+
 // makeconstraint.py:259-280
 __device__ __forceinline__ double scale_factor(const Sym2& ci, const Sym2& cm, const Sym2& ct, double Gamma,
                                                double target_p) {
@@ -388,6 +397,13 @@ __device__ __forceinline__ double cov_from_sums(const double* __restrict__ s, co
                                                 double n, double inv_nm1) {
     double si = s[L.o_s1 + i], sj = s[L.o_s1 + j];
     return (s[L.s2(i, j)] - si * sj / n) * inv_nm1;
+}
+
+// same with 1/n supplied: one multiply instead of an IEEE division per entry (<= 1 ulp apart)
+__device__ __forceinline__ double cov_from_sums_r(const double* __restrict__ s, const SumsLayout& L, int i, int j,
+                                                  double inv_n, double inv_nm1) {
+    double si = s[L.o_s1 + i], sj = s[L.o_s1 + j];
+    return (s[L.s2(i, j)] - si * sj * inv_n) * inv_nm1;
 }
 
 // ordered atomic max on doubles (buffer initialised with 0xFF bytes)

@@ -332,24 +332,58 @@ struct MinkOut {
     uint8_t* status;
 };
 
+// 16-byte asynchronous global -> shared copies (LDGSTS): the next cell's sums land while this cell is fitted
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(d), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" :: "n"(N) : "memory"); }
+
+// Persistent blocks stride over the cells; the moment part of a cell's packed sums (n, S1, S2: 4.5 KB at ph16)
+// is double-buffered in shared memory.  At one MPC step (C ~ 100 cells) every block sees one cell and this is
+// the old one-block-per-cell kernel; at the batched c4 size (819 200 cells) the prefetch hides the load
+// latency that otherwise idles a block between its barrier and its arithmetic.
 __global__ void minkowski_kernel(const double* __restrict__ sums, const double* __restrict__ pivot,
                                  const double* __restrict__ ref, int64_t ref_cell_stride,
-                                 const double* __restrict__ eps_cell, int T, int prediction_horizon, double R,
-                                 double target_p, double tol, int maxiter, int accel, MinkOut out) {
+                                 const double* __restrict__ eps_cell, int64_t C, int T, int prediction_horizon,
+                                 double R, double target_p, double tol, int maxiter, int accel, MinkOut out) {
     extern __shared__ __align__(16) double smem[];
     const SumsLayout L(T);
     const int mom_len = L.o_coll;                 // n, S1, S2
-    double* s_sums = smem;                        // [mom_len]
-    unsigned long long* s_pl = reinterpret_cast<unsigned long long*>(smem + mom_len);   // [T]
-    const int64_t c = blockIdx.x;
+    const int buf_len = (mom_len + 1) & ~1;       // whole 16-byte chunks (a sums row is longer than that)
+    unsigned long long* s_pl = reinterpret_cast<unsigned long long*>(smem + 2 * buf_len);   // [T]
+    double* s_const = smem + 2 * buf_len + T;     // [3] per-cell constants: chi2 quantiles and Gamma
     const int tid = threadIdx.x;
     const int P = T * (T - 1) / 2;
-    const double* g = sums + c * (int64_t)L.len;
-    for (int i = tid; i < mom_len; i += blockDim.x) s_sums[i] = g[i];
+    auto prefetch = [&](int64_t cell, int b) {
+        const double* g = sums + cell * (int64_t)L.len;
+        double* dst = smem + b * buf_len;
+        for (int i = tid; i < (buf_len >> 1); i += blockDim.x) cp_async16(dst + 2 * i, g + 2 * i);
+        cp_async_commit();
+    };
+    int cur = 0;
+    if ((int64_t)blockIdx.x < C) prefetch(blockIdx.x, 0);
+    for (int64_t c = blockIdx.x; c < C; c += gridDim.x, cur ^= 1) {
+    const double* s_sums = smem + cur * buf_len;
     if (tid < T) s_pl[tid] = (unsigned long long)__double_as_longlong(1.0);
+    if (tid == blockDim.x - 1) {
+        // eps_ijt, chi2 quantiles (:910-913) and norm.ppf(1 - eps_ijt) (makeconstraint:297) depend on the cell only
+        const double e = eps_cell[c] / (double)prediction_horizon;
+        s_const[0] = chi2_ppf_df2(1.0 - e);
+        s_const[1] = chi2_ppf_df2(target_p);
+        s_const[2] = normcdfinv(1.0 - e);
+    }
+    if (c + gridDim.x < C) {
+        prefetch(c + gridDim.x, cur ^ 1);
+        cp_async_wait<1>();
+    } else {
+        cp_async_wait<0>();
+    }
     __syncthreads();
     const double n = s_sums[0];
-    const double inv_nm1 = 1.0 / (n - 1.0);
+    const double inv_nm1 = 1.0 / (n - 1.0), inv_n = 1.0 / n;
     const double* piv = pivot + c * 2 * T;
     const double* rf = ref + c * ref_cell_stride;
 
@@ -362,14 +396,14 @@ __global__ void minkowski_kernel(const double* __restrict__ sums, const double* 
         const int it = 2 * t, iu = 2 * tau;
         int status = 0;
         // np.cov of [x_t, y_t, x_tau, y_tau] (makeconstraint.py:55)
-        Sym2 St{cov_from_sums(s_sums, L, it, it, n, inv_nm1), cov_from_sums(s_sums, L, it, it + 1, n, inv_nm1),
-                cov_from_sums(s_sums, L, it + 1, it + 1, n, inv_nm1)};
-        Sym2 Su{cov_from_sums(s_sums, L, iu, iu, n, inv_nm1), cov_from_sums(s_sums, L, iu, iu + 1, n, inv_nm1),
-                cov_from_sums(s_sums, L, iu + 1, iu + 1, n, inv_nm1)};
-        const double c00 = cov_from_sums(s_sums, L, it, iu, n, inv_nm1);
-        const double c01 = cov_from_sums(s_sums, L, it, iu + 1, n, inv_nm1);
-        const double c10 = cov_from_sums(s_sums, L, it + 1, iu, n, inv_nm1);
-        const double c11 = cov_from_sums(s_sums, L, it + 1, iu + 1, n, inv_nm1);
+        Sym2 St{cov_from_sums_r(s_sums, L, it, it, inv_n, inv_nm1), cov_from_sums_r(s_sums, L, it, it + 1, inv_n, inv_nm1),
+                cov_from_sums_r(s_sums, L, it + 1, it + 1, inv_n, inv_nm1)};
+        Sym2 Su{cov_from_sums_r(s_sums, L, iu, iu, inv_n, inv_nm1), cov_from_sums_r(s_sums, L, iu, iu + 1, inv_n, inv_nm1),
+                cov_from_sums_r(s_sums, L, iu + 1, iu + 1, inv_n, inv_nm1)};
+        const double c00 = cov_from_sums_r(s_sums, L, it, iu, inv_n, inv_nm1);
+        const double c01 = cov_from_sums_r(s_sums, L, it, iu + 1, inv_n, inv_nm1);
+        const double c10 = cov_from_sums_r(s_sums, L, it + 1, iu, inv_n, inv_nm1);
+        const double c11 = cov_from_sums_r(s_sums, L, it + 1, iu + 1, inv_n, inv_nm1);
         // Sigma_mu = C Sigma_tau^-1 C^T (:65); Sigma_infer = Sigma_t - Sigma_mu (:68)
         const double du = det2(Su);
         if (du == 0.0 || !isfinite(du)) status = CCMPC_ST_SINGULAR;
@@ -380,9 +414,7 @@ __global__ void minkowski_kernel(const double* __restrict__ sums, const double* 
         Sym2 Smu{fma(w00, c00, w01 * c01), fma(w00, c10, w01 * c11), fma(w10, c10, w11 * c11)};
         Sym2 Sinf{St.xx - Smu.xx, St.xy - Smu.xy, St.yy - Smu.yy};
         // eps_ijt, chi2 quantiles (:910-913)
-        const double eps_ijt = eps_cell[c] / (double)prediction_horizon;
-        const double chi_eps = chi2_ppf_df2(1.0 - eps_ijt);
-        const double chi_p = chi2_ppf_df2(target_p);
+        const double chi_eps = s_const[0], chi_p = s_const[1];
         Sym2 a{Sinf.xx * chi_eps, Sinf.xy * chi_eps, Sinf.yy * chi_eps};
         Sym2 b{Smu.xx * chi_p, Smu.xy * chi_p, Smu.yy * chi_p};
         int it1, it2;
@@ -414,7 +446,7 @@ __global__ void minkowski_kernel(const double* __restrict__ sums, const double* 
             else { code = tg.idx | 2; }
         }
         // recursive-feasibility lower bound (:942-943)
-        const double pl = lower_bound_prob(Sinf, Smu, St, eps_ijt);
+        const double pl = lower_bound_prob_gamma(Sinf, Smu, St, s_const[2]);
         if (pl < 1.0) atomicMin(&s_pl[t], (unsigned long long)__double_as_longlong(pl));
 
         const int64_t o = c * P + tid;
@@ -437,6 +469,8 @@ __global__ void minkowski_kernel(const double* __restrict__ sums, const double* 
             out.mean[(c * T + tid) * 2 + 1] = piv[2 * tid + 1] + s_sums[L.o_s1 + 2 * tid + 1] / n;
         }
     }
+    __syncthreads();      // s_const / this buffer are rewritten by the next cell
+    }   // cells of this block
 }
 
 // ---------------------------------------------------------------------------
@@ -574,10 +608,13 @@ extern "C" int ccmpc_minkowski_halfplanes(const double* sums, const double* pivo
     const int P = T * (T - 1) / 2;
     int threads = ((P > T ? P : T) + 31) / 32 * 32;
     SumsLayout L(T);
-    size_t smem = (size_t)(L.o_coll + T) * sizeof(double);
+    size_t smem = (size_t)(2 * ((L.o_coll + 1) & ~1) + T + 3) * sizeof(double);
     MinkOut out{nd, ab, q, q1, betas, cov_infer, cov_mu, prob_pair, prob_lower, mean, idx_side, status};
-    minkowski_kernel<<<(unsigned)C, threads, smem, (cudaStream_t)stream>>>(
-        sums, pivot, ref, ref_cell_stride, eps_cell, T, prediction_horizon, R, target_p, tol, maxiter, accel, out);
+    CCMPC_REQUIRE(((uintptr_t)sums & 15) == 0, "ccmpc_minkowski_halfplanes: sums must be 16-byte aligned");
+    const int64_t cap = 148 * 5;                  // persistent: 5 resident 128-thread blocks per SM (92 registers)
+    const unsigned grid = (unsigned)(C < cap ? C : cap);
+    minkowski_kernel<<<grid, threads, smem, (cudaStream_t)stream>>>(
+        sums, pivot, ref, ref_cell_stride, eps_cell, C, T, prediction_horizon, R, target_p, tol, maxiter, accel, out);
     return check_launch("minkowski_kernel");
 }
 
