@@ -63,11 +63,12 @@ struct MvoeSpectrum {
     int status;
 };
 
+template <bool FAST = false>
 __device__ __forceinline__ MvoeSpectrum mvoe_spectrum(const Sym2& s1, const Sym2& s2) {
     MvoeSpectrum sp;
     double d1 = det2(s1);
     sp.status = (d1 == 0.0 || !isfinite(d1)) ? CCMPC_ST_SINGULAR : CCMPC_ST_OK;
-    double inv = 1.0 / d1;
+    double inv = FAST ? rcp_newton(d1) : 1.0 / d1;
     // trace(Sigma1^-1 Sigma2) = (s1.yy s2.xx - 2 s1.xy s2.xy + s1.xx s2.yy) / det(Sigma1)
     double num = fma(s1.yy, s2.xx, fma(-2.0 * s1.xy, s2.xy, s1.xx * s2.yy));
     sp.tr = num * inv;
@@ -348,8 +349,24 @@ __device__ __forceinline__ double lower_bound_prob(const Sym2& ci, const Sym2& c
     return chi2_cdf_df2(r * r);
 }
 
-// same with Gamma = norm.ppf(1 - eps_t) supplied (it is a per-cell constant in the Minkowski loop)
+// same with Gamma = norm.ppf(1 - eps_t) supplied (it is a per-cell constant in the Minkowski loop).
+// FAST: alpha = (|ci|_F^2 / |ct|_F^2)^(1/4) etc. with MUFU + Newton reciprocal / square roots (~1 ulp each)
+// instead of six IEEE square roots and three divisions.
+template <bool FAST = false>
 __device__ __forceinline__ double lower_bound_prob_gamma(const Sym2& ci, const Sym2& cm, const Sym2& ct, double Gamma) {
+    if (FAST) {
+        const double xi = fma(ci.xx, ci.xx, fma(2.0 * ci.xy, ci.xy, ci.yy * ci.yy));
+        const double xm = fma(cm.xx, cm.xx, fma(2.0 * cm.xy, cm.xy, cm.yy * cm.yy));
+        const double xt = fma(ct.xx, ct.xx, fma(2.0 * ct.xy, ct.xy, ct.yy * ct.yy));
+        const double it = rcp_newton(xt);
+        auto root4 = [](double v) {                       // v^(1/4), v >= 0 (0 stays 0)
+            const double s = v > 0.0 ? v * rsqrt_newton<2>(v) : 0.0;
+            return s > 0.0 ? s * rsqrt_newton<2>(s) : 0.0;
+        };
+        const double alpha = root4(xi * it), beta = root4(xm * it);
+        const double r = Gamma * (1.0 - alpha) * rcp_newton(beta);
+        return chi2_cdf_df2(r * r);
+    }
     double base = sqrt(fro_norm(ct));
     double alpha = sqrt(fro_norm(ci)) / base;
     double beta = sqrt(fro_norm(cm)) / base;

@@ -345,6 +345,9 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 // is double-buffered in shared memory.  At one MPC step (C ~ 100 cells) every block sees one cell and this is
 // the old one-block-per-cell kernel; at the batched c4 size (819 200 cells) the prefetch hides the load
 // latency that otherwise idles a block between its barrier and its arithmetic.
+// FAST (accel = 2): direct MVOE solve and MUFU + Newton reciprocals / square roots around it (results within a few
+// ulp of the IEEE forms; the reference-sequence modes keep IEEE division and sqrt).
+template <bool FAST>
 __global__ void minkowski_kernel(const double* __restrict__ sums, const double* __restrict__ pivot,
                                  const double* __restrict__ ref, int64_t ref_cell_stride,
                                  const double* __restrict__ eps_cell, int64_t C, int T, int prediction_horizon,
@@ -407,7 +410,7 @@ __global__ void minkowski_kernel(const double* __restrict__ sums, const double* 
         // Sigma_mu = C Sigma_tau^-1 C^T (:65); Sigma_infer = Sigma_t - Sigma_mu (:68)
         const double du = det2(Su);
         if (du == 0.0 || !isfinite(du)) status = CCMPC_ST_SINGULAR;
-        const double idu = 1.0 / du;
+        const double idu = FAST ? rcp_newton(du) : 1.0 / du;
         const double i00 = Su.yy * idu, i01 = -Su.xy * idu, i11 = Su.xx * idu;
         const double w00 = fma(c00, i00, c01 * i01), w01 = fma(c00, i01, c01 * i11);
         const double w10 = fma(c10, i00, c11 * i01), w11 = fma(c10, i01, c11 * i11);
@@ -418,23 +421,24 @@ __global__ void minkowski_kernel(const double* __restrict__ sums, const double* 
         Sym2 a{Sinf.xx * chi_eps, Sinf.xy * chi_eps, Sinf.yy * chi_eps};
         Sym2 b{Smu.xx * chi_p, Smu.xy * chi_p, Smu.yy * chi_p};
         int it1, it2;
-        MvoeSpectrum sp = mvoe_spectrum(a, b);
+        double ib1, ib2;
+        MvoeSpectrum sp = mvoe_spectrum<FAST>(a, b);
         if (status == 0) status = sp.status;
-        const double beta1 = mvoe_beta(sp, tol, maxiter, accel, it1, status);
-        Sym2 Q1 = mvoe_q(a, b, beta1);                               // :915
+        const double beta1 = mvoe_beta(sp, tol, maxiter, accel, it1, status, &ib1);
+        Sym2 Q1 = FAST ? mvoe_q_inv(a, b, beta1, ib1) : mvoe_q(a, b, beta1);   // :915
         const double r2 = R * R;
-        MvoeSpectrum sp2 = mvoe_spectrum_iso(Q1, r2);
+        MvoeSpectrum sp2 = mvoe_spectrum_iso<FAST>(Q1, r2);
         if (status == 0) status = sp2.status;
-        const double beta2 = mvoe_beta(sp2, tol, maxiter, accel, it2, status);
-        Sym2 Q = mvoe_q_iso(Q1, r2, beta2);                           // :917-918
+        const double beta2 = mvoe_beta(sp2, tol, maxiter, accel, it2, status, &ib2);
+        Sym2 Q = FAST ? mvoe_q_iso_inv(Q1, r2, beta2, ib2) : mvoe_q_iso(Q1, r2, beta2);   // :917-918
         // mean, slope, tangent, side (:895, :923-939)
         const double mx = piv[it] + s_sums[L.o_s1 + it] / n;
         const double my = piv[it + 1] + s_sums[L.o_s1 + it + 1] / n;
         const double rx = rf[2 * t], ry = rf[2 * t + 1];
         const double dy = ry - my;
-        const double m = -(rx - mx) / dy;
+        const double m = FAST ? -(rx - mx) * rcp_newton(dy) : -(rx - mx) / dy;
         if (dy == 0.0 && status == 0) status = CCMPC_ST_DEGENERATE_SLOPE;
-        TangentStar tg = tangent_star(mx, my, Q, 1.0, m, rx, ry);
+        TangentStar tg = tangent_star<FAST>(mx, my, Q, 1.0, m, rx, ry);
         const double n0 = -m, d = tg.d_star;
         int code = 0;
         double A0 = n0, A1 = 1.0, bb = d;
@@ -446,7 +450,7 @@ __global__ void minkowski_kernel(const double* __restrict__ sums, const double* 
             else { code = tg.idx | 2; }
         }
         // recursive-feasibility lower bound (:942-943)
-        const double pl = lower_bound_prob_gamma(Sinf, Smu, St, s_const[2]);
+        const double pl = lower_bound_prob_gamma<FAST>(Sinf, Smu, St, s_const[2]);
         if (pl < 1.0) atomicMin(&s_pl[t], (unsigned long long)__double_as_longlong(pl));
 
         const int64_t o = c * P + tid;
@@ -613,8 +617,12 @@ extern "C" int ccmpc_minkowski_halfplanes(const double* sums, const double* pivo
     CCMPC_REQUIRE(((uintptr_t)sums & 15) == 0, "ccmpc_minkowski_halfplanes: sums must be 16-byte aligned");
     const int64_t cap = 148 * 5;                  // persistent: 5 resident 128-thread blocks per SM (92 registers)
     const unsigned grid = (unsigned)(C < cap ? C : cap);
-    minkowski_kernel<<<grid, threads, smem, (cudaStream_t)stream>>>(
-        sums, pivot, ref, ref_cell_stride, eps_cell, C, T, prediction_horizon, R, target_p, tol, maxiter, accel, out);
+    if (accel == 2)
+        minkowski_kernel<true><<<grid, threads, smem, (cudaStream_t)stream>>>(
+            sums, pivot, ref, ref_cell_stride, eps_cell, C, T, prediction_horizon, R, target_p, tol, maxiter, accel, out);
+    else
+        minkowski_kernel<false><<<grid, threads, smem, (cudaStream_t)stream>>>(
+            sums, pivot, ref, ref_cell_stride, eps_cell, C, T, prediction_horizon, R, target_p, tol, maxiter, accel, out);
     return check_launch("minkowski_kernel");
 }
 

@@ -210,14 +210,16 @@ def _pipeline(dev, g):
     return samples, offsets, pivot, sums, eps
 
 
-def test_minkowski_halfplanes_match_reference_golden(dev, golden):
+@pytest.mark.parametrize("accel", [0, 2])
+def test_minkowski_halfplanes_match_reference_golden(dev, golden, accel):
     """ref_pipeline.npz was produced by the reference's predict_moments / compute_mvoe /
-    choose_closest_tangent / compute_lower_bound inside the restated loop of v8ideal:881-947."""
+    choose_closest_tangent / compute_lower_bound inside the restated loop of v8ideal:881-947.
+    accel = 2: direct MVOE solve + MUFU/Newton reciprocals, same tolerances."""
     from ccmpc_b200 import ops
     g = golden("ref_pipeline")
     T = int(g["T"])
     samples, offsets, pivot, sums, eps = _pipeline(dev, g)
-    out = ops.minkowski_halfplanes(sums, pivot, T_(g["ref_traj"], dev), eps, prediction_horizon=T)
+    out = ops.minkowski_halfplanes(sums, pivot, T_(g["ref_traj"], dev), eps, prediction_horizon=T, accel=accel)
     h = {k: v.cpu().numpy() for k, v in out.items()}
     assert not h["status"].any()
     np.testing.assert_array_equal(h["idx_side"] & 1, g["mk_idx"])                          # bit-exact
