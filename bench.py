@@ -489,6 +489,49 @@ def bench_also(torch, ops, midlevel, synth, dev, args, world=1, rank=0, dist=Non
     assert int(fit[3].max().item()) == 0
     del s1, s2, fit
     del cov, mu, ref, bufs
+    # ---- c4 in its FULL Minkowski form: every (scenario, obstacle, mode) cell runs the whole (t, tau) loop of
+    #      v8ideal:893-947 from its packed sums (Schur split, two MVOE fits, tangent, side, lower bound per pair):
+    #      4096 x 8 x 25 cells x 120 pairs x 2 fits = 1.97e8 fits per GPU
+    Cf = S * O * K
+    scf = synth.make_scene(C4["seed"], 8, 4, T)
+    _, posf = synth.sample_scene(scf, 512 * 32, C4["seed"])
+    posf = torch.from_numpy(posf.reshape(-1, T, 2)).to(dev)                  # 256 distinct cells x 512 samples
+    offf = torch.arange(257, dtype=torch.int64, device=dev) * 512
+    pivb = ops.cell_pivot(posf, offf)
+    sumb = ops.sample_sums(posf, offf, pivb)
+    reps = (Cf + 255) // 256
+    sums_f = sumb.repeat(reps, 1)[:Cf].contiguous()
+    piv_f = pivb.repeat(reps, 1, 1)[:Cf].contiguous()
+    ref_f = torch.from_numpy(synth.reference_trajectory(T)).to(dev)
+    eps_f = torch.full((Cf,), 0.05 / O, dtype=torch.float64, device=dev)
+    Pf = T * (T - 1) // 2
+    mk = ops.minkowski_alloc(Cf, T, dev, fields=("nd", "ab", "idx_side", "prob_lower", "status"))
+    for accel in (0, 2):
+        for _ in range(2):
+            ops.minkowski_halfplanes(sums_f, piv_f, ref_f, eps_f, T, accel=accel, out=mk)
+        torch.cuda.synchronize()
+        a, b = ev(), ev()
+        a.record()
+        for _ in range(5):
+            ops.minkowski_halfplanes(sums_f, piv_f, ref_f, eps_f, T, accel=accel, out=mk)
+        b.record()
+        torch.cuda.synchronize()
+        ms = a.elapsed_time(b) / 5
+        if world > 1:
+            mt = torch.tensor([ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(mt, op=dist.ReduceOp.MAX)
+            ms = float(mt.item())
+        nbytes = sums_f.numel() * 8 + sum(v.numel() * v.element_size() for v in mk.values())
+        out["mvoe_minkowski_full" if accel == 0 else "mvoe_minkowski_full_direct"] = {
+            "metric": "mvoe_fits_per_sec", "value": 2 * Cf * Pf * world / (ms * 1e-3), "unit": "fits/s", "ms": ms,
+            "fits": 2 * Cf * Pf * world, "rows": Cf * Pf * world, "n_gpus": world,
+            "workload": f"c4 full: {Cf} cells per GPU x {Pf} (t, tau) pairs: cov from sums -> Schur split -> MVOE x2 -> "
+                        f"tangent -> side -> lower bound (v8ideal:893-947), 256 distinct cells tiled",
+            "iterate": ("reference sequence from beta = 1", "", "direct solve")[accel],
+            "roofline": {"bound": "issue/fp64", "achieved": nbytes / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                         "frac": nbytes / (ms * 1e-3) / 1e9 / peak, "per": "GPU"}}
+    assert int(mk["status"].max().item()) == 0
+    del sums_f, piv_f, mk, posf
     if rank != 0:
         return out
     # ---- c2: the full constraint build of one MPC step, host samples -> host rows --------------

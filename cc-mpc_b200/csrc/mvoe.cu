@@ -367,16 +367,21 @@ __global__ void minkowski_kernel(const double* __restrict__ sums, const double* 
         cp_async_commit();
     };
     int cur = 0;
+    double last_eps = __longlong_as_double(0x7ff8000000000000LL);      // NaN: never equal
     if ((int64_t)blockIdx.x < C) prefetch(blockIdx.x, 0);
     for (int64_t c = blockIdx.x; c < C; c += gridDim.x, cur ^= 1) {
     const double* s_sums = smem + cur * buf_len;
     if (tid < T) s_pl[tid] = (unsigned long long)__double_as_longlong(1.0);
     if (tid == blockDim.x - 1) {
-        // eps_ijt, chi2 quantiles (:910-913) and norm.ppf(1 - eps_ijt) (makeconstraint:297) depend on the cell only
+        // eps_ijt, chi2 quantiles (:910-913) and norm.ppf(1 - eps_ijt) (makeconstraint:297) depend on the cell's
+        // eps only (eps_ura[o, k] = eps / O, v8ideal:2920-2926): recomputed when it changes, not per cell
         const double e = eps_cell[c] / (double)prediction_horizon;
-        s_const[0] = chi2_ppf_df2(1.0 - e);
-        s_const[1] = chi2_ppf_df2(target_p);
-        s_const[2] = normcdfinv(1.0 - e);
+        if (e != last_eps) {
+            s_const[0] = chi2_ppf_df2(1.0 - e);
+            s_const[1] = chi2_ppf_df2(target_p);
+            s_const[2] = normcdfinv(1.0 - e);
+            last_eps = e;
+        }
     }
     if (c + gridDim.x < C) {
         prefetch(c + gridDim.x, cur ^ 1);
