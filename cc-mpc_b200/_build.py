@@ -12,7 +12,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libccmpc.so")
-SOURCES = ["abi.cu", "mvoe.cu", "stats.cu", "rollout.cu", "l4.cu", "cost.cu", "group.cu", "gmm.cu", "risk.cu"]
+SOURCES = ["abi.cu", "mvoe.cu", "stats.cu", "rollout.cu", "l4.cu", "cost.cu", "group.cu", "gmm.cu", "risk.cu", "fused.cu"]
 HEADERS = ["common.cuh", "philox.cuh", "rollout.cuh", os.path.join("..", "..", "include", "ccmpc.h")]
 
 NVCC_FLAGS = [

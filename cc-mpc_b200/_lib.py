@@ -45,6 +45,9 @@ SIGNATURES = {
     "ccmpc_mc_risk_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int]),
     "ccmpc_mc_risk": (c_int, [_P, _P, _P, c_int, _P, c_int64, c_int64, c_int, c_uint64, c_uint64, _P, c_int64, c_double,
                                _P, _P, _P, _P, c_size_t, _P]),
+    "ccmpc_mc_rollout_sums_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int]),
+    "ccmpc_mc_rollout_sums": (c_int, [_P, _P, _P, c_int, _P, c_int64, c_int64, c_int, c_uint64, c_uint64, _P, _P, c_int64,
+                                       c_double, _P, _P, _P, _P, _P, c_size_t, _P]),
     "ccmpc_gmm2d_sample": (c_int, [_P, _P, _P, _P, _P, c_int64, c_int64, c_int, c_int, c_int, c_uint64, _P,
                                     c_uint64, _P, _P, _P, _P, _P, _P]),
 }

@@ -412,6 +412,42 @@ def mc_rollout(mean, cov, cross, x0, n: int, Tsh: int, seed: int = 0, sample_off
     return traj, z_out, status, x0_out
 
 
+def mc_rollout_sums_workspace(C: int, n: int, Tsh: int, device) -> torch.Tensor:
+    nbytes = _lib.load().ccmpc_mc_rollout_sums_workspace_bytes(int(C), int(n), int(Tsh))
+    return torch.empty(max(int(nbytes), 16), dtype=torch.uint8, device=device)
+
+
+def mc_rollout_sums(mean, cov, cross, x0, n: int, Tsh: int, pivot, ego, R: float = R_EV_OV, seed: int = 0,
+                    sample_offset: int = 0, materialize: bool = True, workspace=None, out=None, sums_out=None):
+    """mc_rollout + sample_sums in one kernel (the trajectory tensor is written once and not read back).
+    Arguments as mc_rollout plus pivot [C,Tsh,2] and ego [Tsh,2] | [C,Tsh,2]; Tsh in (8, 16), Philox noise.
+    -> traj [C,n,Tsh,2] | None (materialize=False), sums [C, sums_len(Tsh)], status [C] uint8, x0_used [C,2]."""
+    lib = _lib.load()
+    _chk(mean, F64, "mean", (2,)); _chk(cov, F64, "cov", (2, 2)); _chk(cross, F64, "cross", (2, 2))
+    _chk(x0, F64, "x0", (2,)); _chk(pivot, F64, "pivot", (2,)); _chk(ego, F64, "ego", (2,))
+    C, Tm = mean.shape[0], mean.shape[1]
+    if tuple(cov.shape) != (C, Tm, 2, 2) or tuple(cross.shape) != (C, Tm, Tm, 2, 2) or \
+            (x0 is not None and tuple(x0.shape) != (C, 2)) or tuple(pivot.shape) != (C, Tsh, 2):
+        raise ValueError("mc_rollout_sums: shapes do not agree")
+    if tuple(ego.shape) == (Tsh, 2):
+        stride = 0
+    elif tuple(ego.shape) == (C, Tsh, 2):
+        stride = 2 * Tsh
+    else:
+        raise ValueError("ego must be [Tsh,2] or [C,Tsh,2]")
+    if workspace is None:
+        workspace = mc_rollout_sums_workspace(C, n, Tsh, mean.device)
+    traj = (out if out is not None else _new((C, n, Tsh, 2), F64, mean)) if materialize else None
+    sums = sums_out if sums_out is not None else _new((C, sums_len(Tsh)), F64, mean)
+    status = _new((C,), U8, mean)
+    x0_out = _new((C, 2), F64, mean)
+    _lib.check(lib.ccmpc_mc_rollout_sums(_p(mean), _p(cov), _p(cross), Tm, _p(x0), C, int(n), int(Tsh),
+                                         int(seed) & 0xFFFFFFFFFFFFFFFF, int(sample_offset), _p(pivot), _p(ego),
+                                         stride, float(R), _p(traj), _p(sums), _p(status), _p(x0_out), _p(workspace),
+                                         workspace.numel(), _stream()), "ccmpc_mc_rollout_sums")
+    return traj, sums, status, x0_out
+
+
 def risk_layout(T: int) -> dict:
     """Offsets into the risk vector of mc_risk: n, coll[T], any, pen[T], d2s[T]."""
     return dict(n=0, coll=1, any=1 + T, pen=2 + T, d2s=2 + 2 * T, len=3 * T + 2)

@@ -337,6 +337,26 @@ int ccmpc_mc_risk(const double* mean, const double* cov, const double* cross, in
                   double* risk, uint8_t* status, double* x0_out,
                   void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---------------------------------------------------------------------------
+ * K1+K2+K6 fused  ccmpc_mc_rollout followed by ccmpc_sample_sums in ONE kernel: the CTA that
+ * rolls 128 samples out (v8ideal:2662-2709, same Philox stream as ccmpc_mc_rollout) writes
+ * them to traj once and reduces them from shared memory (np.mean / np.cov of every (t, tau)
+ * pair, makeconstraint:55, v8ideal:2586-2606; A9 counts) - the trajectory tensor is not read
+ * back.  Philox noise only; Tsh = 8 or 16; no yaw sums (those entries of the layout are 0).
+ *   pivot [C,Tsh,2] (shift of the power sums; the moment means are a good choice),
+ *   ego [Tsh,2] (stride 0) or [C,Tsh,2] (stride 2 Tsh).
+ *   out: traj [C,n,Tsh,2] (NULL: do not materialise), sums [C, ccmpc_sums_len(Tsh)] in the
+ *   packed sums layout, status [C], x0_out [C,2] (nullable) as in ccmpc_mc_rollout.
+ *   workspace: ccmpc_mc_rollout_sums_workspace_bytes(C, n, Tsh) bytes.
+ */
+size_t ccmpc_mc_rollout_sums_workspace_bytes(int64_t C, int64_t n, int Tsh);
+int ccmpc_mc_rollout_sums(const double* mean, const double* cov, const double* cross, int Tm,
+                          const double* x0, int64_t C, int64_t n, int Tsh,
+                          uint64_t seed, uint64_t sample_offset,
+                          const double* pivot, const double* ego, int64_t ego_cell_stride, double R,
+                          double* traj, double* sums, uint8_t* status, double* x0_out,
+                          void* workspace, size_t workspace_bytes, void* stream);
+
 /* Philox-4x32-10 known-answer hook: out[i] = philox(ctr[i], key[i]) (4 words each). */
 int ccmpc_philox4x32(const uint32_t* ctr, const uint32_t* key, int64_t M, uint32_t* out, void* stream);
 

@@ -793,3 +793,39 @@ def test_group_by_mode_fused_yaws_equal_yaws_from_positions(dev):
     pos_last_cell = T_(np.repeat(pos_last, S, axis=0), dev)
     want = ops.yaws_from_positions(out["samples"], out["offsets"], pos_last_cell)
     assert torch.equal(out["yaws"], want)
+
+
+# --------------------------------------------------------- fused rollout + store + sums
+@pytest.mark.parametrize("Tsh,n", [(16, 100_003), (8, 5000), (16, 130), (8, 1)])
+def test_mc_rollout_sums_equals_rollout_then_sample_sums(dev, Tsh, n):
+    """ccmpc_mc_rollout_sums = ccmpc_mc_rollout followed by ccmpc_sample_sums: the trajectories are bit-identical,
+    the counts bit-exact, the power sums equal to fp64 round-off (different partition of the same additions)."""
+    from ccmpc_b200 import ops
+    sc, mean, cov, cross = _scene_moments(9, 2, 3, Tsh + 1)
+    C = 6
+    rng = np.random.default_rng(2)
+    ego = mean[:, 1:Tsh + 1] + rng.normal(size=(C, Tsh, 2)) * 1.5
+    args = (T_(mean, dev), T_(cov, dev), T_(cross, dev))
+    pivot = T_(mean[:, 1:Tsh + 1], dev)
+    traj, _, st, x0 = ops.mc_rollout(*args, None, n, Tsh, seed=31)
+    offsets = torch.arange(C + 1, dtype=torch.int64, device=dev) * n
+    want = ops.sample_sums(traj.view(C * n, Tsh, 2), offsets, pivot, ego=T_(ego, dev))
+    traj2, sums, st2, x0b = ops.mc_rollout_sums(*args, None, n, Tsh, pivot, T_(ego, dev), seed=31)
+    assert torch.equal(traj2, traj) and torch.equal(st, st2) and torch.equal(x0, x0b)
+    L = ops.sums_layout(Tsh)
+    s, w = sums.cpu().numpy(), want.cpu().numpy()
+    np.testing.assert_array_equal(s[:, 0], w[:, 0])
+    np.testing.assert_array_equal(s[:, L["coll"]:L["pen"]], w[:, L["coll"]:L["pen"]])          # coll[T], any
+    scale = np.maximum(np.abs(w), 1.0)
+    assert np.max(np.abs(s - w)[:, :L["yaw"]] / scale[:, :L["yaw"]]) < 1e-11
+    assert not s[:, L["yaw"]:].any()
+    # without materialising, with one shared ego plan
+    _, sums_b, _, _ = ops.mc_rollout_sums(*args, x0, n, Tsh, pivot, T_(ego[0], dev), seed=31, materialize=False)
+    want_b = ops.sample_sums(traj.view(C * n, Tsh, 2), offsets, pivot, ego=T_(ego[0], dev))
+    np.testing.assert_array_equal(sums_b.cpu().numpy()[:, L["coll"]:L["pen"]], want_b.cpu().numpy()[:, L["coll"]:L["pen"]])
+    # moments downstream agree
+    ma = ops.moments_from_sums(sums, pivot, want_yaw=False)
+    mb = ops.moments_from_sums(want, pivot, want_yaw=False)
+    if n > 1:
+        assert relerr(ma["cov"].cpu().numpy(), mb["cov"].cpu().numpy()) < 1e-10
+        assert relerr(ma["mean"].cpu().numpy(), mb["mean"].cpu().numpy()) < 1e-13
