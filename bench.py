@@ -412,7 +412,48 @@ def bench_also(torch, ops, midlevel, synth, dev, args, world=1, rank=0, dist=Non
         "roofline": {"bound": "issue", "algorithmic_hbm_bytes": 0,
                      "note": "0 algorithmic HBM bytes: bound by instruction issue (Philox + Box-Muller + fp64 chain); "
                              "the materialising path moves 32 B per trajectory-step"}}
-    del m3, c3, x3, ws3, risk
+    # ---- the headline step with rollout and sums FUSED (same outputs: trajectories materialised, packed sums,
+    #      moments; the trajectory tensor is written once and not read back)
+    traj3 = torch.empty((C3c, n3, T3, 2), dtype=torch.float64, device=dev)
+    piv3 = m3[:, 1:T3 + 1].contiguous()
+    wsf = ops.mc_rollout_sums_workspace(C3c, n3, T3, dev)
+    sums3 = torch.empty((C3c, ops.sums_len(T3)), dtype=torch.float64, device=dev)
+    mom3 = None
+
+    def fused_step(i):
+        nonlocal mom3
+        ops.mc_rollout_sums(m3, c3, x3, None, n3, T3, piv3, ego3, seed=1234 + i, sample_offset=rank * n3,
+                            workspace=wsf, out=traj3, sums_out=sums3)
+        if world > 1:
+            dist.all_reduce(sums3, op=dist.ReduceOp.SUM)
+        mom3 = ops.moments_from_sums(sums3, piv3, want_yaw=False, out=mom3)
+
+    for i in range(3):
+        fused_step(i)
+    torch.cuda.synchronize()
+    a, b = ev(), ev()
+    a.record()
+    for i in range(reps):
+        fused_step(3 + i)
+    b.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b) / reps
+    if world > 1:
+        mt = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(mt, op=dist.ReduceOp.MAX)
+        ms = float(mt.item())
+    assert int(sums3[0, 0].item()) == n3 * world
+    out["mc_step_fused"] = {
+        "metric": "mc_traj_steps_per_sec", "value": C3c * n3 * T3 * world / (ms * 1e-3), "unit": "traj-steps/s",
+        "ms": ms, "n_gpus": world,
+        "workload": "the headline c3 step (rollout -> trajectories in HBM -> counts / cost / all (t, tau) moments"
+                    f"{' -> all-reduce' if world > 1 else ''} -> moments) with rollout, store and sums in ONE kernel",
+        "roofline": {"bound": "fp64 pipe / latency", "algorithmic_hbm_bytes": C3c * n3 * T3 * 16,
+                     "achieved": C3c * n3 * T3 * 16 / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                     "frac": C3c * n3 * T3 * 16 / (ms * 1e-3) / 1e9 / peak,
+                     "note": "16 B per trajectory-step (written once) instead of 32 B; ncu: tensor (DMMA) pipe 34 % + "
+                             "FP64 22 %, issue 43 %, 16 warps / SM - neither HBM nor a pipe is saturated"}}
+    del m3, c3, x3, ws3, risk, traj3, wsf, sums3
     # ---- c4: batched MVOE footprint fit + tangent half-plane sweep ---------------------------
     S, O, T, K = C4["S"], C4["O"], C4["T"], C4["K"]
     rng = np.random.default_rng(C4["seed"])

@@ -18,6 +18,9 @@ namespace ccmpc {
 
 constexpr int FU_THREADS = 128;
 constexpr int FU_WARPS = FU_THREADS / 32;
+#ifndef FU_CTAS_PER_SM
+#define FU_CTAS_PER_SM 4
+#endif
 
 __device__ __forceinline__ void fu_dmma8x8x4(double& c0, double& c1, double a, double b) {
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
@@ -39,7 +42,7 @@ struct FusedSmem {                                   // per-warp epilogue area (
 
 // TSH = 4 NF timesteps.  grid (gx, C): CTA (bx, c) rolls out and reduces tiles bx, bx + gx, ... of cell c.
 template <int NF>
-__global__ void __launch_bounds__(FU_THREADS)
+__global__ void __launch_bounds__(FU_THREADS, FU_CTAS_PER_SM)
 rollout_sums_kernel(const double* __restrict__ mean, const double* __restrict__ cov, const double* __restrict__ cross,
                     int Tm, const double* __restrict__ x0, int64_t n, uint32_t seed_lo, uint32_t seed_hi,
                     uint64_t sample_offset, const double* __restrict__ pivot, const double* __restrict__ ego,
@@ -125,7 +128,7 @@ rollout_sums_kernel(const double* __restrict__ mean, const double* __restrict__ 
             for (int rw = r0; rw < rows; rw += RPP) __stcs(out2 + rw * TSH + t, stage[rw * STRIDE2 + t]);
         }
         // ---- phase 3: this warp's 32 rows, 4-sample groups: shift, S1, A9 predicate, Gram update
-#pragma unroll 2
+#pragma unroll 4
         for (int g = 0; g < 8; ++g) {
             const int row = 32 * warp + 4 * g + r;
             const bool rv = row < rows;
@@ -243,7 +246,7 @@ __global__ void fused_finalize_kernel(const double* __restrict__ partials, int n
 }
 
 static int fused_grid_x(int64_t n, int64_t C) {
-    int64_t want = (148 * 4) / C;                     // one wave of 4 resident CTAs per SM, split over the cells
+    int64_t want = (148 * FU_CTAS_PER_SM) / C;         // one wave of resident CTAs, split over the cells
     int64_t need = (n + FU_THREADS - 1) / FU_THREADS;
     int64_t g = want < need ? want : need;
     return (int)(g < 1 ? 1 : g);
