@@ -829,3 +829,35 @@ def test_mc_rollout_sums_equals_rollout_then_sample_sums(dev, Tsh, n):
     if n > 1:
         assert relerr(ma["cov"].cpu().numpy(), mb["cov"].cpu().numpy()) < 1e-10
         assert relerr(ma["mean"].cpu().numpy(), mb["mean"].cpu().numpy()) < 1e-13
+
+
+@pytest.mark.parametrize("accel", [0, 2])
+def test_minkowski_halfplanes_batched_cells_are_independent(dev, golden, accel):
+    """More cells than persistent blocks (the kernel then walks several cells per block through its double-buffered
+    sums): every copy of a golden cell, wherever it sits in the batch and whichever eps its neighbours carry,
+    gives bit-identical rows to the small launch checked against the reference above."""
+    from ccmpc_b200 import ops
+    g = golden("ref_pipeline")
+    T = int(g["T"])
+    samples, offsets, pivot, sums, eps = _pipeline(dev, g)
+    C0 = sums.shape[0]
+    ref = T_(g["ref_traj"], dev)
+    small = ops.minkowski_halfplanes(sums, pivot, ref, eps, prediction_horizon=T, accel=accel)
+    reps = 3001 // C0 + 1                                   # > 148 x 5 blocks, not a multiple of the grid
+    C = reps * C0
+    eps_b = eps.repeat(reps)
+    big = ops.minkowski_halfplanes(sums.repeat(reps, 1), pivot.repeat(reps, 1, 1), ref, eps_b, prediction_horizon=T,
+                                   accel=accel)
+    for k, v in small.items():
+        got = big[k].reshape((reps, C0) + tuple(v.shape[1:]))
+        assert torch.equal(got, v.unsqueeze(0).expand_as(got)) or \
+            bool(((got == v.unsqueeze(0)) | (got.isnan() & v.unsqueeze(0).isnan())).all()), k
+    # a different eps on every other cell must only change those cells
+    eps_c = eps_b.clone()
+    eps_c[1::2] *= 0.5
+    mixed = ops.minkowski_halfplanes(sums.repeat(reps, 1), pivot.repeat(reps, 1, 1), ref, eps_c, prediction_horizon=T,
+                                     accel=accel)
+    assert torch.equal(mixed["nd"][0::2], big["nd"][0::2]) and not torch.equal(mixed["nd"][1::2], big["nd"][1::2])
+    half = ops.minkowski_halfplanes(sums.repeat(reps, 1)[1::2].contiguous(), pivot.repeat(reps, 1, 1)[1::2].contiguous(),
+                                    ref, eps_c[1::2].contiguous(), prediction_horizon=T, accel=accel)
+    assert torch.equal(mixed["nd"][1::2], half["nd"]) and torch.equal(mixed["prob_lower"][1::2], half["prob_lower"])
