@@ -732,6 +732,41 @@ def bench_also(torch, ops, midlevel, synth, dev, args, world=1, rank=0, dist=Non
                     f"device sampling of {C5['O']} x {C5['N']} trajectories (Philox, fresh key per step) -> mode "
                     f"grouping -> yaws -> sums/counts -> affine half-planes -> L4 -> D2H, one CUDA graph per step",
         "launches_per_step": plan.launches_per_step}
+    del plan
+    # ---- the same, with the predictor's dynamics: the GMM2D is over unicycle CONTROLS (heading rate, acceleration)
+    #      and every sample is integrated to positions on the device (p_y_xz: a_dist.rsample ->
+    #      dynamic.integrate_samples, prediction.py:85-86)
+    upmf, _, umus, uls, urho, ux0 = synth.unicycle_control_params(C5["O"], S, C5["T"], seed=C5["seed"])
+    upos = ux0[:, :2].astype(np.float64) + synth.MINPOS
+    plan = midlevel.StepPlan.from_gmm(C5["O"], C5["N"], C5["T"], upos, prediction_horizon=C5["T"], Z=S,
+                                      minpos=synth.MINPOS, device=dev, builder="affine", seed=C5["seed"],
+                                      dynamics="unicycle", dt=0.5)
+    plan.run_gmm(upmf, umus, uls, urho, ref_traj=ref0, step_seed=0, x0=ux0)
+    hx = plan.host_gmm["x0"].numpy()
+    lat = []
+    for i in range(10 + C5["steps"]):
+        hx[:, :2] += np.float32(0.01)                # the vehicles move (untimed host work)
+        plan.host_gmm["seed"][0] = i
+        ref_i = ref0 + 0.02 * i
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        res = plan.run(ref_traj=ref_i)
+        dt = (time.perf_counter() - t0) * 1e3
+        if i >= 10:
+            lat.append(dt)
+    assert not res["g_status"].any() and int(res["g_offsets"][-1]) == C5["O"] * C5["N"]
+    out["replay_c5_sampler_unicycle"] = {
+        "metric": "mpc_step_latency_ms", "unit": "ms", "higher_is_better": False, "steps": C5["steps"],
+        "p50_host_to_host": float(np.percentile(lat, 50)), "p95_host_to_host": float(np.percentile(lat, 95)),
+        "mean_host_to_host": float(np.mean(lat)),
+        "h2d_bytes_per_step": int(sum(h.numel() * h.element_size() for h in plan.host_gmm.values() if h is not None)
+                                  + plan.host_pmf.numel() * 8 + plan.host_ref.numel() * 8),
+        "d2h_bytes_per_step": int(plan.host_arena.numel()),
+        "cells": int(res["g_n_states"].sum()),
+        "workload": f"c5 from the predictor's CONTROL distribution: latent pmf ({S} states) + GMM2D over (heading rate, "
+                    f"acceleration) + vehicle states H2D -> device sampling + unicycle integration of {C5['O']} x "
+                    f"{C5['N']} trajectories -> mode grouping -> yaws -> sums/counts -> affine half-planes -> L4 -> D2H, "
+                    f"one CUDA graph per step", "launches_per_step": plan.launches_per_step}
     return out
 
 

@@ -50,6 +50,8 @@ SIGNATURES = {
                                        c_double, _P, _P, _P, _P, _P, c_size_t, _P]),
     "ccmpc_gmm2d_sample": (c_int, [_P, _P, _P, _P, _P, c_int64, c_int64, c_int, c_int, c_int, c_uint64, _P,
                                     c_uint64, _P, _P, _P, _P, _P, _P]),
+    "ccmpc_gmm2d_sample_dynamics": (c_int, [_P, _P, _P, _P, _P, c_int, _P, c_double, c_int64, c_int64, c_int, c_int,
+                                             c_int, c_uint64, _P, c_uint64, _P, _P, _P, _P, _P, _P]),
 }
 
 

@@ -664,7 +664,9 @@ class StepPlan:
                                      log_sigmas=torch.zeros((V, S, self.T, G, 2), dtype=f32).pin_memory(),
                                      corrs=torch.zeros((V, S, self.T, G), dtype=f32).pin_memory(),
                                      log_pis=torch.zeros((V, S, self.T, G), dtype=f32).pin_memory() if G > 1 else None,
-                                     seed=torch.zeros(1, dtype=torch.int64).pin_memory())
+                                     seed=torch.zeros(1, dtype=torch.int64).pin_memory(),
+                                     x0=(torch.zeros((V, 4), dtype=f32).pin_memory()
+                                         if self.sampler.get("dynamics") not in (None, "none") else None))
                 self.gmm = {k: (None if v is None else torch.empty(v.shape, dtype=v.dtype, device=dev))
                             for k, v in self.host_gmm.items()}
         self.host_samples = (torch.empty((self.N, self.T, 2), dtype=torch.float64).pin_memory()
@@ -763,25 +765,31 @@ class StepPlan:
 
     @classmethod
     def from_gmm(cls, V: int, N: int, T: int, pos_last, prediction_horizon: int, Z: int = 25, G: int = 1,
-                 seed: int = 0, **kw) -> "StepPlan":
+                 seed: int = 0, dynamics: Optional[str] = None, dt: float = 0.5, **kw) -> "StepPlan":
         """Sampler mode: the planner hands over the predictor's OUTPUT DISTRIBUTION - latent pmf (V, Z) and GMM2D
         parameters per (vehicle, latent, timestep, component) - instead of N sampled trajectories per vehicle.
         ``model.latent.sample_p`` + ``GMM2D.rsample`` (prediction.py:81-86), the D2H copy of the samples
         (:88-93) and the bucket-by-latent loop (v8ideal:486-494) all run on the device inside one CUDA graph;
-        the step's H2D traffic is the parameters (KBs) rather than the sample tensor (MBs)."""
+        the step's H2D traffic is the parameters (KBs) rather than the sample tensor (MBs).
+        ``dynamics``: None when the GMM2D is over positions; "unicycle" / "single_integrator" when it is over
+        controls and each sample is integrated from the vehicle state x0 = (x, y, phi, v) with step ``dt`` -
+        ``dynamic.integrate_samples``, which is what p_y_xz hands back as `predictions` (prediction.py:85-86)."""
+        if dynamics not in ops.DYNAMICS:
+            raise ValueError(f"from_gmm: unknown dynamics {dynamics!r}")
         return cls.from_predictions(V, N, T, pos_last, prediction_horizon, S=Z,
-                                    sampler=dict(G=int(G), seed=int(seed)), **kw)
+                                    sampler=dict(G=int(G), seed=int(seed), dynamics=dynamics, dt=float(dt)), **kw)
 
     def run_gmm(self, latent_probs=None, mus=None, log_sigmas=None, corrs=None, log_pis=None, ref_traj=None,
-                step_seed: Optional[int] = None) -> dict:
+                step_seed: Optional[int] = None, x0=None) -> dict:
         """Sampler-mode step: GMM2D parameters in -> host rows out (one graph launch + one sync).  ``step_seed``
         is added to the plan's seed on the device, so every replay of the captured graph draws fresh samples."""
         if self.sampler is None:
             raise RuntimeError("run_gmm needs a plan built by StepPlan.from_gmm")
-        for name, val in (("mus", mus), ("log_sigmas", log_sigmas), ("corrs", corrs), ("log_pis", log_pis)):
+        for name, val in (("mus", mus), ("log_sigmas", log_sigmas), ("corrs", corrs), ("log_pis", log_pis), ("x0", x0)):
             if val is not None:
                 if self.host_gmm[name] is None:
-                    raise ValueError(f"{name} given but the plan was built with G = 1")
+                    raise ValueError(f"{name} given but the plan was built " +
+                                     ("without dynamics" if name == "x0" else "with G = 1"))
                 self.host_gmm[name].copy_(torch.as_tensor(np.asarray(val, dtype=np.float32)).reshape(self.host_gmm[name].shape))
         if latent_probs is not None:
             self.host_pmf.copy_(torch.as_tensor(np.asarray(latent_probs, dtype=np.float64)).reshape(self.host_pmf.shape))
@@ -837,7 +845,8 @@ class StepPlan:
             self.ref.copy_(self.host_ref, non_blocking=True)
             ops.gmm2d_sample(self.pmf, self.gmm["mus"], self.gmm["log_sigmas"], self.gmm["corrs"], self.pred.shape[1],
                              log_pis=self.gmm["log_pis"], seed=int(self.sampler.get("seed", 0)),
-                             seed_dev=self.gmm["seed"], out=(self.z, self.pred))
+                             seed_dev=self.gmm["seed"], out=(self.z, self.pred),
+                             dynamics=self.sampler.get("dynamics"), x0=self.gmm["x0"], dt=self.sampler.get("dt", 0.5))
             self._enqueue_ingest()
         elif self.ingest is not None:
             self.pred.copy_(self.host_pred, non_blocking=True)

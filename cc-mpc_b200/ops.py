@@ -488,12 +488,17 @@ def mc_risk(mean, cov, cross, x0, n: int, Tsh: int, ego, R: float = R_EV_OV, see
     return risk, status, x0_out
 
 
+DYNAMICS = {None: 0, "none": 0, "single_integrator": 1, "unicycle": 2}
+
+
 def gmm2d_sample(latent_pmf, mus, log_sigmas, corrs, n: int, log_pis=None, seed: int = 0, sample_offset: int = 0,
-                 noise=None, out=None, seed_dev=None):
+                 noise=None, out=None, seed_dev=None, dynamics=None, x0=None, dt: float = 0.5):
     """Stage 1 on the device (prediction.py:76-104; GMM2D.rsample of the missing Trajectron++ submodule).
     latent_pmf [V,Z] f64, mus / log_sigmas [V,Z,T,G,2] f32, corrs [V,Z,T,G] f32, log_pis [V,Z,T,G] f32 (None iff
     G = 1); noise = (u_z [V,N], u_c [V,N,T], eps [V,N,T,2]) f32 for deterministic parity, else Philox.
     seed_dev: optional int64 [1] device word added to ``seed`` at run time (fresh draws per CUDA-graph replay).
+    dynamics: None (the GMM is over positions), "single_integrator" or "unicycle" (the GMM is over controls and
+    every sample is integrated from x0 [V,4] f32 = (x, y, phi, v) with step dt: `dynamic.integrate_samples`).
     -> (z [V,N] int32, predictions [V,N,T,2] float32): the inputs of group_by_mode."""
     lib = _lib.load()
     F32 = torch.float32
@@ -517,6 +522,17 @@ def gmm2d_sample(latent_pmf, mus, log_sigmas, corrs, n: int, log_pis=None, seed:
         out = (torch.empty((V, n), dtype=torch.int32, device=mus.device),
                torch.empty((V, n, T, 2), dtype=F32, device=mus.device))
     z, pred = out
+    if dynamics not in DYNAMICS:
+        raise ValueError(f"gmm2d_sample: dynamics must be one of {sorted(k for k in DYNAMICS if k)} or None")
+    if DYNAMICS[dynamics]:
+        _chk(x0, F32, "x0", (4,))
+        if x0 is None or tuple(x0.shape) != (V, 4):
+            raise ValueError("gmm2d_sample: dynamics needs x0 [V,4] float32 (x, y, phi, v)")
+        _lib.check(lib.ccmpc_gmm2d_sample_dynamics(
+            _p(latent_pmf), _p(log_pis), _p(mus), _p(log_sigmas), _p(corrs), DYNAMICS[dynamics], _p(x0), float(dt), V,
+            int(n), Z, T, G, int(seed) & (2 ** 64 - 1), _p(seed_dev), int(sample_offset), _p(u_z), _p(u_c), _p(eps),
+            _p(z), _p(pred), _stream()), "ccmpc_gmm2d_sample_dynamics")
+        return z, pred
     _lib.check(lib.ccmpc_gmm2d_sample(_p(latent_pmf), _p(log_pis), _p(mus), _p(log_sigmas), _p(corrs), V, int(n), Z,
                                       T, G, int(seed) & (2 ** 64 - 1), _p(seed_dev), int(sample_offset), _p(u_z), _p(u_c),
                                       _p(eps),

@@ -285,6 +285,31 @@ int ccmpc_gmm2d_sample(const double* latent_pmf, const float* log_pis, const flo
                        const float* u_z, const float* u_c, const float* eps,
                        int32_t* z_out, float* predictions, void* stream);
 
+/* Stage 1 with the predictor's dynamics: the GMM2D above is over CONTROLS and every sample is
+ * integrated to positions, which is what model.p_y_xz returns as `predictions` in PREDICT mode
+ * (prediction.py:85-86: a_dist.rsample() -> dynamic.integrate_samples; Trajectron++ submodule absent,
+ * arithmetic restated from the published model/dynamics/{single_integrator,unicycle}.py, float32):
+ *   dynamics = 0 : none - identical to ccmpc_gmm2d_sample (x0, dt ignored)
+ *   dynamics = 1 : single integrator, u = velocity:  p_t = p_0 + dt * sum_{s<=t} u_s
+ *   dynamics = 2 : unicycle, u = (dphi, a), state (x, y, phi, v); per step, w = dphi if |dphi| > 1e-2 else 1:
+ *        phi' = phi + w dt, ds = (sin phi' - sin phi)/w, dc = (cos phi' - cos phi)/w
+ *        |dphi| >  1e-2: x += (a/w) dc + v ds + (a/w) sin(phi') dt; y += -v dc + (a/w) ds - (a/w) cos(phi') dt; phi = phi'
+ *        |dphi| <= 1e-2: x += v cos(phi) dt + (a/2) cos(phi) dt^2;  y += v sin(phi) dt + (a/2) sin(phi) dt^2
+ *        v += a dt
+ *   x0 [V,4] float32 (x, y, phi, v) of each vehicle at the current frame (phi already carries the
+ *   model's learned heading correction; rows 16-byte aligned), dt the predictor's step.
+ *   The control draws use the same Philox counters as ccmpc_gmm2d_sample: integrating the controls
+ *   that entry point returns (same seed / offset) reproduces this one's predictions.
+ *   Everything else as ccmpc_gmm2d_sample; T <= 256.
+ */
+int ccmpc_gmm2d_sample_dynamics(const double* latent_pmf, const float* log_pis, const float* mus,
+                                const float* log_sigmas, const float* corrs,
+                                int dynamics, const float* x0, double dt,
+                                int64_t V, int64_t N, int Z, int T, int G,
+                                uint64_t seed, const uint64_t* seed_dev, uint64_t sample_offset,
+                                const float* u_z, const float* u_c, const float* eps,
+                                int32_t* z_out, float* predictions, void* stream);
+
 /* ---------------------------------------------------------------------------
  * K1  Monte Carlo rollout.  Replaces MidlevelAgent.predict_ideal's loop body
  * (v8ideal:2662-2709) for C cells x n samples: per step t < Tsh

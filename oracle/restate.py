@@ -589,6 +589,53 @@ def gmm2d_sample(latent_pmf, log_pis, mus, log_sigmas, corrs, u_z, u_c, eps):
     return z, pred
 
 
+def integrate_samples(controls, x0, dt, dynamics="unicycle"):
+    """`dynamic.integrate_samples` of model.p_y_xz in PREDICT mode (prediction.py:85-86: the control samples of
+    a_dist.rsample() become the `predictions` the planner receives).  The code is in the Trajectron++ submodule
+    that is NOT in /root/reference; this follows the PUBLISHED model/dynamics/single_integrator.py and
+    unicycle.py (`dynamic` + `integrate_samples`), float32 like the model.  PARITY UNPINNED.
+    controls (V,N,T,2) float32; x0 (V,4) = (x, y, phi, v) at the current frame (phi includes the model's learned
+    heading correction, v = |velocity|); -> positions (V,N,T,2) float32."""
+    f = np.float32
+    u = np.asarray(controls, f)
+    x0 = np.asarray(x0, f)
+    V, N, T, _ = u.shape
+    dt = f(dt)
+    out = np.zeros((V, N, T, 2), f)
+    if dynamics == "single_integrator":
+        x = np.broadcast_to(x0[:, None, 0], (V, N)).astype(f)
+        y = np.broadcast_to(x0[:, None, 1], (V, N)).astype(f)
+        for t in range(T):
+            x = x + u[:, :, t, 0] * dt
+            y = y + u[:, :, t, 1] * dt
+            out[:, :, t, 0], out[:, :, t, 1] = x, y
+        return out
+    if dynamics != "unicycle":
+        raise ValueError(dynamics)
+    x = np.broadcast_to(x0[:, None, 0], (V, N)).astype(f)
+    y = np.broadcast_to(x0[:, None, 1], (V, N)).astype(f)
+    phi = np.broadcast_to(x0[:, None, 2], (V, N)).astype(f)
+    v = np.broadcast_to(x0[:, None, 3], (V, N)).astype(f)
+    for t in range(T):
+        dphi, a = u[:, :, t, 0], u[:, :, t, 1]
+        small = np.abs(dphi) <= f(1e-2)
+        w = np.where(small, f(1), dphi).astype(f)
+        phin = phi + w * dt
+        s0, c0, s1, c1 = np.sin(phi), np.cos(phi), np.sin(phin), np.cos(phin)
+        ds, dc = (s1 - s0) / w, (c1 - c0) / w
+        aw = a / w
+        x1 = x + aw * dc + v * ds + aw * s1 * dt
+        y1 = y - v * dc + aw * ds - aw * c1 * dt
+        x2 = x + v * c0 * dt + (a / f(2)) * c0 * (dt * dt)
+        y2 = y + v * s0 * dt + (a / f(2)) * s0 * (dt * dt)
+        x = np.where(small, x2, x1).astype(f)
+        y = np.where(small, y2, y1).astype(f)
+        phi = np.where(small, phi, phi + dphi * dt).astype(f)
+        v = (v + a * dt).astype(f)
+        out[:, :, t, 0], out[:, :, t, 1] = x, y
+    return out
+
+
 def episode_cost(X_star, U_star, goal=GOAL):
     """dataForCost_ref.py:198-232.
 

@@ -206,3 +206,33 @@ def gmm2d_params(scene: GmmScene, Z=25, slots=None, local=True):
         log_sigmas[:, sl, :, 0, 1] = np.log(sy[:, j])
         corrs[:, sl, :, 0] = scene.chol[:, j, :, 1, 0] / sy[:, j]
     return pmf, mus, log_sigmas, corrs
+
+
+def unicycle_control_params(V, Z, T, seed, G=1, dt=0.5):
+    """Synthetic predictor output in CONTROL space, the way Trajectron++ emits it for vehicles
+    (dynamic = Unicycle): per vehicle a latent pmf over Z states (Dirichlet(0.3), 1-5 states above the 0.1
+    filter of ovehicle.py:58) and, per (latent, timestep), G-component GMM2D parameters over
+    u = (heading rate [rad/s], acceleration [m/s^2]); each latent is a manoeuvre: heading rate in
+    U(-0.35, 0.35) with every fifth latent driving straight (|dphi| <= 1e-2, the small-angle branch),
+    acceleration in U(-1.5, 1.5), standard deviations 0.02-0.08 rad/s and 0.1-0.5 m/s^2.  Initial states
+    x0 = (x, y, phi, v): local-frame positions in [0,50] x [0,40], speed U(3,10) m/s (max_v = 10, v8ideal:90).
+    -> latent_pmf (V,Z) f64, log_pis (V,Z,T,G) f32 or None, mus, log_sigmas (V,Z,T,G,2) f32, corrs (V,Z,T,G) f32,
+       x0 (V,4) f32."""
+    rng = np.random.default_rng(seed)
+    pmf = rng.dirichlet(np.full(Z, 0.3), size=V)
+    turn = rng.uniform(-0.35, 0.35, (V, Z, 1, G))
+    turn[:, ::5] = rng.uniform(-8e-3, 8e-3, turn[:, ::5].shape)
+    acc = rng.uniform(-1.5, 1.5, (V, Z, 1, G))
+    mus = np.zeros((V, Z, T, G, 2), np.float32)
+    mus[..., 0] = turn + rng.normal(0, 0.01, (V, Z, T, G))
+    mus[:, ::5, :, :, 0] = turn[:, ::5]
+    mus[..., 1] = acc + rng.normal(0, 0.1, (V, Z, T, G))
+    log_sigmas = np.zeros((V, Z, T, G, 2), np.float32)
+    log_sigmas[..., 0] = np.log(rng.uniform(0.02, 0.08, (V, Z, T, G)))
+    log_sigmas[:, ::5, :, :, 0] = np.log(1e-4)          # straight manoeuvres stay inside the small-angle branch
+    log_sigmas[..., 1] = np.log(rng.uniform(0.1, 0.5, (V, Z, T, G)))
+    corrs = rng.uniform(-0.5, 0.5, (V, Z, T, G)).astype(np.float32)
+    log_pis = rng.normal(size=(V, Z, T, G)).astype(np.float32) if G > 1 else None
+    x0 = np.stack([rng.uniform(0, 50, V), rng.uniform(0, 40, V), rng.uniform(-np.pi, np.pi, V),
+                   rng.uniform(3, 10, V)], axis=1).astype(np.float32)
+    return pmf, log_pis, mus, log_sigmas, corrs, x0

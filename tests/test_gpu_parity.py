@@ -861,3 +861,99 @@ def test_minkowski_halfplanes_batched_cells_are_independent(dev, golden, accel):
     half = ops.minkowski_halfplanes(sums.repeat(reps, 1)[1::2].contiguous(), pivot.repeat(reps, 1, 1)[1::2].contiguous(),
                                     ref, eps_c[1::2].contiguous(), prediction_horizon=T, accel=accel)
     assert torch.equal(mixed["nd"][1::2], half["nd"]) and torch.equal(mixed["prob_lower"][1::2], half["prob_lower"])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dyn", ["unicycle", "single_integrator"])
+@pytest.mark.parametrize("V,N,Z,T,G", [(3, 700, 25, 16, 1), (2, 333, 7, 9, 3), (1, 1, 1, 1, 1), (2, 129, 4, 2, 1)])
+def test_gmm2d_sample_dynamics_supplied_noise_matches_oracle(dev, dyn, V, N, Z, T, G):
+    """Control-space GMM2D + dynamic.integrate_samples on the device (prediction.py:85-86; published Trajectron++
+    unicycle / single integrator, parity unpinned): same uniforms / normals in -> the oracle's latents bit-exact
+    and its float32 positions within float32 recursion round-off (the reference arithmetic IS float32; sinf/cosf
+    and FMA contraction differ from NumPy by an ulp per step, and (sin a - sin b)/dphi amplifies that by up to
+    1/dphi = 100 -> 1e-4 m per step at 10 m/s)."""
+    from ccmpc_b200 import ops
+    from oracle import restate, synth
+    pmf, lp, mus, ls, rho, x0 = synth.unicycle_control_params(V, Z, T, seed=200 + G, G=G)
+    rng = np.random.default_rng(300 + T)
+    u_z = rng.random((V, N), dtype=np.float32)
+    u_c = rng.random((V, N, T), dtype=np.float32)
+    eps = rng.standard_normal((V, N, T, 2)).astype(np.float32)
+    f = lambda a: None if a is None else torch.from_numpy(a).to(dev)
+    z, pred = ops.gmm2d_sample(T_(pmf, dev), f(mus), f(ls), f(rho), N, log_pis=f(lp), noise=(f(u_z), f(u_c), f(eps)),
+                               dynamics=dyn, x0=f(x0), dt=0.5)
+    z_ref, u_ref = restate.gmm2d_sample(pmf, lp, mus, ls, rho, u_z, u_c, eps)
+    pos_ref = restate.integrate_samples(u_ref, x0, 0.5, dyn)
+    np.testing.assert_array_equal(z.cpu().numpy(), z_ref)
+    err = np.abs(pred.cpu().numpy().astype(np.float64) - pos_ref).max(axis=(2, 3))
+    # a G > 1 component boundary one float32 ulp away can flip a draw: at most a couple of samples
+    assert (err > 2e-3).sum() <= (2 if G > 1 else 0), err.max()
+
+
+@pytest.mark.gpu
+def test_gmm2d_sample_dynamics_philox_consistent_with_control_sampler(dev):
+    """Philox mode: the dynamics entry point draws the SAME controls as ccmpc_gmm2d_sample for the same key, so
+    integrating that entry point's controls with the oracle reproduces its positions; latents are bit-identical,
+    the stream is shard invariant, dynamics = none delegates, and the output feeds group_by_mode."""
+    from ccmpc_b200 import ops
+    from oracle import restate, synth
+    V, Z, T, N = 4, 25, 16, 50_000
+    pmf, lp, mus, ls, rho, x0 = synth.unicycle_control_params(V, Z, T, seed=9, G=2)
+    f = lambda a: None if a is None else torch.from_numpy(a).to(dev)
+    args = (T_(pmf, dev), f(mus), f(ls), f(rho))
+    zc, u = ops.gmm2d_sample(*args, N, log_pis=f(lp), seed=11)
+    z0, u0 = ops.gmm2d_sample(*args, N, log_pis=f(lp), seed=11, dynamics="none")
+    assert torch.equal(z0, zc) and torch.equal(u0, u)
+    for dyn in ("unicycle", "single_integrator"):
+        z, pos = ops.gmm2d_sample(*args, N, log_pis=f(lp), seed=11, dynamics=dyn, x0=f(x0), dt=0.5)
+        assert torch.equal(z, zc)
+        want = restate.integrate_samples(u.cpu().numpy(), x0, 0.5, dyn)
+        assert np.abs(pos.cpu().numpy().astype(np.float64) - want).max() < 2e-3
+        za, pa = ops.gmm2d_sample(*args, 20_001, log_pis=f(lp), seed=11, dynamics=dyn, x0=f(x0))
+        zb, pb = ops.gmm2d_sample(*args, N - 20_001, log_pis=f(lp), seed=11, sample_offset=20_001, dynamics=dyn, x0=f(x0))
+        assert torch.equal(torch.cat([za, zb], dim=1), z) and torch.equal(torch.cat([pa, pb], dim=1), pos)
+        sd = torch.tensor([4], dtype=torch.int64, device=dev)
+        z2, p2 = ops.gmm2d_sample(*args, N, log_pis=f(lp), seed=7, seed_dev=sd, dynamics=dyn, x0=f(x0))
+        assert torch.equal(z2, z) and torch.equal(p2, pos)
+    # unicycle samples: speeds stay physical and the grouped rows are complete
+    z, pos = ops.gmm2d_sample(*args, N, log_pis=f(lp), seed=11, dynamics="unicycle", x0=f(x0))
+    step = (pos[:, :, 1:] - pos[:, :, :-1]).norm(dim=-1) / 0.5
+    assert float(step.max()) < 10 + 1.5 * 8 + 3 and torch.isfinite(pos).all()
+    g = ops.group_by_mode(pos, z, T_(pmf, dev), minpos=tuple(synth.MINPOS))
+    assert int(g["offsets"][-1]) == V * N and not g["status"].any()
+    with pytest.raises(ValueError):
+        ops.gmm2d_sample(*args, N, log_pis=f(lp), dynamics="unicycle")
+    with pytest.raises(ValueError):
+        ops.gmm2d_sample(*args, N, log_pis=f(lp), dynamics="bicycle", x0=f(x0))
+
+
+@pytest.mark.gpu
+def test_step_plan_sampler_mode_with_unicycle_dynamics(dev):
+    """StepPlan.from_gmm(dynamics="unicycle"): control-space GMM2D + unicycle integration + grouping + constraint
+    build in one CUDA graph gives exactly the rows of the ingest plan fed with the positions the dynamics sampler
+    draws for the same key; a new x0 / step_seed changes the rows without re-capturing."""
+    from ccmpc_b200 import midlevel, ops
+    from oracle import synth
+    V, Z, T, N = 3, 25, 8, 4000
+    pmf, lp, mus, ls, rho, x0 = synth.unicycle_control_params(V, Z, T, seed=77)
+    pos_last = x0[:, :2].astype(np.float64) + synth.MINPOS
+    ref = synth.reference_trajectory(T)
+    kw = dict(minpos=tuple(synth.MINPOS), device=dev, builder="affine")
+    plan = midlevel.StepPlan.from_gmm(V, N, T, pos_last, prediction_horizon=T, Z=Z, seed=40, dynamics="unicycle",
+                                      dt=0.5, **kw)
+    ing = midlevel.StepPlan.from_predictions(V, N, T, pos_last, prediction_horizon=T, S=Z, **kw)
+    f = lambda a: torch.from_numpy(a).to(dev)
+    prev = None
+    for step, x0s in ((0, x0), (1, x0 + np.float32([0.5, -0.25, 0.1, 0.3]))):
+        res = {k: v.copy() for k, v in plan.run_gmm(pmf, mus, ls, rho, ref_traj=ref, step_seed=step, x0=x0s).items()}
+        z, pos = ops.gmm2d_sample(T_(pmf, dev), f(mus), f(ls), f(rho), N, seed=40 + step, dynamics="unicycle",
+                                  x0=f(np.ascontiguousarray(x0s)), dt=0.5)
+        want = ing.run_predictions(pos.cpu().numpy(), z.cpu().numpy(), pmf, ref_traj=ref)
+        for k in res:
+            np.testing.assert_array_equal(res[k], want[k], err_msg=f"{k} differs at step {step}")
+        assert res["counts"].sum() == V * N
+        if prev is not None:
+            assert not np.array_equal(prev["mean"], res["mean"])
+        prev = res
+    with pytest.raises(ValueError):
+        midlevel.StepPlan.from_gmm(V, N, T, pos_last, prediction_horizon=T, Z=Z).run_gmm(pmf, mus, ls, rho, ref_traj=ref, x0=x0)

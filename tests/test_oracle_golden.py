@@ -188,3 +188,37 @@ def test_oracle_gmm2d_sample_restatement_is_a_gmm():
         d = mus[0, 0, 1, g].astype(np.float64) - m
         S += w[g] * (L @ L.T + np.outer(d, d))
     assert np.abs(np.cov(sel.T) - S).max() < 0.03 * np.abs(S).max() + 0.02
+
+
+def test_oracle_integrate_samples_solves_the_unicycle_ode():
+    """The integrate_samples restatement (prediction.py:85-86; Trajectron++ submodule absent => parity unpinned):
+    the published unicycle step is the EXACT solution of x' = v cos(phi), y' = v sin(phi), phi' = dphi, v' = a
+    under piecewise-constant controls, so it must agree with a fine RK4 integration of that ODE in float64;
+    the small-angle branch (|dphi| <= 1e-2) is its dphi -> 0 limit; the single integrator is a cumulative sum."""
+    from oracle import restate
+    rng = np.random.default_rng(7)
+    V, N, T, dt = 3, 40, 12, 0.5
+    u = np.stack([rng.uniform(-0.4, 0.4, (V, N, T)), rng.uniform(-2, 2, (V, N, T))], axis=-1).astype(np.float32)
+    u[:, ::4, :, 0] = rng.uniform(-9e-3, 9e-3, u[:, ::4, :, 0].shape)           # straight segments
+    x0 = np.stack([rng.uniform(0, 50, V), rng.uniform(0, 40, V), rng.uniform(-3, 3, V), rng.uniform(3, 10, V)],
+                  axis=1).astype(np.float32)
+    got = restate.integrate_samples(u, x0, dt, "unicycle").astype(np.float64)
+
+    def rhs(s, c):
+        return np.stack([s[..., 3] * np.cos(s[..., 2]), s[..., 3] * np.sin(s[..., 2]), c[..., 0], c[..., 1]], axis=-1)
+    s = np.broadcast_to(x0[:, None, :].astype(np.float64), (V, N, 4)).copy()
+    sub, want = 64, np.zeros((V, N, T, 2))
+    for t in range(T):
+        c = u[:, :, t].astype(np.float64).copy()
+        small = np.abs(c[..., 0]) <= 1e-2
+        c[..., 0] = np.where(small, 0.0, c[..., 0])          # the published small-angle branch holds the heading
+        h = dt / sub
+        for _ in range(sub):
+            k1 = rhs(s, c); k2 = rhs(s + 0.5 * h * k1, c); k3 = rhs(s + 0.5 * h * k2, c); k4 = rhs(s + h * k3, c)
+            s = s + h / 6 * (k1 + 2 * k2 + 2 * k3 + k4)
+        want[:, :, t] = s[..., :2]
+    # float32 recursion over 12 steps (incl. the (sin a - sin b)/dphi cancellation) against the float64 ODE
+    assert np.abs(got - want).max() < 5e-3
+    si = restate.integrate_samples(u, x0, dt, "single_integrator").astype(np.float64)
+    want_si = x0[:, None, None, :2].astype(np.float64) + np.cumsum(u.astype(np.float64), axis=2) * dt
+    assert np.abs(si - want_si).max() < 1e-4
