@@ -951,7 +951,7 @@ def test_step_plan_sampler_mode_with_unicycle_dynamics(dev):
         want = ing.run_predictions(pos.cpu().numpy(), z.cpu().numpy(), pmf, ref_traj=ref)
         for k in res:
             np.testing.assert_array_equal(res[k], want[k], err_msg=f"{k} differs at step {step}")
-        assert res["counts"].sum() == V * N
+        assert int(res["g_offsets"][-1]) == V * N and not res["g_status"].any()
         if prev is not None:
             assert not np.array_equal(prev["mean"], res["mean"])
         prev = res
