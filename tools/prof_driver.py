@@ -3,6 +3,7 @@
 
   python tools/prof_driver.py sweep [accel]     # c4 MVOE sweep, accel = 0 | 1 | 2
   python tools/prof_driver.py fit   [accel]     # c4-sized stand-alone footprint fit
+  python tools/prof_driver.py sums | risk | rollout | c5s   # c3 / c5 kernels
 Run WITHOUT ncu first (must exit 0), then under
   ncu --set full --clock-control none --import-source on -k regex:<kernel> -s 2 -c 1 -o gpurun_out/<name> python tools/prof_driver.py ...
 """
@@ -42,6 +43,23 @@ def main():
         for i in range(3):
             plan.run_gmm(pmf, mus, ls, rho, ref_traj=sc.ref_traj, step_seed=i)
         print("ok c5s")
+        return
+    if what == "sums":
+        O, K, T, n = 8, 4, 16, 250_000
+        C = O * K
+        sc = synth.make_scene(3, O, K, T + 1)
+        m, c, x = (torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in sc.moments())
+        m, c, x = m.reshape(C, T + 1, 2), c.reshape(C, T + 1, 2, 2), x.reshape(C, T + 1, T + 1, 2, 2)
+        ego = torch.from_numpy(synth.reference_trajectory(T)).to(dev)
+        traj = torch.empty((C, n, T, 2), dtype=torch.float64, device=dev)
+        ops.mc_rollout(m, c, x, None, n, T, seed=1, out=traj)
+        flat = traj.view(C * n, T, 2)
+        offsets = torch.arange(C + 1, dtype=torch.int64, device=dev) * n
+        pv = m[:, 1:T + 1].contiguous()
+        for i in range(4):
+            ops.sample_sums(flat, offsets, pv, ego=ego)
+        torch.cuda.synchronize()
+        print("ok sums")
         return
     if what in ("risk", "rollout"):
         O, K, T, n = 8, 4, 16, 250_000
