@@ -140,3 +140,32 @@ def test_cov_side_file_roundtrip(tmp_path):
     avrP, avrS, avrSOV, worst, X_star, U_star, goal, x_init, timeout = ep.get_data()
     assert abs(avrS - 0.2) < 1e-12 and abs(worst - 0.3) < 1e-12 and timeout == [False] * 3
     assert np.allclose(X_star[2], 2.0) and np.allclose(U_star[1], 0.1)
+
+
+def test_error_convention_argument_checks():
+    """SURVEY 8(b) error convention of the C ABI: 0 = ok, negative code + ccmpc_last_error_string() otherwise.
+    Argument validation returns before any CUDA call, so this runs without a GPU (no compute is issued: every
+    call below is rejected, the pointers are never dereferenced)."""
+    import ctypes
+    from ccmpc_b200 import _lib
+    lib = _lib.load()
+    buf = (ctypes.c_double * 64)()
+    p = ctypes.cast(buf, ctypes.c_void_p).value & ~15
+    rc = lib.ccmpc_mvoe_fit(None, None, 0.0, -1, 1e-8, 1000, 0, None, None, None, None, None)
+    assert rc == -1 and "ccmpc_mvoe_fit" in _lib.last_error()
+    rc = lib.ccmpc_mvoe_fit(None, None, 0.0, 4, 1e-8, 1000, 0, None, None, None, None, None)
+    assert rc == -1 and "null" in _lib.last_error()
+    rc = lib.ccmpc_gmm2d_sample_dynamics(None, None, None, None, None, 7, None, 0.5, 1, 1, 1, 1, 1, 0, None, 0, None,
+                                         None, None, None, None, None)
+    assert rc == -1 and "dynamics" in _lib.last_error()
+    rc = lib.ccmpc_gmm2d_sample(p, None, p, p, p, 1, 1, 1, 1, 2, 0, None, 0, None, None, None, None, p, None)
+    assert rc == -1 and "log_pis" in _lib.last_error()                       # G > 1 without mixture weights
+    rc = lib.ccmpc_sample_sums(p, p, 10, 1, 17, p, None, 0, 3.4, None, p, None, 0, None)
+    assert rc == -1 and "T" in _lib.last_error()                             # horizon beyond CCMPC_MAX_T
+    rc = lib.ccmpc_sample_sums(p, p, 10, 1, 8, p, None, 0, 3.4, None, p, None, 0, None)
+    assert rc == -3 and "workspace" in _lib.last_error()                     # CCMPC_E_WORKSPACE
+    with pytest.raises(_lib.CcmpcError, match="workspace"):
+        _lib.check(rc, "ccmpc_sample_sums")
+    # empty problems are accepted without touching the device
+    assert lib.ccmpc_gmm2d_sample(None, None, None, None, None, 0, 0, 1, 1, 1, 0, None, 0, None, None, None, None,
+                                  None, None) == 0
