@@ -32,9 +32,13 @@ rollout_kernel(const double* __restrict__ mean, const double* __restrict__ cov, 
                double* __restrict__ z_out, uint8_t* __restrict__ status, double* __restrict__ x0_out) {
     extern __shared__ __align__(16) double smem[];
     const int Tsh = TSH > 0 ? TSH : Tsh_rt;
+    // timesteps staged between two flushes: half the horizon at TSH = 16 (128 B per row and flush - still whole
+    // lines - for half the shared memory, so registers, not the tile, bound the resident warps)
+    constexpr int FL = (TSH == 16) ? 8 : TSH;
+    const int fl = FL > 0 ? FL : Tsh;
     StepParams* sp = reinterpret_cast<StepParams*>(smem);                       // [Tsh]
     double2* stage = reinterpret_cast<double2*>(smem + Tsh * SP_D);              // [128][stride2]
-    const int stride2 = Tsh | 1;
+    const int stride2 = fl | 1;
     const int tid = threadIdx.x;
     const int64_t c = blockIdx.y;
     __shared__ double s_x0[2];
@@ -44,62 +48,73 @@ rollout_kernel(const double* __restrict__ mean, const double* __restrict__ cov, 
 
     const int64_t i0 = (int64_t)blockIdx.x * RO_THREADS;
     const int64_t i = i0 + tid;
+    const bool valid = i < n;                    // lanes past the end run along (warp-level flushes) but touch no memory
     const int rows = (int)min((int64_t)RO_THREADS, n - i0);
-    if (i < n) {
-        double x = s_x0[0], y = s_x0[1];
-        const uint64_t gi = sample_offset + (uint64_t)i;
-        const uint32_t gi_lo = (uint32_t)gi, gi_hi = (uint32_t)(gi >> 32);
-        const double2* zin2 = ZIN ? reinterpret_cast<const double2*>(z_in) + (c * n + i) * Tsh : nullptr;
-        double2* zout2 = ZOUT ? reinterpret_cast<double2*>(z_out) + (c * n + i) * Tsh : nullptr;
-        double2* my_stage = stage + tid * stride2;
+    const int lane = tid & 31, w0 = tid & ~31;
+    const int wrows = min(32, rows - w0);
+    if (wrows <= 0) return;                      // whole warp past the end
+    double2* out2 = reinterpret_cast<double2*>(traj) + (c * n + i0 + w0) * Tsh;
+    const double2* wstage = stage + w0 * stride2;
 
-        auto step = [&](int t, double zx, double zy) {
-            if (ZOUT) zout2[t] = make_double2(zx, zy);
-            const StepParams& p = sp[t];
-            const double dx = x - p.mux, dy = y - p.muy;
-            const double cmx = p.mnx + fma(dx, p.a00, dy * p.a01);
-            const double cmy = p.mny + fma(dx, p.a10, dy * p.a11);
-            x = cmx + zx * p.l00;
-            y = cmy + fma(zx, p.l10, zy * p.l11);
-            my_stage[t] = make_double2(x, y);
-        };
-#pragma unroll
-        for (int t2 = 0; t2 < (TSH > 0 ? (TSH + 1) / 2 : (Tsh + 1) / 2); ++t2) {
-            const int t = 2 * t2;
-            if (ZIN) {
-                const double2 za = zin2[t];
-                step(t, za.x, za.y);
-                if (t + 1 < Tsh) {
-                    const double2 zb = zin2[t + 1];
-                    step(t + 1, zb.x, zb.y);
-                }
-            } else {
-                // one Philox block = 4 words = 2 Box-Muller pairs = the noise of steps t and t + 1
-                Philox r = philox4x32_10(gi_lo, gi_hi, (uint32_t)c, (uint32_t)t2, seed_lo, seed_hi);
-                float za, zb, zc, zd;
-                box_muller(r.c[0], r.c[1], za, zb);
-                box_muller(r.c[2], r.c[3], zc, zd);
-                step(t, (double)za, (double)zb);
-                if (t + 1 < Tsh) step(t + 1, (double)zc, (double)zd);
+    // the warp stores the timesteps [tb, tb + cnt) of the 32 rows it staged: contiguous cnt * 16 B per row
+    auto flush = [&](int tb, int cnt) {
+        __syncwarp();
+        if (FL > 0 && (32 % (FL > 0 ? FL : 1)) == 0) {
+            constexpr int TT = FL > 0 ? FL : 1;
+            constexpr int RPP = 32 / TT;                   // rows per pass
+            const int t = lane % TT, r0 = lane / TT;
+#pragma unroll 4
+            for (int r = r0; r < wrows; r += RPP) __stcs(out2 + r * Tsh + tb + t, wstage[r * stride2 + t]);
+        } else {
+            const int total = wrows * cnt;
+            for (int e = lane; e < total; e += 32) {
+                const int r = e / cnt, t = e - r * cnt;
+                __stcs(out2 + r * Tsh + tb + t, wstage[r * stride2 + t]);
             }
         }
-    }
-    __syncthreads();
-    // contiguous store of the CTA's (rows, Tsh, 2) block
-    double2* out2 = reinterpret_cast<double2*>(traj) + (c * n + i0) * Tsh;
-    if (TSH > 0 && (RO_THREADS % TSH) == 0) {
-        constexpr int TT = TSH > 0 ? TSH : 1;
-        constexpr int RPP = RO_THREADS / TT;           // rows per pass
-        const int t = tid % TT, r0 = tid / TT;
-#pragma unroll 4
-        for (int r = r0; r < rows; r += RPP) __stcs(out2 + r * TT + t, stage[r * stride2 + t]);
-    } else {
-        const int total = rows * Tsh;
-        for (int e = tid; e < total; e += RO_THREADS) {
-            const int r = e / Tsh, t = e - r * Tsh;
-            __stcs(out2 + e, stage[r * stride2 + t]);
+        __syncwarp();
+    };
+
+    double x = s_x0[0], y = s_x0[1];
+    const uint64_t gi = sample_offset + (uint64_t)i;
+    const uint32_t gi_lo = (uint32_t)gi, gi_hi = (uint32_t)(gi >> 32);
+    const double2* zin2 = ZIN ? reinterpret_cast<const double2*>(z_in) + (c * n + i) * Tsh : nullptr;
+    double2* zout2 = ZOUT ? reinterpret_cast<double2*>(z_out) + (c * n + i) * Tsh : nullptr;
+    double2* my_stage = stage + tid * stride2;
+
+    auto step = [&](int t, double zx, double zy) {
+        if (ZOUT && valid) zout2[t] = make_double2(zx, zy);
+        const StepParams& p = sp[t];
+        const double dx = x - p.mux, dy = y - p.muy;
+        const double cmx = p.mnx + fma(dx, p.a00, dy * p.a01);
+        const double cmy = p.mny + fma(dx, p.a10, dy * p.a11);
+        x = cmx + zx * p.l00;
+        y = cmy + fma(zx, p.l10, zy * p.l11);
+        my_stage[FL > 0 ? (t % FL) : t] = make_double2(x, y);
+    };
+#pragma unroll
+    for (int t2 = 0; t2 < (TSH > 0 ? (TSH + 1) / 2 : (Tsh + 1) / 2); ++t2) {
+        const int t = 2 * t2;
+        if (ZIN) {
+            const double2 za = valid ? zin2[t] : make_double2(0.0, 0.0);
+            step(t, za.x, za.y);
+            if (t + 1 < Tsh) {
+                const double2 zb = valid ? zin2[t + 1] : make_double2(0.0, 0.0);
+                step(t + 1, zb.x, zb.y);
+            }
+        } else {
+            // one Philox block = 4 words = 2 Box-Muller pairs = the noise of steps t and t + 1
+            Philox r = philox4x32_10(gi_lo, gi_hi, (uint32_t)c, (uint32_t)t2, seed_lo, seed_hi);
+            float za, zb, zc, zd;
+            box_muller(r.c[0], r.c[1], za, zb);
+            box_muller(r.c[2], r.c[3], zc, zd);
+            step(t, (double)za, (double)zb);
+            if (t + 1 < Tsh) step(t + 1, (double)zc, (double)zd);
         }
+        if (FL > 0 && FL < TSH && (t + 2) % FL == 0 && t + 2 < TSH) flush(t + 2 - FL, FL);
     }
+    if (FL > 0) flush(TSH - FL, FL);
+    else flush(0, Tsh);
 }
 
 __global__ void philox_kernel(const uint32_t* __restrict__ ctr, const uint32_t* __restrict__ key, int64_t M,
@@ -128,7 +143,7 @@ extern "C" int ccmpc_mc_rollout(const double* mean, const double* cov, const dou
         cudaError_t e = cudaMemsetAsync(status, 0, (size_t)C, st);
         if (e != cudaSuccess) { set_error("ccmpc_mc_rollout: memset: %s", cudaGetErrorString(e)); return CCMPC_E_LAUNCH; }
     }
-    const size_t smem = (size_t)Tsh * sizeof(StepParams) + (size_t)RO_THREADS * (Tsh | 1) * 16;
+    const size_t smem = (size_t)Tsh * sizeof(StepParams) + (size_t)RO_THREADS * ((Tsh == 16 ? 8 : Tsh) | 1) * 16;
     dim3 grid((unsigned)((n + RO_THREADS - 1) / RO_THREADS), (unsigned)C);
 #define CCMPC_RO_LAUNCH(TSH, ZI, ZO)                                                                          \
     rollout_kernel<TSH, ZI, ZO><<<grid, RO_THREADS, smem, st>>>(mean, cov, cross, Tm, x0, n, Tsh, (uint32_t)seed, \
