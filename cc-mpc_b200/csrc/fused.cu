@@ -118,14 +118,18 @@ rollout_sums_kernel(const double* __restrict__ mean, const double* __restrict__ 
                     my_stage[t] = make_double2(pivot[(c * TSH + t) * 2], pivot[(c * TSH + t) * 2 + 1]);
             }
         }
-        __syncthreads();
-        // ---- phase 2: contiguous store of the (rows, TSH, 2) block
+        __syncwarp();                                 // every phase works on the warp's own 32 rows: no CTA barrier,
+                                                      // so the issue-bound rollout of one warp overlaps the FP64-pipe-bound
+                                                      // sums of the others
+        // ---- phase 2: contiguous store of the warp's (wrows, TSH, 2) block
         if (traj) {
-            double2* out2 = reinterpret_cast<double2*>(traj) + (c * n + i0) * TSH;
-            constexpr int RPP = FU_THREADS / TSH;
-            const int t = tid % TSH, r0 = tid / TSH;
+            const int wrows = min(32, rows - 32 * warp);
+            double2* out2 = reinterpret_cast<double2*>(traj) + (c * n + i0 + 32 * warp) * TSH;
+            const double2* wstage = stage + 32 * warp * STRIDE2;
+            constexpr int RPP = 32 / TSH;
+            const int t = lane % TSH, r0 = lane / TSH;
 #pragma unroll 4
-            for (int rw = r0; rw < rows; rw += RPP) __stcs(out2 + rw * TSH + t, stage[rw * STRIDE2 + t]);
+            for (int rw = r0; rw < wrows; rw += RPP) __stcs(out2 + rw * TSH + t, wstage[rw * STRIDE2 + t]);
         }
         // ---- phase 3: this warp's 32 rows, 4-sample groups: shift, S1, A9 predicate, Gram update
 #pragma unroll 4
@@ -167,11 +171,12 @@ rollout_sums_kernel(const double* __restrict__ mean, const double* __restrict__ 
                 for (int bj = 0; bj <= bi; ++bj, ++ti) fu_dmma8x8x4(acc[ti][0], acc[ti][1], f[bi], f[bj]);
         }
         rows_done += rows;
-        __syncthreads();                              // the tile is overwritten by the next rollout
+        __syncwarp();                                 // the warp's rows are overwritten by its next rollout
     }
+    __syncthreads();                                  // the epilogue area aliases the staged tiles of all warps
 
     // ---- warp epilogue (as stats.cu): fixed-order shuffles over the 4 sample rows, then shared memory
-    //      (the staged tile is dead: the last loop iteration ended with a barrier)
+    //      (the staged tiles are dead: barrier above)
     double* wsm = smem + (size_t)warp * SM::PW;
 #pragma unroll
     for (int ti = 0; ti < NT; ++ti)
