@@ -23,9 +23,15 @@ namespace ccmpc {
 
 constexpr int RO_THREADS = 128;
 
+#ifndef RO_FLUSH
+#define RO_FLUSH 8
+#endif
+#ifndef RO_MIN_CTAS
+#define RO_MIN_CTAS 1
+#endif
 // TSH > 0: compile-time horizon (fully unrolled step loop, shift/mask index math); TSH = 0: runtime Tsh.
 template <int TSH, bool ZIN, bool ZOUT>
-__global__ void __launch_bounds__(RO_THREADS)
+__global__ void __launch_bounds__(RO_THREADS, RO_MIN_CTAS)
 rollout_kernel(const double* __restrict__ mean, const double* __restrict__ cov, const double* __restrict__ cross,
                int Tm, const double* __restrict__ x0, int64_t n, int Tsh_rt, uint32_t seed_lo, uint32_t seed_hi,
                uint64_t sample_offset, const double* __restrict__ z_in, double* __restrict__ traj,
@@ -34,7 +40,7 @@ rollout_kernel(const double* __restrict__ mean, const double* __restrict__ cov, 
     const int Tsh = TSH > 0 ? TSH : Tsh_rt;
     // timesteps staged between two flushes: half the horizon at TSH = 16 (128 B per row and flush - still whole
     // lines - for half the shared memory, so registers, not the tile, bound the resident warps)
-    constexpr int FL = (TSH == 16) ? 8 : TSH;
+    constexpr int FL = (TSH == 16 || TSH == 8) ? RO_FLUSH : TSH;
     const int fl = FL > 0 ? FL : Tsh;
     StepParams* sp = reinterpret_cast<StepParams*>(smem);                       // [Tsh]
     double2* stage = reinterpret_cast<double2*>(smem + Tsh * SP_D);              // [128][stride2]
@@ -143,7 +149,7 @@ extern "C" int ccmpc_mc_rollout(const double* mean, const double* cov, const dou
         cudaError_t e = cudaMemsetAsync(status, 0, (size_t)C, st);
         if (e != cudaSuccess) { set_error("ccmpc_mc_rollout: memset: %s", cudaGetErrorString(e)); return CCMPC_E_LAUNCH; }
     }
-    const size_t smem = (size_t)Tsh * sizeof(StepParams) + (size_t)RO_THREADS * ((Tsh == 16 ? 8 : Tsh) | 1) * 16;
+    const size_t smem = (size_t)Tsh * sizeof(StepParams) + (size_t)RO_THREADS * (((Tsh == 16 || Tsh == 8) ? RO_FLUSH : Tsh) | 1) * 16;
     dim3 grid((unsigned)((n + RO_THREADS - 1) / RO_THREADS), (unsigned)C);
 #define CCMPC_RO_LAUNCH(TSH, ZI, ZO)                                                                          \
     rollout_kernel<TSH, ZI, ZO><<<grid, RO_THREADS, smem, st>>>(mean, cov, cross, Tm, x0, n, Tsh, (uint32_t)seed, \
