@@ -19,9 +19,15 @@ namespace ccmpc {
 
 constexpr int ST_THREADS = 256;
 constexpr int SS_WARPS = ST_THREADS / 32;
-constexpr int SS_DEPTH = 3;            // 4-sample groups in flight per warp (register prefetch ring)
+#ifndef SS_DEPTH_DEF
+#define SS_DEPTH_DEF 3
+#endif
+constexpr int SS_DEPTH = SS_DEPTH_DEF;            // 4-sample groups in flight per warp (register prefetch ring)
 constexpr int SS_DEPTH_YAW = 2;        // ... when the yaw tensor is streamed as well (register budget)
-constexpr int SS_SLAB = 2048;          // samples per unit (= per CTA) for large inputs; see pick_slab()
+#ifndef SS_SLAB_DEF
+#define SS_SLAB_DEF 2048
+#endif
+constexpr int SS_SLAB = SS_SLAB_DEF;          // samples per unit (= per CTA) for large inputs; see pick_slab()
 
 // ---------------------------------------------------------------------------
 // The 2T x 2T second-moment matrix is a Gram matrix  G = U^T U  over samples
@@ -99,8 +105,13 @@ __global__ void __launch_bounds__(ST_THREADS, 2) sample_sums_kernel(const StatsA
     const int64_t c = lo;                // cub[c] <= u < cub[c+1]: empty cells own no unit and are never hit
     const int slab_idx = u - a.cub[c];
     const int64_t cell_end = a.offsets[c + 1];
-    const int64_t begin = a.offsets[c] + (int64_t)slab_idx * a.slab;
-    const int rows_unit = (int)min((int64_t)a.slab, cell_end - begin);
+    // balanced split: the cell's ceil(n_c / slab) units get equal shares (multiples of 4 rows) instead of
+    // full slabs + a remainder, so one wave of CTAs finishes together
+    const int64_t n_cell = cell_end - a.offsets[c];
+    const int units_cell = a.cub[c + 1] - a.cub[c];
+    const int64_t share = (((n_cell + units_cell - 1) / units_cell) + 3) & ~(int64_t)3;
+    const int64_t begin = a.offsets[c] + (int64_t)slab_idx * share;
+    const int rows_unit = (int)max((int64_t)0, min(share, cell_end - begin));
     const int ngroups = (rows_unit + 3) >> 2;
     const int rounds = (ngroups + GPR - 1) / GPR;          // uniform loop bounds: the DMMAs below sit in
     const int full_rounds = (rows_unit >> 2) / GPR;        // provably convergent control flow
@@ -477,16 +488,24 @@ static int64_t max_units(int64_t n_total, int64_t C, int slab) { return n_total 
 // Samples per CTA.  2048 amortises the CTA epilogue at Monte Carlo sizes; one MPC step (c2: 20 000 rows,
 // c5: 160 000 rows) would then fill only 10-80 of the 296 resident CTA slots, so the slab shrinks (power of
 // two, >= 256) until the grid covers the machine about once.
-static int pick_slab(int64_t n_total) {
+// Large inputs over few cells (c3: 8M rows, 32 cells): ONE wave - the slab grows until the at most
+// n_total / slab + C units fit the 296 resident CTA slots, so the per-unit prologue / epilogue (~3.6 us: unit
+// lookup, pipeline fill, CTA reduction, partial vector) is paid once per CTA instead of 13 times.
+static int pick_slab(int64_t n_total, int64_t C) {
+    const int64_t slots = 148 * 2;
+    if (C <= slots / 2) {
+        const int64_t one_wave = ((n_total + (slots - C) - 1) / (slots - C) + 3) & ~(int64_t)3;
+        if (one_wave >= SS_SLAB && one_wave < ((int64_t)1 << 24)) return (int)one_wave;
+    }
     int slab = SS_SLAB;
-    while (slab > 256 && n_total / slab < 148 * 2) slab >>= 1;
+    while (slab > 256 && n_total / slab < slots) slab >>= 1;
     return slab;
 }
 
 extern "C" size_t ccmpc_sample_sums_workspace_bytes(int64_t n_total, int64_t C, int T) {
     if (T < 1 || T > CCMPC_MAX_T || n_total < 0 || C < 0) return 0;
     size_t cub = ((size_t)(C + 1) * sizeof(int32_t) + 255) / 256 * 256;
-    return cub + (size_t)max_units(n_total, C, pick_slab(n_total)) * SumsLayout(T).len * sizeof(double) + 256;
+    return cub + (size_t)max_units(n_total, C, pick_slab(n_total, C)) * SumsLayout(T).len * sizeof(double) + 256;
 }
 
 extern "C" int ccmpc_sample_sums(const double* samples, const int64_t* offsets, int64_t n_total, int64_t C, int T,
@@ -509,7 +528,7 @@ extern "C" int ccmpc_sample_sums(const double* samples, const int64_t* offsets, 
     int32_t* cub = reinterpret_cast<int32_t*>(workspace);
     size_t cub_bytes = ((size_t)(C + 1) * sizeof(int32_t) + 255) / 256 * 256;
     double* partials = reinterpret_cast<double*>(reinterpret_cast<char*>(workspace) + cub_bytes);
-    const int slab = pick_slab(n_total);
+    const int slab = pick_slab(n_total, C);
     unit_scan_kernel<<<1, 1024, 0, st>>>(offsets, C, slab, cub);
     int rc = check_launch("unit_scan_kernel");
     if (rc) return rc;
