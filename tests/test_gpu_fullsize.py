@@ -192,3 +192,50 @@ def test_c5_fullsize_step_against_oracle(dev):
         assert np.allclose(res["aff_offset_rhs"][c][:, 1], ref["rhs"], rtol=1e-9, atol=0)
         coll, any_, _, _ = restate.collision_counts(cell, sc.ref_traj)
         assert np.array_equal(res["counts"][c][:T], coll) and res["counts"][c][T] == any_
+
+
+# ------------------------------------------------------------------------------------------ ragged one-wave sums
+@pytest.mark.parametrize("T", [16, 8, 5])
+def test_sample_sums_one_wave_ragged_cells(dev, T):
+    """Large input over few ragged cells (empty, 1 row, sizes that are not multiples of 4): sample_sums runs as ONE
+    wave of balanced units.  Counts are bit-exact against plain torch fp64 elementwise ops, every sum matches a
+    per-cell launch (which takes the small-input slab path) to round-off, and the row counts add up."""
+    from ccmpc_b200 import ops
+    sizes = [0, 1, 123_457, 700_001, 3, 250_000, 99_999, 0, 31]
+    C, N = len(sizes), sum(sizes)
+    g = torch.Generator(device=dev).manual_seed(17 + T)
+    centre = torch.rand((C, 1, T, 2), generator=g, device=dev, dtype=torch.float64) * 40 + 150
+    offsets = torch.tensor(np.concatenate([[0], np.cumsum(sizes)]), dtype=torch.int64, device=dev)
+    samples = torch.empty((N, T, 2), dtype=torch.float64, device=dev)
+    for c, n in enumerate(sizes):
+        if n:
+            samples[offsets[c]:offsets[c + 1]] = centre[c] + torch.randn((n, T, 2), generator=g, device=dev,
+                                                                         dtype=torch.float64) * 2.0
+    pivot = ops.cell_pivot(samples, offsets)
+    ego = (centre[:, 0] + 2.5).contiguous()                          # per-cell plan about 3.5 m from the centre
+    sums = ops.sample_sums(samples, offsets, pivot, ego=ego, R=3.4)
+    L = ops.sums_layout(T) if hasattr(ops, "sums_layout") else None
+    s = sums.cpu().numpy()
+    np.testing.assert_array_equal(s[:, 0], np.array(sizes, dtype=np.float64))
+    for c, n in enumerate(sizes):
+        if not n:
+            assert not s[c].any()
+            continue
+        x = samples[offsets[c]:offsets[c + 1]]
+        one = ops.sample_sums(x.contiguous(), torch.tensor([0, n], dtype=torch.int64, device=dev),
+                              pivot[c:c + 1].contiguous(), ego=ego[c:c + 1].contiguous(), R=3.4).cpu().numpy()[0]
+        scale = np.maximum(np.abs(one), 1.0)
+        assert np.max(np.abs(s[c] - one) / scale) < 1e-10, c
+        # A9 counts, same operation order as the oracle (no FMA): torch elementwise fp64
+        dx, dy = ego[c, :, 0] - x[:, :, 0], ego[c, :, 1] - x[:, :, 1]
+        hit = (dx * dx + dy * dy) < 3.4 * 3.4
+        coll = hit.sum(dim=0).cpu().numpy().astype(np.float64)
+        anyc = float(hit.any(dim=1).sum())
+        if L is not None:
+            np.testing.assert_array_equal(s[c, L["coll"]:L["coll"] + T], coll)
+            assert s[c, L["coll"] + T] == anyc
+        else:
+            m = ops.moments_from_sums(sums, pivot)
+            np.testing.assert_array_equal(m["counts"][c, :T].cpu().numpy().astype(np.float64), coll)
+            assert float(m["counts"][c, T]) == anyc
+        assert coll.sum() > 0 or n < 100
