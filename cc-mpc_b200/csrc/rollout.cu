@@ -27,7 +27,7 @@ constexpr int RO_THREADS = 128;
 #define RO_FLUSH 8
 #endif
 #ifndef RO_MIN_CTAS
-#define RO_MIN_CTAS 1
+#define RO_MIN_CTAS 8
 #endif
 // TSH > 0: compile-time horizon (fully unrolled step loop, shift/mask index math); TSH = 0: runtime Tsh.
 template <int TSH, bool ZIN, bool ZOUT>
@@ -52,15 +52,20 @@ rollout_kernel(const double* __restrict__ mean, const double* __restrict__ cov, 
     rollout_setup<RO_THREADS>(mean, cov, cross, Tm, x0, c, Tsh, seed_lo, seed_hi, sp, s_x0, status, x0_out, tid);
     __syncthreads();
 
-    const int64_t i0 = (int64_t)blockIdx.x * RO_THREADS;
+    // persistent over the cell's 128-sample tiles: the per-step parameters above are built once per CTA, not
+    // once per tile (ncu: with one tile per CTA the setup barrier was the second largest stall)
+    const int lane = tid & 31, w0 = tid & ~31;
+    double2* my_stage = stage + tid * stride2;
+    const double2* wstage = stage + w0 * stride2;
+    const int64_t ntiles = (n + RO_THREADS - 1) / RO_THREADS;
+    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const int64_t i0 = tile * RO_THREADS;
     const int64_t i = i0 + tid;
     const bool valid = i < n;                    // lanes past the end run along (warp-level flushes) but touch no memory
     const int rows = (int)min((int64_t)RO_THREADS, n - i0);
-    const int lane = tid & 31, w0 = tid & ~31;
     const int wrows = min(32, rows - w0);
-    if (wrows <= 0) return;                      // whole warp past the end
+    if (wrows <= 0) continue;                    // whole warp past the end
     double2* out2 = reinterpret_cast<double2*>(traj) + (c * n + i0 + w0) * Tsh;
-    const double2* wstage = stage + w0 * stride2;
 
     // the warp stores the timesteps [tb, tb + cnt) of the 32 rows it staged: contiguous cnt * 16 B per row
     auto flush = [&](int tb, int cnt) {
@@ -86,7 +91,6 @@ rollout_kernel(const double* __restrict__ mean, const double* __restrict__ cov, 
     const uint32_t gi_lo = (uint32_t)gi, gi_hi = (uint32_t)(gi >> 32);
     const double2* zin2 = ZIN ? reinterpret_cast<const double2*>(z_in) + (c * n + i) * Tsh : nullptr;
     double2* zout2 = ZOUT ? reinterpret_cast<double2*>(z_out) + (c * n + i) * Tsh : nullptr;
-    double2* my_stage = stage + tid * stride2;
 
     auto step = [&](int t, double zx, double zy) {
         if (ZOUT && valid) zout2[t] = make_double2(zx, zy);
@@ -121,6 +125,7 @@ rollout_kernel(const double* __restrict__ mean, const double* __restrict__ cov, 
     }
     if (FL > 0) flush(TSH - FL, FL);
     else flush(0, Tsh);
+    }   // tiles of this CTA
 }
 
 __global__ void philox_kernel(const uint32_t* __restrict__ ctr, const uint32_t* __restrict__ key, int64_t M,
@@ -150,7 +155,10 @@ extern "C" int ccmpc_mc_rollout(const double* mean, const double* cov, const dou
         if (e != cudaSuccess) { set_error("ccmpc_mc_rollout: memset: %s", cudaGetErrorString(e)); return CCMPC_E_LAUNCH; }
     }
     const size_t smem = (size_t)Tsh * sizeof(StepParams) + (size_t)RO_THREADS * (((Tsh == 16 || Tsh == 8) ? RO_FLUSH : Tsh) | 1) * 16;
-    dim3 grid((unsigned)((n + RO_THREADS - 1) / RO_THREADS), (unsigned)C);
+    // one wave: at most 148 * RO_MIN_CTAS resident CTAs over all cells, each looping over its cell's tiles
+    const int64_t ntiles = (n + RO_THREADS - 1) / RO_THREADS;
+    const int64_t cap = std::max<int64_t>(1, (148 * RO_MIN_CTAS) / C);
+    dim3 grid((unsigned)std::min(ntiles, cap), (unsigned)C);
 #define CCMPC_RO_LAUNCH(TSH, ZI, ZO)                                                                          \
     rollout_kernel<TSH, ZI, ZO><<<grid, RO_THREADS, smem, st>>>(mean, cov, cross, Tm, x0, n, Tsh, (uint32_t)seed, \
                                                                 (uint32_t)(seed >> 32), sample_offset, z, traj,   \
