@@ -241,6 +241,19 @@ def run_ours(args):
     pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
     mean_p, cov_p, cross_p, ego_p = (pin(mean_h.reshape(C, T + 1, 2)), pin(cov_h.reshape(C, T + 1, 2, 2)),
                                      pin(cross_h.reshape(C, T + 1, T + 1, 2, 2)), pin(ego_h))
+    # the step's host inputs live in ONE pinned arena (one H2D copy per step on the end-to-end leg)
+    _parts = (mean_h.reshape(C, T + 1, 2), cov_h.reshape(C, T + 1, 2, 2), cross_h.reshape(C, T + 1, T + 1, 2, 2), ego_h)
+    _sizes = [int(np.prod(a.shape)) for a in _parts]
+    arena_p = torch.empty(sum(_sizes), dtype=torch.float64).pin_memory()
+    arena_d = torch.empty(sum(_sizes), dtype=torch.float64, device=dev)
+    _o, host_views, dev_views = 0, [], []
+    for a, sz in zip(_parts, _sizes):
+        arena_p[_o:_o + sz].copy_(torch.from_numpy(np.ascontiguousarray(a)).reshape(-1))
+        host_views.append(arena_p[_o:_o + sz].view(a.shape))
+        dev_views.append(arena_d[_o:_o + sz].view(a.shape))
+        _o += sz
+    mean_p, cov_p, cross_p, ego_p = host_views
+    pivot_e2e = torch.empty((C, T, 2), dtype=torch.float64, device=dev)
     mean_d, cov_d, cross_d, ego_d = (t.to(dev) for t in (mean_p, cov_p, cross_p, ego_p))
     pivot = mean_d[:, 1:T + 1].contiguous()
     traj = torch.empty((C, n, T, 2), dtype=torch.float64, device=dev)
@@ -255,8 +268,10 @@ def run_ours(args):
     def step(i, events=None, from_host=False):
         nonlocal mom_out
         if from_host:
-            m, c, x, e = (t.to(dev, non_blocking=True) for t in (mean_p, cov_p, cross_p, ego_p))
-            pv = m[:, 1:T + 1].contiguous()
+            arena_d.copy_(arena_p, non_blocking=True)
+            m, c, x, e = dev_views
+            pv = pivot_e2e
+            pv.copy_(m[:, 1:T + 1])
         else:
             m, c, x, e, pv = mean_d, cov_d, cross_d, ego_d, pivot
         if events:
