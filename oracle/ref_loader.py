@@ -63,3 +63,62 @@ def npu():
             sys.path.remove(root)
         _cache["npu"] = ref_npu
     return _cache["npu"]
+
+
+# --------------------------------------------------------------------------
+# Executing single functions / methods of modules that cannot be IMPORTED here
+# --------------------------------------------------------------------------
+# v8ideal/__init__.py, midlevel/util.py, midlevel/ovehicle.py and
+# dataForCost_ref.py import carla / cvxpy / docplex / matplotlib / control /
+# openpyxl at module level, but the bodies of the functions on the hot path use
+# only numpy / scipy / pickle / os / logging / copy.  `extract` parses the
+# reference file, takes the named FunctionDef nodes (nothing else of the file
+# is compiled or executed, nothing is copied into this repo) and executes them
+# in a caller-supplied namespace.  Methods are re-wrapped in a ClassDef of the
+# reference's class name so that private-name mangling (`self.__params`,
+# `self.__compute_vertices`) resolves exactly as in the reference.
+import ast
+
+V8IDEAL = "collect/in_simulation/midlevel/v8ideal/__init__.py"
+MIDLEVEL_UTIL = "collect/in_simulation/midlevel/util.py"
+OVEHICLE = "collect/in_simulation/midlevel/ovehicle.py"
+DATA_FOR_COST = "dataForCost_ref.py"
+
+
+def _find_defs(tree, names, class_name=None):
+    body = tree.body
+    if class_name is not None:
+        cls = [n for n in body if isinstance(n, ast.ClassDef) and n.name == class_name]
+        if not cls:
+            raise KeyError(class_name)
+        body = cls[0].body
+    found = {n.name: n for n in body if isinstance(n, ast.FunctionDef) and n.name in names}
+    missing = [n for n in names if n not in found]
+    if missing:
+        raise KeyError(f"{missing} not found")
+    return [found[n] for n in names]
+
+
+def extract(rel: str, names, namespace: dict, class_name: str = None):
+    """Compile ONLY the named functions of reference file ``rel`` and exec them in ``namespace``.
+
+    With ``class_name`` the functions are that class's methods; a class of the same name holding only
+    those methods is created in ``namespace`` (decorators such as ``@classmethod`` are kept,
+    ``@profile``-style project decorators must be present in the namespace).  Returns the namespace."""
+    path = os.path.join(REFERENCE_ROOT, rel)
+    import warnings
+    with open(path, "r", encoding="utf-8") as f, warnings.catch_warnings():
+        warnings.simplefilter("ignore", SyntaxWarning)       # plot labels elsewhere in the file
+        tree = ast.parse(f.read(), filename=path)
+    defs = _find_defs(tree, list(names), class_name)
+    if class_name is None:
+        mod = ast.Module(body=defs, type_ignores=[])
+    else:
+        cls = ast.ClassDef(name=class_name, bases=[ast.Name(id="object", ctx=ast.Load())], keywords=[],
+                           body=defs, decorator_list=[])
+        if "type_params" in ast.ClassDef._fields:
+            cls.type_params = []
+        mod = ast.Module(body=[cls], type_ignores=[])
+    ast.fix_missing_locations(mod)
+    exec(compile(mod, path, "exec"), namespace)      # line numbers stay the reference's own
+    return namespace
