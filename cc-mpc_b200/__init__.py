@@ -16,7 +16,7 @@ compute call needs the CUDA library and a CUDA device and fails loudly otherwise
 """
 from . import _build, _lib  # noqa: F401
 
-__version__ = "0.1.0"
+__version__ = "0.2.0"
 
 
 def build(force: bool = False) -> str:

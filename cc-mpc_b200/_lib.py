@@ -18,6 +18,7 @@ SIGNATURES = {
     "ccmpc_version": (c_int, []),
     "ccmpc_last_error_string": (c_char_p, []),
     "ccmpc_launch_count": (c_uint64, []),
+    "ccmpc_source_hash": (c_uint64, []),
     "ccmpc_mvoe_fit": (c_int, [_P, _P, c_double, c_int64, c_double, c_int, c_int, _P, _P, _P, _P, _P]),
     "ccmpc_mvoe_halfplane_sweep": (c_int, [_P, _P, _P, c_int64, c_int, c_int, c_int, c_double, c_double, c_double,
                                             c_int, c_int, _P, _P, _P, _P, _P]),
@@ -41,6 +42,8 @@ SIGNATURES = {
     "ccmpc_group_by_mode": (c_int, [_P, _P, _P, _P, c_int64, c_int64, c_int, c_int, c_double, c_double, c_double,
                                      _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, c_size_t, _P]),
     "ccmpc_episode_cost": (c_int, [_P, _P, _P, c_int64, c_int, c_double, c_double, _P, _P, _P]),
+    "ccmpc_halfplanes_to_block": (c_int, [_P, c_int, _P, c_int, _P, _P, c_int64, c_int, c_int, c_int, _P, c_int64, _P, _P,
+                                           _P, _P, _P, _P, _P]),
     "ccmpc_philox4x32": (c_int, [_P, _P, c_int64, _P, _P]),
     "ccmpc_mc_risk_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int]),
     "ccmpc_mc_risk": (c_int, [_P, _P, _P, c_int, _P, c_int64, c_int64, c_int, c_uint64, c_uint64, _P, c_int64, c_double,
@@ -76,6 +79,12 @@ def load(build_if_missing: bool = True):
         if not build_if_missing:
             raise CcmpcError(f"{path} not found (run `python -m ccmpc_b200._build`); there is no fallback path")
         _build.build_library()
+    elif _build.is_stale():
+        # a .so older than csrc/ or include/ccmpc.h would be called with the NEW argument lists below:
+        # rebuild when a compiler is here, refuse otherwise (no silent ABI mismatch)
+        if _build.find_nvcc() is None:
+            raise CcmpcError(f"{path} is older than its sources and nvcc is not available to rebuild it")
+        _build.build_library(force=True)
     lib = ctypes.CDLL(path)
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(lib, name)      # AttributeError if the symbol is missing: fail loudly
@@ -83,6 +92,9 @@ def load(build_if_missing: bool = True):
         fn.argtypes = args
     if lib.ccmpc_version() <= 0:
         raise CcmpcError("libccmpc.so reports a bad version")
+    if int(lib.ccmpc_source_hash()) != _build.source_hash():
+        raise CcmpcError(f"{path} was built from other sources than the ones next to it "
+                         f"(run `python -m ccmpc_b200._build --force`)")
     _lib = lib
     return lib
 

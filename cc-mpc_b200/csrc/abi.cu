@@ -32,3 +32,7 @@ int check_launch(const char* what) {
 extern "C" int ccmpc_version(void) { return CCMPC_VERSION; }
 extern "C" const char* ccmpc_last_error_string(void) { return ccmpc::g_err; }
 extern "C" uint64_t ccmpc_launch_count(void) { return ccmpc::g_launches.load(std::memory_order_relaxed); }
+#ifndef CCMPC_SRC_HASH
+#define CCMPC_SRC_HASH 0ULL
+#endif
+extern "C" uint64_t ccmpc_source_hash(void) { return CCMPC_SRC_HASH; }

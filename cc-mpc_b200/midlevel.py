@@ -53,6 +53,42 @@ def eps_allocation(K_per_obstacle: Sequence[int], eps: float = EPS_TOTAL) -> np.
     return out
 
 
+def _accel_mode(accel) -> int:
+    """0: the reference's iterate sequence (makeconstraint:24-32); 1: float32 warm start, same fp64 map and
+    stopping rule; 2: direct solve of the stationarity cubic accepted under the reference's rule."""
+    a = int(accel)
+    if a not in (0, 1, 2) or (not isinstance(accel, (bool, int, np.integer))):
+        raise ValueError(f"accel must be 0, 1 or 2 (got {accel!r})")
+    return a
+
+
+def raise_for_status(status: np.ndarray, populated: Optional[np.ndarray] = None, what: str = "constraint build"):
+    """Turn the per-row ``status`` bytes of a builder into the exception the reference raises at the same point.
+
+    ST_SINGULAR            ``np.linalg.inv(cov_tau)`` on a singular matrix (makeconstraint:65; also a cell with
+                           fewer than 2 samples, whose np.cov is NaN) -> ``np.linalg.LinAlgError``
+    ST_NO_TANGENT          ``choose_closest_tangent`` returned 4 x None and ``n_star @ mean`` fails
+                           (makeconstraint:191-192, v8ideal:926) -> ``TypeError``
+    ST_DEGENERATE_SLOPE    ``ref_y == mean_y``: the reference divides by zero (v8ideal:923) and hands +-inf / NaN
+                           rows to the solver, which rejects them -> ``InSimulationException``
+    ST_NOT_CONVERGED       the fixed point did not meet the tolerance in maxiter steps: the reference returns the
+                           last iterate silently, and so do we (no exception).
+    ``populated`` [C] masks out cells that hold no samples by construction (fixed-layout ingest plans)."""
+    st = np.asarray(status)
+    if populated is not None:
+        st = st[np.asarray(populated, dtype=bool)]
+    if not st.size:
+        return
+    for code, exc, msg in ((ops.ST_SINGULAR, np.linalg.LinAlgError, "Singular matrix"),
+                           (ops.ST_NO_TANGENT, TypeError,
+                            "unsupported operand type(s) for @: 'NoneType' and 'numpy.ndarray'"),
+                           (ops.ST_DEGENERATE_SLOPE, InSimulationException,
+                            "reference point and obstacle mean share the y coordinate: tangent slope is infinite")):
+        hit = np.argwhere(st == code)
+        if hit.size:
+            raise exc(f"{msg} ({what}: {hit.shape[0]} row(s), first at index {tuple(int(i) for i in hit[0])})")
+
+
 def _h2d(arr: np.ndarray, device, dtype=None) -> torch.Tensor:
     """Host ndarray -> device through a pinned staging buffer (async on the current stream)."""
     t = torch.from_numpy(np.ascontiguousarray(arr))
@@ -220,6 +256,27 @@ class HalfPlanes:
     cell_obstacle: np.ndarray
     cell_mode: np.ndarray
     extra: Dict[str, np.ndarray] = field(default_factory=dict)
+    dev: Optional[dict] = None   # device tensors of the same rows (nd, rhs, idx_side, t) for :meth:`block`
+    T: int = 0                   # horizon of the rows (columns of the stacked state = nx * T)
+
+    def block(self, nx: int = 4, nu: int = 2, Gamma=None, x_bar=None, u_bar=None, T: Optional[int] = None,
+              to_host: bool = True):
+        """All rows as ONE inequality block in the planner's stacked state x (X = x.reshape(T, nx), v8ideal:2894):
+        ``A_x @ x <= b_x`` - what ``cvxpy_constraints`` hands over as one Python expression per row
+        (v8ideal:927-936).  With the LTV model ``Gamma, x_bar, u_bar`` of v8ideal:2873-2889 the block is also
+        given in the decision variable: ``A_u @ u <= b_u``.  Built on the device (ccmpc_halfplanes_to_block)."""
+        if self.dev is None:
+            raise RuntimeError("these rows were not produced by a builder (no device handles)")
+        raise_for_status(self.status, what="block")
+        T = int(self.T if T is None else T)
+        d = self.dev
+        g = xb = ub = None
+        if Gamma is not None:
+            dev = d["nd"].device
+            g, xb, ub = (_h2d(np.asarray(a, dtype=np.float64), dev) for a in (Gamma, x_bar, u_bar))
+        out = ops.halfplanes_to_block(d["nd"], d["rhs"], d["idx_side"], d["t"], T, nx=nx, nu=nu, gamma=g, x_bar=xb,
+                                      u_bar=ub)
+        return {k: v.cpu().numpy() for k, v in out.items()} if to_host else out
 
     def A_b(self):
         """(A, b) with A x <= b, the form v8ideal:933-939 saves."""
@@ -230,6 +287,7 @@ class HalfPlanes:
     def cvxpy_constraints(self, temp_x):
         """Rows as cvxpy constraints on the planner's ``temp_x`` (v8ideal:927-936 / :1503-1515)."""
         import cvxpy as cp  # planner-side dependency; not needed by the kernels
+        raise_for_status(self.status, what="cvxpy_constraints")
         rows = []
         flat_n = self.n.reshape(-1, 2)
         for r in range(flat_n.shape[0]):
@@ -249,10 +307,11 @@ class MidlevelConstraints:
 
     def __init__(self, prediction_horizon: int, ego_vehicle_id: int = 0, out_dir: Optional[str] = "out/data",
                  device=None, R: float = ops.R_EV_OV, target_p: float = ops.TARGET_P,
-                 n_ideal_samples: int = N_IDEAL_SAMPLES, seed: int = 0, accel: bool = False,
+                 n_ideal_samples: int = N_IDEAL_SAMPLES, seed: int = 0, accel: int = 0,
                  frame_stride: int = 10):
         if not 1 <= prediction_horizon <= ops.MAX_T:
             raise ValueError(f"prediction_horizon must be in 1..{ops.MAX_T}")
+        self.accel = _accel_mode(accel)
         self.prediction_horizon = int(prediction_horizon)
         self.ego_vehicle_id = ego_vehicle_id
         self.out_dir = out_dir
@@ -261,7 +320,6 @@ class MidlevelConstraints:
         self.target_p = float(target_p)
         self.n_ideal_samples = int(n_ideal_samples)
         self.seed = int(seed)
-        self.accel = bool(accel)
         self.frame_stride = int(frame_stride)          # predict_ideal reads frame - 10 (v8ideal:2626)
         self._moments: Dict[int, Moments] = {}
         self._calls = 0
@@ -483,12 +541,16 @@ class MidlevelConstraints:
 
     def compute_obstacle_constraints_GMM_Minkowski_idealprediction(
             self, params, ovehicles, Delta2=None, Omicron=None, temp_x=None, eps_ura=None, segments=None,
-            Tsh=None, ref_traj=None, ego=None, want_violations=False):
+            Tsh=None, ref_traj=None, ego=None, want_violations=False, ideal_noise: Optional[dict] = None):
         """v8ideal:781-964.  Returns the reference's 9-tuple
         ``(constraints, vertices, A_union, b_union, OVconstraint, direct, ovStateMean_tau_1,
         ovStateCov_tau_1, 0)`` where ``constraints`` is a :class:`HalfPlanes` (or the list of
         cvxpy rows when ``temp_x`` is given) and ``vertices`` is a zero-argument callable that
-        materialises the per-sample box corners on demand (only plots read them)."""
+        materialises the per-sample box corners on demand (only plots read them).
+
+        ``ideal_noise`` = dict(x0 [C,2], z [C,n,Tsh,2] device tensor) replaces the Philox draws of the
+        predict_ideal branch (deterministic parity mode).  A degenerate cell raises what the reference
+        raises at the same point (:func:`raise_for_status`)."""
         cells = ovehicles if isinstance(ovehicles, CellBatch) else CellBatch.from_ovehicles(ovehicles, self.device)
         Tpred = self.prediction_horizon
         T = int(Tsh if Tsh is not None else Tpred)
@@ -496,9 +558,11 @@ class MidlevelConstraints:
             eps_ura = eps_allocation(cells.n_states)
         if cells.T != Tpred:
             raise ValueError(f"cells carry horizon {cells.T}; the planner's prediction_horizon is {Tpred}")
+        if getattr(self, "road_boundary_constraints", False) and (Omicron is not None or segments is not None):
+            raise NotImplementedError("road-boundary slack S_big (v8ideal:797-818) is not part of this path")
         # sums of the raw predictions: L4 polytopes, [tau+1|tau] bookkeeping, and the rows when T == Tpred
         if T < Tpred:
-            self.predict_ideal(cells, T, self.ego_vehicle_id, params)               # :824-825
+            self.predict_ideal(cells, T, self.ego_vehicle_id, params, **(ideal_noise or {}))   # :824-825
             work = self.last_ideal
             out, sums_w, pivot_w = self.minkowski(work, ref_traj, eps_ura, ego=ego, want_violations=want_violations)
             sums_c, pivot_c = self._sums(cells)
@@ -510,18 +574,22 @@ class MidlevelConstraints:
         moments = self.moments_of(work, sums_w, pivot_w)
         # ---- one synchronising copy of the small results
         host = {k: v.cpu().numpy() for k, v in out.items()}
+        raise_for_status(host["status"], what="Minkowski builder")                   # :907, :924-926
         A_union = self._nested_tko(cells, At.cpu().numpy(), Tpred)
         b_union = self._nested_tko(cells, b0.cpu().numpy(), Tpred)
         ov_mean, ov_cov, inj = self._ov_state(cells, mom)
-        OVconstraint = any(bool(v) for v in inj)
+        OVconstraint = any(bool(v) for v in inj)                                     # :849-851
         direct = [None] * cells.O
         side = np.where(host["idx_side"] & 2, -1, 1).astype(np.int32)
         C, P = side.shape
+        t_rows = np.broadcast_to(_pair_t(T), (C, P)).copy()
         hp = HalfPlanes(n=host["nd"][..., :2], d=host["nd"][..., 2], rhs=host["nd"][..., 2],
                         idx=(host["idx_side"] & 1).astype(np.int32), side=side,
-                        t=np.broadcast_to(_pair_t(T), (C, P)).copy(), status=host["status"],
+                        t=t_rows, status=host["status"],
                         cell_obstacle=work.cell_obstacle, cell_mode=work.cell_mode,
-                        extra={k: host[k] for k in host if k not in ("nd", "idx_side", "status")})
+                        extra={k: host[k] for k in host if k not in ("nd", "idx_side", "status")},
+                        dev=dict(nd=out["nd"], rhs=out["nd"][..., 2], idx_side=out["idx_side"],
+                                 t=_h2d(t_rows, self.device)), T=T)
         self.save_moments(None, cells.O, cells.n_states, T, Tpred, self.ego_vehicle_id, params,
                           _precomputed=moments)                                       # :960
         # prob_lower_save[t] is overwritten across (o, k): the last cell wins (:947)
@@ -536,7 +604,8 @@ class MidlevelConstraints:
             self, params, ovehicles, Delta2=None, Omicron=None, temp_x=None, eps_ura=None, segments=None,
             Tsh=None, ref_traj=None):
         """v8ideal:1378-1539 (receding horizon, nominal).  Same 9-tuple; rows are
-        ``n.x >= d + offset`` / ``n.x <= d - offset`` (:1503-1515)."""
+        ``n.x >= d + offset`` / ``n.x <= d - offset`` (:1503-1515).  ``OVconstraint`` is always False:
+        the reference hard-codes ``out_junction = False`` (:1424)."""
         cells = ovehicles if isinstance(ovehicles, CellBatch) else CellBatch.from_ovehicles(ovehicles, self.device)
         Tpred = self.prediction_horizon
         T = int(Tsh if Tsh is not None else Tpred)
@@ -544,6 +613,9 @@ class MidlevelConstraints:
             eps_ura = eps_allocation(cells.n_states)
         if cells.T != Tpred:
             raise ValueError(f"cells carry horizon {cells.T}; the planner's prediction_horizon is {Tpred}")
+        if getattr(self, "road_boundary_constraints", False) and (Omicron is not None or segments is not None):
+            # the reference adds the slack S_big_repeated[0, t] to every row here (:1505, :1511)
+            raise NotImplementedError("road-boundary slack S_big (v8ideal:1395-1416) is not part of this path")
         ref_np = np.zeros((Tpred, 2))
         r = np.asarray(ref_traj, dtype=np.float64)[:, :2]
         ref_np[:min(T, r.shape[0])] = r[:T]
@@ -552,42 +624,57 @@ class MidlevelConstraints:
                                     R=self.R)
         At, b0, mom = self._l4(cells, sums, pivot)
         host = {k: v.cpu().numpy()[:, :T] for k, v in out.items()}
+        raise_for_status(host["status"], what="affine builder")                       # :1499-1503
         A_union = self._nested_tko(cells, At.cpu().numpy(), Tpred)
         b_union = self._nested_tko(cells, b0.cpu().numpy(), Tpred)
-        ov_mean, ov_cov, inj = self._ov_state(cells, mom)
+        ov_mean, ov_cov, _ = self._ov_state(cells, mom)
         side = np.where(host["idx_side"] & 2, -1, 1).astype(np.int32)
         C = side.shape[0]
+        t_rows = np.broadcast_to(np.arange(T, dtype=np.int32), (C, T)).copy()
+        dev_rows = {k: out[k][:, :T].contiguous() for k in ("nd", "offset_rhs", "idx_side")}
         hp = HalfPlanes(n=host["nd"][..., :2], d=host["nd"][..., 2], rhs=host["offset_rhs"][..., 1],
                         idx=(host["idx_side"] & 1).astype(np.int32), side=side,
-                        t=np.broadcast_to(np.arange(T, dtype=np.int32), (C, T)).copy(), status=host["status"],
+                        t=t_rows, status=host["status"],
                         cell_obstacle=cells.cell_obstacle, cell_mode=cells.cell_mode,
-                        extra=dict(offset=host["offset_rhs"][..., 0], mean=host["mean"], cov=host["cov"]))
+                        extra=dict(offset=host["offset_rhs"][..., 0], mean=host["mean"], cov=host["cov"]),
+                        dev=dict(nd=dev_rows["nd"], rhs=dev_rows["offset_rhs"][..., 1], idx_side=dev_rows["idx_side"],
+                                 t=_h2d(t_rows, self.device)), T=T)
         constraints = hp.cvxpy_constraints(temp_x) if temp_x is not None else hp
-        # the affine builder only reports OV presence when out_junction is set (:1443-1446); callers that
-        # need it pass the flag through params
-        OVconstraint = any(bool(v) for v in inj) if getattr(params, "out_junction", True) else False
+        OVconstraint = False                                                          # out_junction = False (:1424)
         return (constraints, self._vertices(cells), A_union, b_union, OVconstraint, [None] * cells.O, ov_mean,
                 ov_cov, 0)
 
     # ------------------------------------------------------ MC risk estimate
     def mc_collision_risk(self, moments: Moments, n_states, T: int, ego_xy, n_samples: Optional[int] = None,
-                          seed: Optional[int] = None, sample_offset: int = 0, process_group=None,
-                          want_moments: bool = True):
+                          seed: Optional[int] = None, sample_offset: Optional[int] = None, process_group=None,
+                          want_moments: bool = True, x0=None, z=None):
         """Stage 1 of the path: rollout n samples per (o, k) cell from the moments, then ONE read of
         the trajectories -> collision counts (A9), soft cost and the shifted power sums; with a
         ``process_group`` the packed sums are all-reduced (sum) across sample shards.
 
+        ``n_samples`` is the TOTAL per cell: with a ``process_group`` and no explicit ``sample_offset`` this rank
+        rolls its ``sharding.sample_shard`` of them (Philox counter = global sample index, so the union of the
+        shards does not depend on the world size); an explicit ``sample_offset`` means "roll exactly n_samples
+        here, starting at that global index" (weak scaling).
+
         Returns dict(sums [C, L] device, counts [C, T+1] int64 device, pivot, cells)."""
-        cells = self.predict_ideal_cells(n_states, T, moments, n_samples=n_samples, seed=seed,
-                                         sample_offset=sample_offset)
+        from . import sharding
+        n = self.n_ideal_samples if n_samples is None else int(n_samples)
+        if sample_offset is None:
+            sample_offset = 0
+            if process_group is not None:
+                import torch.distributed as dist
+                sample_offset, n = sharding.sample_shard(n, dist.get_rank(process_group),
+                                                         dist.get_world_size(process_group))
+        cells = self.predict_ideal_cells(n_states, T, moments, n_samples=n, seed=seed,
+                                         sample_offset=sample_offset, x0=x0, z=z)
         # common pivot on every rank: the moment means x_{t+1} ~ mean[t+1]  (SURVEY 8e)
         idx = [int(np.nonzero((moments.cell_obstacle == o) & (moments.cell_mode == min(k, max(moments.n_states) - 1)))[0][0])
                for o, k in zip(cells.cell_obstacle, cells.cell_mode)]
         pivot = moments.mean.index_select(0, torch.as_tensor(idx, device=self.device))[:, 1:T + 1].contiguous()
         sums, _ = self._sums(cells, ego=ego_xy, pivot=pivot)
         if process_group is not None:
-            import torch.distributed as dist
-            dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=process_group)
+            sharding.allreduce_sums(sums, group=process_group)
         mom = ops.moments_from_sums(sums, pivot, want_cross=want_moments, want_counts=True, want_yaw=False)
         return dict(sums=sums, counts=mom["counts"], pivot=pivot, cells=cells, moments=mom)
 
@@ -618,7 +705,7 @@ class StepPlan:
 
     def __init__(self, offsets_host, cell_obstacle, cell_mode, n_states, pos_last_cell, T: int,
                  prediction_horizon: int, eps_ura=None, device=None, bbox=BBOX_DEFAULT, R: float = ops.R_EV_OV,
-                 target_p: float = ops.TARGET_P, accel: bool = False, use_graph: bool = True,
+                 target_p: float = ops.TARGET_P, accel: int = 0, use_graph: bool = True,
                  builder: str = "minkowski", ingest: Optional[dict] = None):
         if builder not in ("minkowski", "affine", "both"):
             raise ValueError("builder must be 'minkowski' (shrinking horizon, v8ideal:881-947), "
@@ -632,7 +719,7 @@ class StepPlan:
         self.C = int(self.offsets_host.size - 1)
         self.N = int(self.offsets_host[-1])
         self.P = self.T * (self.T - 1) // 2
-        self.R, self.target_p, self.accel = float(R), float(target_p), bool(accel)
+        self.R, self.target_p, self.accel = float(R), float(target_p), _accel_mode(accel)
         dev = self.device
         if eps_ura is None:
             eps_ura = eps_allocation(self.n_states)

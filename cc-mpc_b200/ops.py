@@ -42,6 +42,10 @@ def _chk(t: Optional[torch.Tensor], dtype, name: str, shape_tail=None):
         raise TypeError(f"{name}: expected dtype {dtype}, got {t.dtype}")
     if not t.is_contiguous():
         raise ValueError(f"{name}: tensor must be contiguous")
+    if t.data_ptr() % 16:
+        # the kernels move double2 / float4 / 16-byte staged records: a contiguous view that starts at an odd
+        # element (e.g. sigma[1:] of an [M,3] tensor) would fault with a sticky misaligned-address error
+        raise ValueError(f"{name}: data pointer must be 16-byte aligned (pass a fresh tensor, not an offset view)")
     if shape_tail is not None and tuple(t.shape[-len(shape_tail):]) != tuple(shape_tail):
         raise ValueError(f"{name}: trailing shape {tuple(t.shape)} does not end with {tuple(shape_tail)}")
     return t
@@ -291,6 +295,58 @@ def violation_counts(samples, offsets, nd, idx_side, out=None):
         out = _new((C, P), I64, samples)
     _lib.check(lib.ccmpc_violation_counts(_p(samples), _p(offsets), N, C, T, _p(nd), _p(idx_side), _p(out),
                                           _stream()), "ccmpc_violation_counts")
+    return out
+
+
+def halfplanes_to_block(nd, rhs, idx_side, t_of_row, T: int, nx: int = 4, nu: int = 2, gamma=None, x_bar=None,
+                        u_bar=None, want_state_block: bool = True, out: Optional[dict] = None):
+    """Emitted rows -> ONE solver-ready block instead of one cvxpy row each (v8ideal:927-936, :1503-1515).
+
+    nd [..., >=2] (unit rows n0, n1 first), rhs [...] or a strided view column (e.g. nd[..., 2] or
+    offset_rhs[..., 1]), idx_side [...] int8, t_of_row [...] int32.
+    -> dict(A_x [rows, nx T], b_x [rows]) with ``A_x @ x <= b_x`` in the stacked state of v8ideal:2873-2894,
+    plus (A_u [rows, nu T], b_u [rows]) with ``A_u @ u <= b_u`` when the LTV model (gamma, x_bar, u_bar) is given."""
+    lib = _lib.load()
+    _chk(nd, F64, "nd"); _chk(idx_side, I8, "idx_side"); _chk(t_of_row, I32, "t_of_row")
+    nd_stride = int(nd.shape[-1])
+    rows = idx_side.numel()
+    if nd.numel() != rows * nd_stride or t_of_row.numel() != rows:
+        raise ValueError("halfplanes_to_block: nd / idx_side / t_of_row disagree on the number of rows")
+    # rhs may be a column view of a [rows, k] tensor: pass base pointer of the column + its stride
+    if not (isinstance(rhs, torch.Tensor) and rhs.is_cuda and rhs.dtype == F64 and rhs.numel() == rows):
+        raise TypeError("rhs: expected a float64 CUDA tensor with one entry per row")
+    flat = rhs.reshape(-1) if rhs.is_contiguous() else rhs
+    strides = [st for st, sz in zip(flat.stride(), flat.shape) if sz > 1]
+    rhs_stride = 1 if flat.is_contiguous() else (strides[-1] if strides else 1)
+    if not flat.is_contiguous():
+        # a column of a contiguous [..., k] tensor: consecutive rows are k apart in every leading dimension
+        exp, ok = rhs_stride, True
+        for st, sz in reversed(list(zip(flat.stride(), flat.shape))):
+            ok &= (sz == 1 or st == exp)
+            exp *= sz
+        if not ok:
+            raise ValueError("rhs: only contiguous tensors or a last-axis column of one are supported")
+    dev = nd.device
+    if out is None:
+        out = {}
+        if want_state_block:
+            out["A_x"] = torch.empty((rows, nx * T), dtype=F64, device=dev)
+            out["b_x"] = torch.empty((rows,), dtype=F64, device=dev)
+        if gamma is not None:
+            out["A_u"] = torch.empty((rows, nu * T), dtype=F64, device=dev)
+            out["b_u"] = torch.empty((rows,), dtype=F64, device=dev)
+    ldg = 0
+    if gamma is not None:
+        _chk(gamma, F64, "gamma"); _chk(x_bar, F64, "x_bar"); _chk(u_bar, F64, "u_bar")
+        if gamma.dim() != 2 or gamma.shape[0] < nx * T or gamma.shape[1] < nu * T or x_bar.numel() < nx * T \
+                or u_bar.numel() < nu * T:
+            raise ValueError("gamma must be [>= nx T, >= nu T], x_bar [>= nx T], u_bar [>= nu T]")
+        ldg = int(gamma.shape[1])
+    _lib.check(lib.ccmpc_halfplanes_to_block(_p(nd), nd_stride, ctypes.c_void_p(rhs.data_ptr()), int(rhs_stride),
+                                             _p(idx_side), _p(t_of_row), rows, int(T), int(nx), int(nu), _p(gamma),
+                                             ldg, _p(x_bar), _p(u_bar), _p(out.get("A_x")), _p(out.get("b_x")),
+                                             _p(out.get("A_u")), _p(out.get("b_u")), _stream()),
+               "ccmpc_halfplanes_to_block")
     return out
 
 

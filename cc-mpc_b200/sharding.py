@@ -49,6 +49,12 @@ def allreduce_sums(sums: torch.Tensor, group=None, async_op: bool = False):
         raise TypeError("packed sums are float64")
     if not dist.is_initialized() or dist.get_world_size(group) == 1:
         return None
+    if sums.is_cuda and dist.get_backend(group) == "gloo":
+        # host-side test rigs (several ranks on one GPU): gloo reduces a host copy
+        host = sums.cpu()
+        dist.all_reduce(host, op=dist.ReduceOp.SUM, group=group)
+        sums.copy_(host)
+        return None
     return dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group, async_op=async_op)
 
 

@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define CCMPC_VERSION 100          /* 0.1.0 */
+#define CCMPC_VERSION 200          /* 0.2.0 */
 #define CCMPC_MAX_T 16             /* longest horizon handled (reference: ph8 / ph16) */
 
 #define CCMPC_OK 0
@@ -54,6 +54,9 @@ int ccmpc_version(void);
 const char* ccmpc_last_error_string(void);
 /* number of libccmpc kernels launched by this process so far (every kernel launch is counted once) */
 uint64_t ccmpc_launch_count(void);
+/* digest of the sources this binary was built from (the Python binding refuses a library whose digest differs
+ * from the sources next to it: a stale build would be called with the wrong argument lists) */
+uint64_t ccmpc_source_hash(void);
 
 /* ---------------------------------------------------------------------------
  * K3  batched MVOE fit.   Replaces makeconstraint.compute_mvoe (:7-38).
@@ -381,6 +384,26 @@ int ccmpc_mc_rollout_sums(const double* mean, const double* cov, const double* c
                           const double* pivot, const double* ego, int64_t ego_cell_stride, double R,
                           double* traj, double* sums, uint8_t* status, double* x0_out,
                           void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------
+ * 8f-4  solver-ready inequality blocks.  Replaces the per-row cvxpy expressions of
+ * v8ideal:927-936 (Minkowski) / :1503-1515 (affine) - one Python object per (o,k,t,tau) - by ONE
+ * dense block in the planner's stacked-state layout x = Gamma (u - u_bar) + x_bar,
+ * X = x.reshape(T, nx) (v8ideal:2873-2894; temp_x[t] = X[t, 0:2], :2931).
+ *   nd [rows, nd_stride >= 2] unit rows (n0, n1, ...); rhs [rows, rhs_stride] right-hand sides
+ *   (Minkowski: the d column of nd, stride 3; affine: offset_rhs[..., 1], stride 2);
+ *   idx_side [rows] int8 (bit1 set: n.x <= rhs, clear: n.x >= rhs); t_of_row [rows] int32.
+ *   out A_x [rows, nx T], b_x [rows]:  A_x x <= b_x  with A_x[r, nx t + (0,1)] = -side n, b_x = -side rhs
+ *   (the (A, b) the reference saves at :931-939), zeros elsewhere.
+ *   Optional (gamma != NULL): gamma [nx T, ldg] row-major (ldg >= nu T), x_bar [nx T], u_bar [nu T]
+ *   (bicycle_v2.py:261-308, built on the host) -> A_u [rows, nu T], b_u [rows] with
+ *   A_u = A_x Gamma[:, :nu T],  b_u = b_x - A_x (x_bar - Gamma u_bar):  A_u u <= b_u.
+ *   Either output pair may be NULL.
+ */
+int ccmpc_halfplanes_to_block(const double* nd, int nd_stride, const double* rhs, int rhs_stride,
+                              const int8_t* idx_side, const int32_t* t_of_row, int64_t rows, int T, int nx, int nu,
+                              const double* gamma, int64_t ldg, const double* x_bar, const double* u_bar,
+                              double* A_x, double* b_x, double* A_u, double* b_u, void* stream);
 
 /* Philox-4x32-10 known-answer hook: out[i] = philox(ctr[i], key[i]) (4 words each). */
 int ccmpc_philox4x32(const uint32_t* ctr, const uint32_t* key, int64_t M, uint32_t* out, void* stream);

@@ -25,7 +25,7 @@ def test_library_exports_every_declared_symbol():
         assert hasattr(lib, n), f"{n} declared in include/ccmpc.h but not exported by libccmpc.so"
         assert n in _lib.SIGNATURES, f"{n} has no ctypes signature"
     assert sorted(_lib.SIGNATURES) == names, "ctypes table and header disagree"
-    assert lib.ccmpc_version() == 100
+    assert lib.ccmpc_version() == 200
     assert lib.ccmpc_sums_len(8) == 1 + 16 + 16 * 17 // 2 + 8 + 1 + 8 + 8 + 8 + 8
     assert lib.ccmpc_sums_len(0) == -1 and lib.ccmpc_sums_len(17) == -1
     assert lib.ccmpc_sample_sums_workspace_bytes(5000 * 4, 100, 8) > 0
