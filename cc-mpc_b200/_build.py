@@ -79,12 +79,14 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
     obj_dir = os.path.join(HERE, "build")
     os.makedirs(obj_dir, exist_ok=True)
     headers = [os.path.normpath(os.path.join(CSRC, x)) for x in HEADERS]
-    flags = [f for f in NVCC_FLAGS if f != "-shared"]
+    extra_env = os.environ.get("CCMPC_EXTRA_NVCC_FLAGS", "").split()     # e.g. -DCCMPC_WS_EXPERIMENTS (tools only)
+    flags = [f for f in NVCC_FLAGS if f != "-shared"] + extra_env
 
     def compile_one(src):
         name = os.path.basename(src)
         extra = [f"-DCCMPC_SRC_HASH=0x{digest:016x}ULL"] if name == "abi.cu" else []
-        tag = _file_digest([src] + headers) + (f"{digest:016x}" if extra else "")
+        tag = _file_digest([src] + headers) + (f"{digest:016x}" if extra else "") + \
+            ("x" + format(abs(hash(tuple(extra_env))) % (1 << 32), "08x") if extra_env else "")
         obj = os.path.join(obj_dir, f"{name}.{tag}.o")
         if os.path.isfile(obj) and not (force and verbose):
             return obj, ""

@@ -1,269 +1,497 @@
 // fused.cu - K1 + K2 + K6 in one kernel: Monte Carlo rollout, trajectory store and the one-pass sums.
 //
 // ccmpc_mc_rollout writes the (C, n, T, 2) trajectory tensor and ccmpc_sample_sums reads it straight back
-// (32 B of HBM traffic per trajectory-step).  Here the CTA that rolls 128 samples out keeps them in shared
-// memory (the transpose tile the rollout kernel stages its coalesced store through anyway), writes them to
-// HBM once, and feeds the SAME tile to the FP64 mma.sync Gram update and the A9 predicate of sample_sums:
-// 16 B per trajectory-step, and the issue-bound rollout phase of one CTA overlaps the FP64-pipe-bound sums
-// phase of its neighbours on the SM.
+// (32 B of HBM traffic per trajectory-step).  Here the samples go through shared memory once: they are
+// written to HBM from there (16 B per trajectory-step) and the SAME tile feeds the FP64 mma.sync Gram
+// update and the A9 predicate.
 //
 //   rollout:  predict_ideal body v8ideal:2662-2709 - same Philox counters and arithmetic as rollout.cu
 //             (sample i of cell c is bit-identical to ccmpc_mc_rollout's)
 //   sums:     np.mean / np.cov of every (t, tau) pair (makeconstraint:55, v8ideal:2586-2606) + A9 counts,
-//             same fragment layout, predicate order and packed layout as stats.cu (ccmpc.h "sums layout")
+//             same fragment layout, predicate order and packed layout as stats.cu (sums_common.cuh)
+//
+// WARP-SPECIALISED, ONE CTA PER SM (round 2).  What binds this kernel is the FP64 pipe, and
+// tools/fp64_sched_bench.cu (profiles/r02_fp64_sched_bench.txt) shows how it is shared on B200:
+//   * one warp per sub-partition issuing mma.sync.m8n8k4.f64 (DMMA) saturates it: 16.3 clk per DMMA;
+//   * a vector FP64 instruction of ANOTHER warp only gets in between two DMMAs: ~25 clk each, whatever the
+//     instruction-level parallelism of that warp, while the DMMA stream loses only ~7 %;
+//   * two DMMA warps on one sub-partition halve each other, and the vector FP64 of one (shift, S1, predicate)
+//     waits for the other's DMMAs.
+// So: exactly ONE consumer warp per sub-partition owns the Gram update (warps 0-3, `setmaxnreg.inc` to 128
+// registers), its own vector FP64 instructions are the only ones on its critical path and are kept to the
+// pivot shift and S1 (the A9 predicate is screened on the integer pipe, below), and the rollout - a long
+// dependent chain of Philox (integer), Box-Muller (MUFU) and 7 FMAs per step that does not mind waiting for
+// DMMA gaps - runs in 20 producer warps (`setmaxnreg.dec` to 64).  A tile = 32 samples x T timesteps, one
+// sample per producer lane, kept as T/8 sub-tiles of [32 rows][128 B] in the TMA 128-byte swizzle (16-byte
+// chunk j of row i sits at chunk j ^ (i & 7)): the lane-per-row writes of one timestep spread over all banks
+// AND the tile is the image a TMA tensor store un-swizzles into the row-major (C, n, T, 2) trajectory tensor.
+// Tiles travel through a ring of 24 shared-memory buffers guarded by mbarriers (full: producer -> consumer;
+// empty: consumer + the producer's own "TMA finished reading" -> next producer).  ONE lane per producer warp
+// stores the finished tile with T/8 cp.async.bulk.tensor instructions (4 KB each; rows past the end of the
+// cell are clipped by the tensor map).
+//
+// Work split: the tiles of all cells form one list, CTA j takes the j-th contiguous share of it; where a share
+// crosses a cell boundary the CTA finishes the cell (partial sums vector out, accumulators cleared, step
+// parameters of the next cell built) and carries on: every SM gets the same number of tiles whatever C is.
+//
+// Measured on the way (c3, one B200; profiles/r02_fused_notes.txt): round-1 kernel 0.817 ms; warp-specialised
+// with one cp.async.bulk per LANE 0.977 ms (the instruction takes uniform operands, the compiler serialises
+// it over the lanes: 18 % of all warp instructions); one TMA tensor store per tile 0.735 ms; two CTAs per SM
+// (two consumer warps per sub-partition) could not get below 0.74 ms for the reason above.
+//
 // Restrictions of this fast path: Philox noise, horizon 8 or 16, no yaw sums.
+#include <stdlib.h>
+#include <string.h>
+#include <cuda.h>          // CUtensorMap (types only: the encoder is fetched through cudaGetDriverEntryPoint)
+
 #include "rollout.cuh"
+#include "sums_common.cuh"
 
 namespace ccmpc {
 
-constexpr int FU_THREADS = 128;
-constexpr int FU_WARPS = FU_THREADS / 32;
-#ifndef FU_CTAS_PER_SM
-#define FU_CTAS_PER_SM 4
+constexpr int WS_CONS = 4;                            // consumer warps: one warpgroup, one warp per sub-partition
+#ifndef WS_PROD_DEF
+#define WS_PROD_DEF 20
 #endif
+constexpr int WS_PROD = WS_PROD_DEF;                  // producer warps (whole warpgroups)
+constexpr int WS_THREADS = 32 * (WS_CONS + WS_PROD);
+constexpr int WS_NB = 24;                             // tile buffers in the ring
+// launch allocation 80 registers x 768 threads; 128 x 128 + 640 x 64 fits it
+constexpr int WS_REGS_CONS = 128, WS_REGS_PROD = 64;
+static_assert(WS_PROD % 4 == 0, "setmaxnreg works on whole warpgroups");
 
-__device__ __forceinline__ void fu_dmma8x8x4(double& c0, double& c1, double a, double b) {
-    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
-                 : "+d"(c0), "+d"(c1)
-                 : "d"(a), "d"(b));
+// ---- mbarrier / bulk-copy PTX ----------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("{\n .reg .b64 st;\n mbarrier.arrive.shared::cta.b64 st, [%0];\n}" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n .reg .pred p;\n"
+        "WAIT_%=:\n"
+        " mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        " @p bra DONE_%=;\n"
+        " bra WAIT_%=;\n"
+        "DONE_%=:\n}" ::"r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+}
+// one [32 rows][16 doubles] box of the (2 T doubles, n samples, C cells) view of the trajectory tensor
+__device__ __forceinline__ void tma_store_box(const CUtensorMap* map, const void* ssrc, int c0, int c1, int c2) {
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(map),
+                 "r"(smem_u32(ssrc)), "r"(c0), "r"(c1), "r"(c2)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() {
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void cta_bar() { asm volatile("bar.sync 2, %0;" ::"n"(WS_THREADS) : "memory"); }
+
+// hi word of a double -> unsigned key ordered like the value (ties in the low word compare equal)
+__device__ __forceinline__ uint32_t hi_key(double v) {
+    const int h = __double2hiint(v);
+    return (uint32_t)h ^ ((uint32_t)(h >> 31) | 0x80000000u);
 }
 
+// EXP: compile-time experiment switches (tools/fused_time.py <exp>): which part of the kernel binds?
+//   bit0 no Gram update, bit1 no A9 predicate, bit2 no Philox / Box-Muller, bit3 no chain.  0 in production.
+static int g_ws_exp = 0;          // read only when built with -DCCMPC_WS_EXPERIMENTS
+[[maybe_unused]] static int* const g_ws_exp_ref = &g_ws_exp;
+
 template <int NF>
-struct FusedSmem {                                   // per-warp epilogue area (doubles), as StatsSmem in stats.cu
-    static constexpr int NT = NF * (NF + 1) / 2;
-    static constexpr int TP = 4 * NF;
-    static constexpr int O_S1 = NT * 64;
-    static constexpr int O_COLL = O_S1 + 8 * NF;
-    static constexpr int O_PEN = O_COLL + TP;
-    static constexpr int O_D2S = O_PEN + TP;
-    static constexpr int O_ANY = O_D2S + TP;
-    static constexpr int PW = O_ANY + 2;
+struct WsLayout {                                     // dynamic shared memory of rollout_sums_ws_kernel
+    static constexpr int TSH = 4 * NF;
+    static constexpr int H = TSH / 8;                 // 128-byte sub-tiles per tile
+    static constexpr size_t SUB = 32 * 128;           // [32 rows][8 double2], 128-byte swizzle
+    static constexpr size_t TILE = H * SUB;
+    static constexpr size_t O_RING = 0;               // 1024-byte aligned: the swizzle pattern is address based
+    static constexpr size_t O_AREA = O_RING + WS_NB * TILE;                     // consumer epilogue areas
+    static constexpr size_t O_SP = O_AREA + (size_t)WS_CONS * SumsWarpArea<NF>::PW * 8;   // StepParams[TSH]
+    static constexpr size_t O_BAR = O_SP + (size_t)TSH * sizeof(StepParams);   // full[NB], empty[NB]
+    static constexpr size_t O_X0 = O_BAR + 2 * WS_NB * 8;
+    static constexpr size_t BYTES = O_X0 + 16;
 };
 
-// TSH = 4 NF timesteps.  grid (gx, C): CTA (bx, c) rolls out and reduces tiles bx, bx + gx, ... of cell c.
-template <int NF>
-__global__ void __launch_bounds__(FU_THREADS, FU_CTAS_PER_SM)
-rollout_sums_kernel(const double* __restrict__ mean, const double* __restrict__ cov, const double* __restrict__ cross,
-                    int Tm, const double* __restrict__ x0, int64_t n, uint32_t seed_lo, uint32_t seed_hi,
-                    uint64_t sample_offset, const double* __restrict__ pivot, const double* __restrict__ ego,
-                    int64_t ego_cell_stride, double r2, double* __restrict__ traj, double* __restrict__ partials,
-                    uint8_t* __restrict__ status, double* __restrict__ x0_out) {
-    constexpr int TSH = 4 * NF;
-    constexpr int NT = FusedSmem<NF>::NT;
-    constexpr int TS = NF / 2;                       // timesteps per lane
-    constexpr int STRIDE2 = TSH | 1;                 // double2 per staged row (odd: conflict-free row writes)
-    using SM = FusedSmem<NF>;
-    extern __shared__ __align__(16) double smem[];
-    StepParams* sp = reinterpret_cast<StepParams*>(smem);                        // [TSH]
-    double2* stage = reinterpret_cast<double2*>(smem + TSH * SP_D);               // [128][STRIDE2]
-    __shared__ double s_x0[2];
+// grid G (<= number of SMs): CTA j handles global tiles [j TT / G, (j + 1) TT / G), TT = C ceil(n / 32).
+// partial sums of the segment (CTA j, cell c) go to slot j + c of `partials`, `slot_cell[j + c] = c`.
+template <int NF, int EXP = 0>
+__global__ void __launch_bounds__(WS_THREADS, 1)
+rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict__ cov,
+                       const double* __restrict__ cross, int Tm, const double* __restrict__ x0, int64_t n,
+                       uint32_t seed_lo, uint32_t seed_hi, uint64_t sample_offset,
+                       const double* __restrict__ pivot, const double* __restrict__ ego, int64_t ego_cell_stride,
+                       double r2, const __grid_constant__ CUtensorMap traj_map, int store_traj,
+                       double* __restrict__ partials, int32_t* __restrict__ slot_cell, uint8_t* __restrict__ status,
+                       double* __restrict__ x0_out, int64_t C) {
+    using WL = WsLayout<NF>;
+    using SM = SumsWarpArea<NF>;
+    constexpr int TSH = WL::TSH, TS = NF / 2, NT = SM::NT;
+    constexpr int exp_flags = EXP;
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    unsigned char* ring = smem_raw + WL::O_RING;
+    double* area = reinterpret_cast<double*>(smem_raw + WL::O_AREA);
+    StepParams* sp = reinterpret_cast<StepParams*>(smem_raw + WL::O_SP);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + WL::O_BAR);
+    uint64_t* empty = full + WS_NB;
+    double* s_x0 = reinterpret_cast<double*>(smem_raw + WL::O_X0);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int r = lane & 3, q = lane >> 2;
-    const int64_t c = blockIdx.y;
 
-    rollout_setup<FU_THREADS>(mean, cov, cross, Tm, x0, c, TSH, seed_lo, seed_hi, sp, s_x0, status, x0_out, tid);
-
-    // ---- per-lane constants of the sums phase: its TS timesteps
-    double pivx[TS], pivy[TS], ex[TS], ey[TS];
-#pragma unroll
-    for (int i = 0; i < TS; ++i) {
-        const int t = TS * q + i;
-        pivx[i] = pivot[(c * TSH + t) * 2];
-        pivy[i] = pivot[(c * TSH + t) * 2 + 1];
-        ex[i] = ego[c * ego_cell_stride + 2 * t];
-        ey[i] = ego[c * ego_cell_stride + 2 * t + 1];
+    if (tid == 0) {
+        for (int b = 0; b < WS_NB; ++b) { mbar_init(full + b, 1); mbar_init(empty + b, 2); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    double acc[NT][2];
-#pragma unroll
-    for (int i = 0; i < NT; ++i) acc[i][0] = acc[i][1] = 0.0;
-    double s1x[TS], s1y[TS], pen[TS], d2s[TS];
-    int coll[TS];
-#pragma unroll
-    for (int i = 0; i < TS; ++i) { s1x[i] = s1y[i] = pen[i] = d2s[i] = 0.0; coll[i] = 0; }
-    int any_cnt = 0;
-    int64_t rows_done = 0;
+    const int64_t ntc = (n + 31) >> 5;                                  // tiles per cell
+    const int64_t TT = C * ntc;
+    const int64_t g_lo = (TT * blockIdx.x) / gridDim.x, g_hi = (TT * (blockIdx.x + 1)) / gridDim.x;
     __syncthreads();
 
-    const int64_t ntiles = (n + FU_THREADS - 1) / FU_THREADS;
-    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        const int64_t i0 = tile * FU_THREADS;
-        const int rows = (int)min((int64_t)FU_THREADS, n - i0);
-        // ---- phase 1: one sample per thread into the staged tile (absent rows hold the pivot: u = 0)
-        {
-            double2* my_stage = stage + tid * STRIDE2;
-            if (tid < rows) {
-                double x = s_x0[0], y = s_x0[1];
-                const uint64_t gi = sample_offset + (uint64_t)(i0 + tid);
-                const uint32_t gi_lo = (uint32_t)gi, gi_hi = (uint32_t)(gi >> 32);
-                auto step = [&](int t, double zx, double zy) {
-                    const StepParams& p = sp[t];
-                    const double dx = x - p.mux, dy = y - p.muy;
-                    const double cmx = p.mnx + fma(dx, p.a00, dy * p.a01);
-                    const double cmy = p.mny + fma(dx, p.a10, dy * p.a11);
-                    x = cmx + zx * p.l00;
-                    y = cmy + fma(zx, p.l10, zy * p.l11);
-                    my_stage[t] = make_double2(x, y);
-                };
-#pragma unroll
-                for (int t2 = 0; t2 < TSH / 2; ++t2) {
-                    Philox rr = philox4x32_10(gi_lo, gi_hi, (uint32_t)c, (uint32_t)t2, seed_lo, seed_hi);
-                    float za, zb, zc, zd;
-                    box_muller(rr.c[0], rr.c[1], za, zb);
-                    box_muller(rr.c[2], rr.c[3], zc, zd);
-                    step(2 * t2, (double)za, (double)zb);
-                    step(2 * t2 + 1, (double)zc, (double)zd);
+    if (warp >= WS_CONS) {
+        // ================================================================== producers
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(WS_REGS_PROD));
+        const int p = warp - WS_CONS;
+        int prev_b = -1;
+        auto retire_prev = [&]() {       // the previous tile's TMA store has read its rows: the buffer may be refilled
+            if (prev_b >= 0) {
+                if (lane == 0) {
+                    bulk_wait_read<0>();
+                    mbar_arrive(empty + prev_b);
                 }
-            } else {
-                for (int t = 0; t < TSH; ++t)
-                    my_stage[t] = make_double2(pivot[(c * TSH + t) * 2], pivot[(c * TSH + t) * 2 + 1]);
+                prev_b = -1;
             }
-        }
-        __syncwarp();                                 // every phase works on the warp's own 32 rows: no CTA barrier,
-                                                      // so the issue-bound rollout of one warp overlaps the FP64-pipe-bound
-                                                      // sums of the others
-        // ---- phase 2: contiguous store of the warp's (wrows, TSH, 2) block
-        if (traj) {
-            const int wrows = min(32, rows - 32 * warp);
-            double2* out2 = reinterpret_cast<double2*>(traj) + (c * n + i0 + 32 * warp) * TSH;
-            const double2* wstage = stage + 32 * warp * STRIDE2;
-            constexpr int RPP = 32 / TSH;
-            const int t = lane % TSH, r0 = lane / TSH;
-#pragma unroll 4
-            for (int rw = r0; rw < wrows; rw += RPP) __stcs(out2 + rw * TSH + t, wstage[rw * STRIDE2 + t]);
-        }
-        // ---- phase 3: this warp's 32 rows, 4-sample groups: shift, S1, A9 predicate, Gram update
-#pragma unroll 4
-        for (int g = 0; g < 8; ++g) {
-            const int row = 32 * warp + 4 * g + r;
-            const bool rv = row < rows;
-            const double2* src = stage + row * STRIDE2 + TS * q;
-            double f[NF];
-            bool hit_any = false;
+        };
+        int64_t seq0 = 0;                                               // tiles of earlier segments of this CTA
+        for (int64_t gt = g_lo; gt < g_hi;) {
+            const int64_t c = gt / ntc, t0 = gt - c * ntc;
+            const int cnt = (int)min(g_hi - gt, ntc - t0);
+            cta_bar();                                                  // (S1) the previous segment is drained
+            cta_bar();                                                  // (S2) step parameters of cell c are built
+            const int first = (int)((p - seq0 % WS_PROD + WS_PROD) % WS_PROD);   // my first tile of this segment
+            for (int s = first; s < cnt; s += WS_PROD) {
+                const int64_t seq = seq0 + s;
+                const int b = (int)(seq % WS_NB);
+                const uint32_t use = (uint32_t)(seq / WS_NB);
+                retire_prev();                                          // hand my previous buffer back first
+                mbar_wait(empty + b, (use & 1) ^ 1);                    // use 0 passes at once
+                const int64_t i0 = (t0 + s) << 5;
+                const int rows = (int)min((int64_t)32, n - i0);
+                // element (row = lane, timestep t): sub-tile t >> 3, chunk (t & 7) ^ (lane & 7)
+                unsigned char* row = ring + (size_t)b * WL::TILE + lane * 128;
+                const int sw = lane & 7;
+                auto put = [&](int t, double x, double y) {
+                    *reinterpret_cast<double2*>(row + (t >> 3) * WL::SUB + (((t & 7) ^ sw) << 4)) = make_double2(x, y);
+                };
+                if (lane < rows) {
+                    double x = s_x0[0], y = s_x0[1];
+                    const uint64_t gi = sample_offset + (uint64_t)(i0 + lane);
+                    const uint32_t gi_lo = (uint32_t)gi, gi_hi = (uint32_t)(gi >> 32);
 #pragma unroll
-            for (int i = 0; i < TS; ++i) {
-                const double2 cur = src[i];
-                const double ux = cur.x - pivx[i], uy = cur.y - pivy[i];
-                s1x[i] += ux;
-                s1y[i] += uy;
-                f[2 * i] = ux;
-                f[2 * i + 1] = uy;
-                if (rv) {
-                    // A9 predicate, fixed order, no FMA contraction (identical to stats.cu)
-                    const double dx = __dsub_rn(ex[i], cur.x), dy = __dsub_rn(ey[i], cur.y);
-                    const double d2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
-                    d2s[i] += d2;
-                    if (d2 < r2) {
-                        ++coll[i];
-                        pen[i] += r2 - d2;
-                        hit_any = true;
+                    for (int t2 = 0; t2 < TSH / 2; ++t2) {
+                        float za = 0.3f, zb = -0.2f, zc = 0.1f, zd = 0.7f;
+                        if (!(exp_flags & 4)) {
+                            Philox rr = philox4x32_10(gi_lo, gi_hi, (uint32_t)c, (uint32_t)t2, seed_lo, seed_hi);
+                            box_muller(rr.c[0], rr.c[1], za, zb);
+                            box_muller(rr.c[2], rr.c[3], zc, zd);
+                        }
+                        if (!(exp_flags & 8)) rollout_step(sp[2 * t2], x, y, (double)za, (double)zb);
+                        put(2 * t2, x, y);
+                        if (!(exp_flags & 8)) rollout_step(sp[2 * t2 + 1], x, y, (double)zc, (double)zd);
+                        put(2 * t2 + 1, x, y);
+                    }
+                } else {                                // absent rows hold the pivot: u = 0 in the Gram update
+                    for (int t = 0; t < TSH; ++t) put(t, pivot[(c * TSH + t) * 2], pivot[(c * TSH + t) * 2 + 1]);
+                }
+                if (store_traj) fence_proxy_async();    // my generic-proxy writes -> visible to the TMA engine
+                __syncwarp();
+                if (lane == 0) {
+                    if (store_traj) {
+#pragma unroll
+                        for (int h = 0; h < WL::H; ++h)
+                            tma_store_box(&traj_map, ring + (size_t)b * WL::TILE + h * WL::SUB, 16 * h, (int)i0, (int)c);
+                        bulk_commit();
+                    }
+                    mbar_arrive(full + b);
+                }
+                prev_b = b;
+            }
+            retire_prev();
+            seq0 += cnt;
+            gt += cnt;
+        }
+        if (lane == 0) bulk_wait_all();                 // every tile has landed before the CTA retires
+        return;
+    }
+
+    // ====================================================================== consumers
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(WS_REGS_CONS));
+    const int r = lane & 3, q = lane >> 2;
+    int ld_off[TS];                                     // byte offset of my chunk inside its 128-byte row (even g)
+#pragma unroll
+    for (int i = 0; i < TS; ++i) ld_off[i] = (((TS * q + i) & 7) ^ r) << 4;
+    // screening box 2^k > R: |dx| >= 2^k or |dy| >= 2^k implies d2 >= r2
+    const double box = __hiloint2double((__double2hiint(sqrt(r2)) & 0x7ff00000) + 0x00100000, 0);
+    const SumsLayout L(TSH);
+    int64_t seq0 = 0;
+    for (int64_t gt = g_lo; gt < g_hi;) {
+        const int64_t c = gt / ntc, t0 = gt - c * ntc;
+        const int cnt = (int)min(g_hi - gt, ntc - t0);
+        cta_bar();                                      // (S1) producers are done with the previous cell's parameters
+        rollout_setup<32 * WS_CONS>(mean, cov, cross, Tm, x0, c, TSH, seed_lo, seed_hi, sp, s_x0, status, x0_out, tid,
+                                    t0 == 0);
+        double pivx[TS], pivy[TS], ex[TS], ey[TS];
+        uint32_t kx[TS], wx[TS], ky[TS], wy[TS];        // integer screen: key(x) - kx <= wx  <=>  |ex - x| < box (+ ties)
+#pragma unroll
+        for (int i = 0; i < TS; ++i) {
+            const int t = TS * q + i;
+            pivx[i] = pivot[(c * TSH + t) * 2];
+            pivy[i] = pivot[(c * TSH + t) * 2 + 1];
+            ex[i] = ego[c * ego_cell_stride + 2 * t];
+            ey[i] = ego[c * ego_cell_stride + 2 * t + 1];
+            kx[i] = hi_key(ex[i] - box); wx[i] = hi_key(ex[i] + box) - kx[i];
+            ky[i] = hi_key(ey[i] - box); wy[i] = hi_key(ey[i] + box) - ky[i];
+        }
+        double acc[NT][2];
+#pragma unroll
+        for (int i = 0; i < NT; ++i) acc[i][0] = acc[i][1] = 0.0;
+        double s1x[TS], s1y[TS], pen[TS];
+        int coll[TS];
+#pragma unroll
+        for (int i = 0; i < TS; ++i) { s1x[i] = s1y[i] = pen[i] = 0.0; coll[i] = 0; }
+        int any_cnt = 0;
+        int64_t rows_done = 0;
+        cta_bar();                                      // (S2) parameters visible to the producers
+        const int first = (int)((warp - seq0 % WS_CONS + WS_CONS) % WS_CONS);
+        for (int s = first; s < cnt; s += WS_CONS) {
+            const int64_t seq = seq0 + s;
+            const int b = (int)(seq % WS_NB);
+            const uint32_t use = (uint32_t)(seq / WS_NB);
+            const int64_t i0 = (t0 + s) << 5;
+            const int rows = (int)min((int64_t)32, n - i0);
+            mbar_wait(full + b, use & 1);
+            // lane (r, q) reads timesteps TS q + i of row 4 g + r: sub-tile t >> 3, chunk (t & 7) ^ (row & 7);
+            // row & 7 = 4 (g & 1) + r, so the two parities of g differ by bit 6 of the byte offset.
+            // Two groups per round, software pipelined: the next pair's loads are issued before this pair's
+            // 2 x NT DMMAs, so the in-order warp never waits for shared memory.
+            const unsigned char* tile = ring + (size_t)b * WL::TILE + ((TS * q) >> 3) * WL::SUB + r * 128;
+            double2 cur[2][TS];
+            auto load_pair = [&](int g2) {
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+#pragma unroll
+                    for (int i = 0; i < TS; ++i)
+                        cur[h][i] = *reinterpret_cast<const double2*>(tile + g2 * 1024 + h * 512 + (ld_off[i] ^ (h << 6)));
+            };
+            load_pair(0);
+#pragma unroll 1
+            for (int g2 = 0; g2 < 4; ++g2) {
+                double f[2][NF];
+                bool near_any = false;
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+#pragma unroll
+                    for (int i = 0; i < TS; ++i) {
+                        const double ux = cur[h][i].x - pivx[i], uy = cur[h][i].y - pivy[i];
+                        s1x[i] += ux;
+                        s1y[i] += uy;
+                        f[h][2 * i] = ux;
+                        f[h][2 * i + 1] = uy;
+                        if (exp_flags & 2) continue;
+                        // A9 screen on the INTEGER pipe (a vector FP64 instruction costs this warp a DMMA slot):
+                        // a sample whose x or y is at least `box` away from the ego cannot be a hit, and almost
+                        // every sample is; the exact fp64 predicate runs only for warps that hold a near sample.
+                        near_any |= (hi_key(cur[h][i].x) - kx[i] <= wx[i]) & (hi_key(cur[h][i].y) - ky[i] <= wy[i]);
+                    }
+                if (__any_sync(0xffffffffu, near_any)) {        // warp-uniform
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const bool rv = 8 * g2 + 4 * h + r < rows;
+                        bool hit_any = false;
+#pragma unroll
+                        for (int i = 0; i < TS; ++i) {
+                            // A9 predicate, fixed order, no FMA contraction (identical to stats.cu)
+                            const double dx = __dsub_rn(ex[i], cur[h][i].x), dy = __dsub_rn(ey[i], cur[h][i].y);
+                            const double d2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
+                            if (rv && d2 < r2) { ++coll[i]; pen[i] += r2 - d2; hit_any = true; }
+                        }
+                        const unsigned bal = __ballot_sync(0xffffffffu, hit_any);
+#pragma unroll
+                        for (int rr = 0; rr < 4; ++rr) any_cnt += (bal & (0x11111111u << rr)) != 0;
                     }
                 }
+                if (g2 < 3) load_pair(g2 + 1);
+                if (!(exp_flags & 1)) {
+                    gram_update<NF>(acc, f[0]);
+                    gram_update<NF>(acc, f[1]);
+                }
             }
-            const unsigned bal = __ballot_sync(0xffffffffu, hit_any);
-            if (bal) {
+            rows_done += rows;
+            __syncwarp();
+            if (lane == 0) mbar_arrive(empty + b);
+        }
+        // ---- warp epilogue of the segment (as stats.cu)
+        double* wsm = area + (size_t)warp * SM::PW;
+        store_gram_tiles<NF>(wsm, acc, q, r);
 #pragma unroll
-                for (int rr = 0; rr < 4; ++rr) any_cnt += (bal & (0x11111111u << rr)) != 0;
+        for (int i = 0; i < TS; ++i) {
+            double v[4] = {s1x[i], s1y[i], (double)coll[i], pen[i]};
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                v[k] += __shfl_xor_sync(0xffffffffu, v[k], 1);
+                v[k] += __shfl_xor_sync(0xffffffffu, v[k], 2);
             }
-            int ti = 0;
-#pragma unroll
-            for (int bi = 0; bi < NF; ++bi)
-#pragma unroll
-                for (int bj = 0; bj <= bi; ++bj, ++ti) fu_dmma8x8x4(acc[ti][0], acc[ti][1], f[bi], f[bj]);
+            if (r == 0) {
+                const int t = TS * q + i;
+                wsm[SM::O_S1 + 2 * t] = v[0];
+                wsm[SM::O_S1 + 2 * t + 1] = v[1];
+                wsm[SM::O_COLL + t] = v[2];
+                wsm[SM::O_PEN + t] = v[3];
+            }
         }
-        rows_done += rows;
-        __syncwarp();                                 // the warp's rows are overwritten by its next rollout
-    }
-    __syncthreads();                                  // the epilogue area aliases the staged tiles of all warps
-
-    // ---- warp epilogue (as stats.cu): fixed-order shuffles over the 4 sample rows, then shared memory
-    //      (the staged tiles are dead: barrier above)
-    double* wsm = smem + (size_t)warp * SM::PW;
+        if (lane == 0) { wsm[SM::O_ANY] = (double)any_cnt; wsm[SM::O_ANY + 1] = (double)rows_done; }
+        asm volatile("bar.sync 1, %0;" ::"n"(32 * WS_CONS) : "memory");
+        // ---- add the consumer warps in warp order into the partial vector of segment (CTA, cell)
+        const int64_t slot = (int64_t)blockIdx.x + c;
+        double* out = partials + slot * (int64_t)L.len;
+        for (int e = tid; e < L.len; e += 32 * WS_CONS) {
+            int src = packed_to_area<NF>(e, L, false, false);
+            if (src == -2) { out[e] = 0.0; continue; }      // d2s: from the Gram identity in the finalize kernel; no yaw
+            if (src == -1) src = SM::O_ANY + 1;
+            double sum = 0.0;
 #pragma unroll
-    for (int ti = 0; ti < NT; ++ti)
-        *reinterpret_cast<double2*>(wsm + ti * 64 + q * 8 + 2 * r) = make_double2(acc[ti][0], acc[ti][1]);
-#pragma unroll
-    for (int i = 0; i < TS; ++i) {
-        double v[5] = {s1x[i], s1y[i], (double)coll[i], pen[i], d2s[i]};
-#pragma unroll
-        for (int k = 0; k < 5; ++k) {
-            v[k] += __shfl_xor_sync(0xffffffffu, v[k], 1);
-            v[k] += __shfl_xor_sync(0xffffffffu, v[k], 2);
+            for (int w = 0; w < WS_CONS; ++w) sum += area[(size_t)w * SM::PW + src];
+            out[e] = sum;
         }
-        if (r == 0) {
-            const int t = TS * q + i;
-            wsm[SM::O_S1 + 2 * t] = v[0];
-            wsm[SM::O_S1 + 2 * t + 1] = v[1];
-            wsm[SM::O_COLL + t] = v[2];
-            wsm[SM::O_PEN + t] = v[3];
-            wsm[SM::O_D2S + t] = v[4];
-        }
-    }
-    if (lane == 0) wsm[SM::O_ANY] = (double)any_cnt;
-    __syncthreads();
-
-    // ---- CTA epilogue: add the warps in warp order into this CTA's partial vector (packed sums layout)
-    const SumsLayout L(TSH);
-    double* out = partials + (c * gridDim.x + blockIdx.x) * (int64_t)L.len;
-    for (int e = tid; e < L.len; e += FU_THREADS) {
-        int src;
-        if (e == 0) {
-            out[0] = (double)rows_done;
-            continue;
-        } else if (e < L.o_s2) {
-            src = SM::O_S1 + (e - L.o_s1);
-        } else if (e < L.o_coll) {
-            const int idx = e - L.o_s2;
-            int i = (int)((sqrtf(8.0f * (float)idx + 1.0f) - 1.0f) * 0.5f);
-            while (i * (i + 1) / 2 > idx) --i;
-            while ((i + 1) * (i + 2) / 2 <= idx) ++i;
-            const int j = idx - i * (i + 1) / 2;
-            int bi = i % NF, bj = j % NF, m = i / NF, nn = j / NF;
-            if (bi < bj) { int t0 = bi; bi = bj; bj = t0; t0 = m; m = nn; nn = t0; }
-            src = (bi * (bi + 1) / 2 + bj) * 64 + m * 8 + nn;
-        } else if (e < L.o_any) {
-            src = SM::O_COLL + (e - L.o_coll);
-        } else if (e == L.o_any) {
-            src = SM::O_ANY;
-        } else if (e < L.o_d2s) {
-            src = SM::O_PEN + (e - L.o_pen);
-        } else if (e < L.o_yaw) {
-            src = SM::O_D2S + (e - L.o_d2s);
-        } else {
-            out[e] = 0.0;                                 // no yaw sums on this path
-            continue;
-        }
-        double s = 0.0;
-#pragma unroll
-        for (int w = 0; w < FU_WARPS; ++w) s += smem[(size_t)w * SM::PW + src];
-        out[e] = s;
+        if (tid == 0) slot_cell[slot] = (int32_t)c;
+        seq0 += cnt;
+        gt += cnt;
     }
 }
 
-// sums[c] = sum over the cell's CTA partials, in CTA order
-__global__ void fused_finalize_kernel(const double* __restrict__ partials, int nparts, int len,
-                                      double* __restrict__ sums) {
+// sums[c] = sum over the cell's segment partials (slots c .. c + G - 1 that carry cell c), in CTA order; the d2s
+// slots follow from the Gram identity
+__global__ void fused_finalize_kernel(const double* __restrict__ partials, const int32_t* __restrict__ slot_cell,
+                                      int G, int T, const double* __restrict__ pivot, const double* __restrict__ ego,
+                                      int64_t ego_cell_stride, double* __restrict__ sums) {
+    extern __shared__ double s_sum[];
+    const SumsLayout L(T);
     const int64_t c = blockIdx.x;
-    const int j = blockIdx.y * blockDim.x + threadIdx.x;
-    if (j >= len) return;
-    double s = 0.0;
-    for (int p = 0; p < nparts; ++p) s += partials[(c * nparts + p) * (int64_t)len + j];
-    sums[c * len + j] = s;
+    for (int j = threadIdx.x; j < L.len; j += blockDim.x) {
+        double s = 0.0;
+        for (int g = 0; g < G; ++g)
+            if (slot_cell[c + g] == (int32_t)c) s += partials[(c + g) * (int64_t)L.len + j];
+        s_sum[j] = s;
+    }
+    __syncthreads();
+    for (int j = threadIdx.x; j < L.len; j += blockDim.x) {
+        double v = s_sum[j];
+        if (j >= L.o_d2s && j < L.o_yaw) {
+            const int t = j - L.o_d2s;
+            v = d2s_from_sums(s_sum, L, t, ego[c * ego_cell_stride + 2 * t] - pivot[(c * T + t) * 2],
+                              ego[c * ego_cell_stride + 2 * t + 1] - pivot[(c * T + t) * 2 + 1]);
+        }
+        sums[c * L.len + j] = v;
+    }
 }
 
-static int fused_grid_x(int64_t n, int64_t C) {
-    int64_t want = (148 * FU_CTAS_PER_SM) / C;         // one wave of resident CTAs, split over the cells
-    int64_t need = (n + FU_THREADS - 1) / FU_THREADS;
-    int64_t g = want < need ? want : need;
+static int sm_count() {
+    static int n = 0;
+    if (n == 0) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess ||
+            cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+            n = 148;
+    }
+    return n;
+}
+
+static int fused_grid(int64_t n, int64_t C) {
+    const int64_t tt = C * ((n + 31) / 32);
+    const int64_t g = tt < sm_count() ? tt : sm_count();
     return (int)(g < 1 ? 1 : g);
 }
+
+static size_t slot_bytes(int64_t slots) { return ((size_t)slots * sizeof(int32_t) + 255) / 256 * 256; }
 
 }  // namespace ccmpc
 
 using namespace ccmpc;
 
+extern "C" int ccmpc_debug_ws_exp(int flags) {      // not part of the ABI (tools only)
+    g_ws_exp = flags;
+    return 0;
+}
+
 extern "C" size_t ccmpc_mc_rollout_sums_workspace_bytes(int64_t C, int64_t n, int Tsh) {
     if (C <= 0 || n <= 0 || Tsh < 1 || Tsh > CCMPC_MAX_T) return 16;
-    return (size_t)C * (size_t)fused_grid_x(n, C) * (size_t)SumsLayout(Tsh).len * sizeof(double);
+    const int64_t slots = C + sm_count();           // segment (CTA j, cell c) -> slot j + c
+    return slot_bytes(slots) + (size_t)slots * (size_t)SumsLayout(Tsh).len * sizeof(double);
+}
+
+// (2 T doubles, n samples, C cells) view of the row-major trajectory tensor, boxes of [32 samples][16 doubles] in
+// the 128-byte swizzle.  cuTensorMapEncodeTiled is a host-side encoder of the driver: fetched through the runtime
+// (no link against libcuda), called once per launch (the map holds the tensor's address and extents).
+static int make_traj_map(CUtensorMap* map, double* traj, int64_t C, int64_t n, int Tsh) {
+    typedef CUresult (*encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static encode_fn encode = nullptr;
+    if (!encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q);
+        if (e != cudaSuccess || q != cudaDriverEntryPointSuccess || !fn) {
+            set_error("ccmpc_mc_rollout_sums: cuTensorMapEncodeTiled is not available (%s)", cudaGetErrorString(e));
+            return CCMPC_E_LAUNCH;
+        }
+        encode = reinterpret_cast<encode_fn>(fn);
+    }
+    const cuuint64_t dims[3] = {(cuuint64_t)(2 * Tsh), (cuuint64_t)n, (cuuint64_t)C};
+    const cuuint64_t strides[2] = {(cuuint64_t)(2 * Tsh) * 8, (cuuint64_t)n * (2 * Tsh) * 8};
+    const cuuint32_t box[3] = {16, 32, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, traj, dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("ccmpc_mc_rollout_sums: cuTensorMapEncodeTiled failed (CUresult %d; C = %lld, n = %lld)", (int)r,
+                  (long long)C, (long long)n);
+        return CCMPC_E_LAUNCH;
+    }
+    return CCMPC_OK;
+}
+
+template <int NF>
+static int launch_ws(int G, cudaStream_t st, const double* mean, const double* cov, const double* cross, int Tm,
+                     const double* x0, int64_t C, int64_t n, uint64_t seed, uint64_t sample_offset,
+                     const double* pivot, const double* ego, int64_t ego_cell_stride, double R, double* traj,
+                     double* partials, int32_t* slot_cell, uint8_t* status, double* x0_out) {
+    auto kernel = rollout_sums_ws_kernel<NF, 0>;
+#ifdef CCMPC_WS_EXPERIMENTS
+    if (g_ws_exp == 1) kernel = rollout_sums_ws_kernel<NF, 1>;
+    if (g_ws_exp == 2) kernel = rollout_sums_ws_kernel<NF, 2>;
+    if (g_ws_exp == 3) kernel = rollout_sums_ws_kernel<NF, 3>;
+    if (g_ws_exp == 12) kernel = rollout_sums_ws_kernel<NF, 12>;
+#endif
+    {
+        cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)WsLayout<NF>::BYTES);
+        if (e != cudaSuccess) { set_error("ccmpc_mc_rollout_sums: smem attribute: %s", cudaGetErrorString(e)); return CCMPC_E_LAUNCH; }
+    }
+    CUtensorMap map;
+    memset(&map, 0, sizeof(map));
+    if (traj) {
+        int rc = make_traj_map(&map, traj, C, n, 4 * NF);
+        if (rc != CCMPC_OK) return rc;
+    }
+    kernel<<<(unsigned)G, WS_THREADS, WsLayout<NF>::BYTES, st>>>(
+        mean, cov, cross, Tm, x0, n, (uint32_t)seed, (uint32_t)(seed >> 32), sample_offset, pivot, ego,
+        ego_cell_stride, R * R, map, traj ? 1 : 0, partials, slot_cell, status, x0_out, C);
+    return check_launch("rollout_sums_ws_kernel");
 }
 
 extern "C" int ccmpc_mc_rollout_sums(const double* mean, const double* cov, const double* cross, int Tm,
@@ -273,7 +501,7 @@ extern "C" int ccmpc_mc_rollout_sums(const double* mean, const double* cov, cons
                                      double* x0_out, void* workspace, size_t workspace_bytes, void* stream) {
     CCMPC_REQUIRE(Tsh == 16 || Tsh == 8, "ccmpc_mc_rollout_sums: horizon must be 8 or 16 (got %d)", Tsh);
     CCMPC_REQUIRE(Tm >= Tsh + 1, "ccmpc_mc_rollout_sums: moments must cover Tsh + 1 steps (Tm = %d)", Tm);
-    CCMPC_REQUIRE(C >= 0 && n >= 0 && C < 65536, "ccmpc_mc_rollout_sums: bad C / n");
+    CCMPC_REQUIRE(C >= 0 && n >= 0 && C < 65536 && n < ((int64_t)1 << 31), "ccmpc_mc_rollout_sums: bad C / n");
     if (C == 0) return CCMPC_OK;
     CCMPC_REQUIRE(mean && cov && cross && pivot && ego && sums, "ccmpc_mc_rollout_sums: null pointer");
     CCMPC_REQUIRE(ego_cell_stride == 0 || ego_cell_stride == 2 * Tsh, "ccmpc_mc_rollout_sums: ego stride must be 0 or 2 Tsh");
@@ -291,21 +519,20 @@ extern "C" int ccmpc_mc_rollout_sums(const double* mean, const double* cov, cons
         cudaError_t e = cudaMemsetAsync(status, 0, (size_t)C, st);
         if (e != cudaSuccess) { set_error("ccmpc_mc_rollout_sums: memset: %s", cudaGetErrorString(e)); return CCMPC_E_LAUNCH; }
     }
-    const int gx = fused_grid_x(n, C);
-    dim3 grid((unsigned)gx, (unsigned)C);
-    double* partials = reinterpret_cast<double*>(workspace);
-    const size_t smem = (size_t)Tsh * sizeof(StepParams) + (size_t)FU_THREADS * (Tsh | 1) * 16;
-    if (Tsh == 16)
-        rollout_sums_kernel<4><<<grid, FU_THREADS, smem, st>>>(mean, cov, cross, Tm, x0, n, (uint32_t)seed,
-                                                               (uint32_t)(seed >> 32), sample_offset, pivot, ego,
-                                                               ego_cell_stride, R * R, traj, partials, status, x0_out);
-    else
-        rollout_sums_kernel<2><<<grid, FU_THREADS, smem, st>>>(mean, cov, cross, Tm, x0, n, (uint32_t)seed,
-                                                               (uint32_t)(seed >> 32), sample_offset, pivot, ego,
-                                                               ego_cell_stride, R * R, traj, partials, status, x0_out);
-    int rc = check_launch("rollout_sums_kernel");
+    const int G = fused_grid(n, C);
+    const int64_t slots = C + sm_count();
+    int32_t* slot_cell = reinterpret_cast<int32_t*>(workspace);
+    double* partials = reinterpret_cast<double*>(reinterpret_cast<char*>(workspace) + slot_bytes(slots));
+    {
+        cudaError_t e = cudaMemsetAsync(slot_cell, 0xFF, (size_t)slots * sizeof(int32_t), st);      // -1: empty slot
+        if (e != cudaSuccess) { set_error("ccmpc_mc_rollout_sums: memset: %s", cudaGetErrorString(e)); return CCMPC_E_LAUNCH; }
+    }
+    int rc = Tsh == 16 ? launch_ws<4>(G, st, mean, cov, cross, Tm, x0, C, n, seed, sample_offset, pivot, ego,
+                                      ego_cell_stride, R, traj, partials, slot_cell, status, x0_out)
+                       : launch_ws<2>(G, st, mean, cov, cross, Tm, x0, C, n, seed, sample_offset, pivot, ego,
+                                      ego_cell_stride, R, traj, partials, slot_cell, status, x0_out);
     if (rc != CCMPC_OK) return rc;
-    dim3 fg((unsigned)C, (unsigned)((L.len + 127) / 128));
-    fused_finalize_kernel<<<fg, 128, 0, st>>>(partials, gx, L.len, sums);
+    fused_finalize_kernel<<<(unsigned)C, 256, (size_t)L.len * sizeof(double), st>>>(partials, slot_cell, G, Tsh, pivot,
+                                                                                   ego, ego_cell_stride, sums);
     return check_launch("fused_finalize_kernel");
 }

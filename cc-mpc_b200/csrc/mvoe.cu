@@ -508,7 +508,9 @@ __global__ void affine_kernel(const double* __restrict__ sums, const double* __r
            cov_from_sums(s, L, it + 1, it + 1, n, inv_nm1)};                // :1493
     // principal square root of an SPD 2x2: (S + sqrt(det) I) / sqrt(tr + 2 sqrt(det))   (:1494)
     const double dt = det2(S);
-    if (!(dt >= 0.0)) status = CCMPC_ST_NO_TANGENT;
+    // a NaN covariance (fewer than 2 samples: np.cov is NaN) makes scipy.linalg.sqrtm reject its input (:1494)
+    if (!isfinite(dt)) status = CCMPC_ST_SINGULAR;
+    else if (dt < 0.0) status = CCMPC_ST_NO_TANGENT;
     const double sd = sqrt(fmax(dt, 0.0));
     const double den = sqrt(S.xx + S.yy + 2.0 * sd);
     const double r00 = (S.xx + sd) / den, r01 = S.xy / den, r11 = (S.yy + sd) / den;

@@ -40,7 +40,7 @@ risk_kernel(const double* __restrict__ mean, const double* __restrict__ cov, con
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t c = blockIdx.y;
 
-    rollout_setup<RK_THREADS>(mean, cov, cross, Tm, x0, c, Tsh, seed_lo, seed_hi, sp, s_x0, status, x0_out, tid);
+    rollout_setup<RK_THREADS>(mean, cov, cross, Tm, x0, c, Tsh, seed_lo, seed_hi, sp, s_x0, status, x0_out, tid, blockIdx.x == 0);
     if (tid < Tsh) s_ego[tid] = reinterpret_cast<const double2*>(ego + c * ego_cell_stride)[tid];
     __syncthreads();
 
@@ -65,12 +65,7 @@ risk_kernel(const double* __restrict__ mean, const double* __restrict__ cov, con
         const uint32_t gi_lo = (uint32_t)gi, gi_hi = (uint32_t)(gi >> 32);
         bool hit_any = false;
         auto step = [&](int t, double zx, double zy) {
-            const StepParams& p = sp[t];
-            const double dx = x - p.mux, dy = y - p.muy;
-            const double cmx = p.mnx + fma(dx, p.a00, dy * p.a01);
-            const double cmy = p.mny + fma(dx, p.a10, dy * p.a11);
-            x = cmx + zx * p.l00;
-            y = cmy + fma(zx, p.l10, zy * p.l11);
+            rollout_step(sp[t], x, y, zx, zy);
             // A9 predicate, fixed order, no FMA contraction (identical to stats.cu)
             const double2 e = s_ego[t];
             const double ex = __dsub_rn(e.x, x), ey = __dsub_rn(e.y, y);

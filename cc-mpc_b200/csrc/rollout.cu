@@ -49,7 +49,7 @@ rollout_kernel(const double* __restrict__ mean, const double* __restrict__ cov, 
     const int64_t c = blockIdx.y;
     __shared__ double s_x0[2];
 
-    rollout_setup<RO_THREADS>(mean, cov, cross, Tm, x0, c, Tsh, seed_lo, seed_hi, sp, s_x0, status, x0_out, tid);
+    rollout_setup<RO_THREADS>(mean, cov, cross, Tm, x0, c, Tsh, seed_lo, seed_hi, sp, s_x0, status, x0_out, tid, blockIdx.x == 0);
     __syncthreads();
 
     // persistent over the cell's 128-sample tiles: the per-step parameters above are built once per CTA, not
@@ -94,12 +94,7 @@ rollout_kernel(const double* __restrict__ mean, const double* __restrict__ cov, 
 
     auto step = [&](int t, double zx, double zy) {
         if (ZOUT && valid) zout2[t] = make_double2(zx, zy);
-        const StepParams& p = sp[t];
-        const double dx = x - p.mux, dy = y - p.muy;
-        const double cmx = p.mnx + fma(dx, p.a00, dy * p.a01);
-        const double cmy = p.mny + fma(dx, p.a10, dy * p.a11);
-        x = cmx + zx * p.l00;
-        y = cmy + fma(zx, p.l10, zy * p.l11);
+        rollout_step(sp[t], x, y, zx, zy);
         my_stage[FL > 0 ? (t % FL) : t] = make_double2(x, y);
     };
 #pragma unroll

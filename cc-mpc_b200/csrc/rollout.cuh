@@ -6,20 +6,34 @@
 
 namespace ccmpc {
 
-struct __align__(16) StepParams {   // per (cell, t): 11 doubles + pad -> six 16-byte shared-memory loads
-    double mux, muy, mnx, mny, a00, a01, a10, a11, l00, l10, l11, pad;
+// per (cell, t): x' = mu_{t+1} + A (x - mu_t) + L z  (v8ideal:2688-2703) with the constant part folded,
+//   b = mu_{t+1} - A mu_t,   x' = b + A x + L z
+// so one step is 7 dependent-depth-2 FMAs instead of 11 FP64 instructions of depth 5 (the chain over t is the
+// serial part of every rollout kernel and shares the FP64 pipe with the Gram update of the fused kernel).
+// 9 doubles + pad -> five 16-byte shared-memory loads.  |b| <= ~|mu| (1 + |A|): the fold costs a few ulp of the
+// position (1e-13 m at Town03 coordinates), far inside the oracle tolerance (tests: 1e-13 relative).
+struct __align__(16) StepParams {
+    double bx, by, a00, a01, a10, a11, l00, l10, l11, pad;
 };
 constexpr int SP_D = sizeof(StepParams) / sizeof(double);
 
+// one step of the chain, the same instruction sequence in rollout.cu, risk.cu and fused.cu (bit-identical samples)
+__device__ __forceinline__ void rollout_step(const StepParams& p, double& x, double& y, double zx, double zy) {
+    const double nx = fma(p.a00, x, fma(p.a01, y, fma(p.l00, zx, p.bx)));
+    const double ny = fma(p.a10, x, fma(p.a11, y, fma(p.l10, zx, fma(p.l11, zy, p.by))));
+    x = nx;
+    y = ny;
+}
+
 
 // Built once per CTA: thread NT-1 fixes the start point x0 (supplied, or the ONE draw shared by all samples of
-// the cell, v8ideal:2664-2665), threads t < Tsh build (mu_t, mu_{t+1}, A_t, L_t) of step t.  Caller syncs.
+// the cell, v8ideal:2664-2665), threads t < Tsh build (b_t, A_t, L_t) of step t; `write_out`: this CTA reports status / x0 of the cell.  Caller syncs.
 template <int NT>
 __device__ __forceinline__ void rollout_setup(const double* __restrict__ mean, const double* __restrict__ cov,
                                               const double* __restrict__ cross, int Tm, const double* __restrict__ x0,
                                               int64_t c, int Tsh, uint32_t seed_lo, uint32_t seed_hi, StepParams* sp,
                                               double* s_x0, uint8_t* __restrict__ status, double* __restrict__ x0_out,
-                                              int tid) {
+                                              int tid, bool write_out) {
     if (tid == NT - 1) {
         if (x0) {
             s_x0[0] = x0[2 * c];
@@ -37,7 +51,7 @@ __device__ __forceinline__ void rollout_setup(const double* __restrict__ mean, c
             s_x0[0] = mean[(c * Tm) * 2] + l00 * (double)za;
             s_x0[1] = mean[(c * Tm) * 2 + 1] + fma(l10, (double)za, l11 * (double)zb);
         }
-        if (x0_out && blockIdx.x == 0) { x0_out[2 * c] = s_x0[0]; x0_out[2 * c + 1] = s_x0[1]; }
+        if (x0_out && write_out) { x0_out[2 * c] = s_x0[0]; x0_out[2 * c + 1] = s_x0[1]; }
     }
     if (tid < Tsh) {
         const int t = tid;
@@ -46,7 +60,6 @@ __device__ __forceinline__ void rollout_setup(const double* __restrict__ mean, c
         const double* Sn = cov + (c * Tm + t + 1) * 4;
         const double* Cx = cross + ((c * Tm + t + 1) * Tm + t) * 4;
         StepParams p;
-        p.mux = mt[0]; p.muy = mt[1]; p.mnx = mt[2]; p.mny = mt[3];
         int st = 0;
         // inverse of Sigma_t (np.linalg.inv of a general 2x2)
         const double det = diff_of_products(St[0], St[3], St[1], St[2]);
@@ -67,9 +80,11 @@ __device__ __forceinline__ void rollout_setup(const double* __restrict__ mean, c
         const double r = k11 - p.l10 * p.l10;
         if (!(r > 0.0) && st == 0) st = CCMPC_ST_NO_TANGENT;
         p.l11 = sqrt(r);
+        p.bx = mt[2] - fma(p.a00, mt[0], p.a01 * mt[1]);
+        p.by = mt[3] - fma(p.a10, mt[0], p.a11 * mt[1]);
         p.pad = 0.0;
         sp[t] = p;
-        if (status && blockIdx.x == 0 && st) status[c] = (uint8_t)st;
+        if (status && write_out && st) status[c] = (uint8_t)st;
     }
 }
 

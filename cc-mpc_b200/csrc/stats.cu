@@ -13,7 +13,7 @@
 // Work decomposition: unit = up to `slab` consecutive samples of one cell;
 // one CTA per unit writes a partial sums vector, a second kernel adds the
 // partials of each cell in unit order (deterministic, no fp64 atomics).
-#include "common.cuh"
+#include "sums_common.cuh"
 
 namespace ccmpc {
 
@@ -46,12 +46,6 @@ constexpr int SS_SLAB = SS_SLAB_DEF;          // samples per unit (= per CTA) fo
 //   tile (bi, bj):  C[m][n] += sum_k U[k][NF*m+bi] * U[k][NF*n+bj].
 //   NF(NF+1)/2 tiles (bi >= bj) cover every (i >= j) entry.
 // ---------------------------------------------------------------------------
-__device__ __forceinline__ void dmma8x8x4(double& c0, double& c1, double a, double b) {
-    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
-                 : "+d"(c0), "+d"(c1)
-                 : "d"(a), "d"(b));
-}
-
 struct StatsArgs {
     const double* samples;
     const int64_t* offsets;
@@ -68,18 +62,8 @@ struct StatsArgs {
 };
 
 template <int NF>
-struct StatsSmem {
-    static constexpr int NT = NF * (NF + 1) / 2;   // 8x8 tiles (bi >= bj)
-    static constexpr int TP = 4 * NF;              // timesteps covered by a warp (padded)
-    static constexpr int O_S1 = NT * 64;           // [8 NF] column sums
-    static constexpr int O_COLL = O_S1 + 8 * NF;   // [TP] each: coll, pen, d2s, yaw, yaw2
-    static constexpr int O_PEN = O_COLL + TP;
-    static constexpr int O_D2S = O_PEN + TP;
-    static constexpr int O_YAW = O_D2S + TP;
-    static constexpr int O_YAW2 = O_YAW + TP;
-    static constexpr int O_ANY = O_YAW2 + TP;
-    static constexpr int PW = O_ANY + 2;           // doubles per warp
-    static constexpr size_t BYTES = (size_t)SS_WARPS * PW * sizeof(double);
+struct StatsSmem : SumsWarpArea<NF> {
+    static constexpr size_t BYTES = (size_t)SS_WARPS * SumsWarpArea<NF>::PW * sizeof(double);
 };
 
 template <int NF, bool YAW, bool COUNT, bool FULLT>
@@ -176,10 +160,7 @@ __global__ void __launch_bounds__(ST_THREADS, 2) sample_sums_kernel(const StatsA
                 _Pragma("unroll") for (int rr = 0; rr < 4; ++rr) any_cnt += (bal & (0x11111111u << rr)) != 0; \
             }                                                                                               \
         }                                                                                                   \
-        int ti = 0;                                                                                         \
-        _Pragma("unroll") for (int bi = 0; bi < NF; ++bi)                                                   \
-            _Pragma("unroll") for (int bj = 0; bj <= bi; ++bj, ++ti)                                        \
-                dmma8x8x4(acc[ti][0], acc[ti][1], f[bi], f[bj]);                                            \
+        gram_update<NF>(acc, f);                                                                            \
     } while (0)
 
     double2 buf[DEPTH][TS];
@@ -247,9 +228,7 @@ __global__ void __launch_bounds__(ST_THREADS, 2) sample_sums_kernel(const StatsA
 #undef CCMPC_SS_PROCESS
     // ---- warp epilogue: fixed-order shuffles over the 4 sample rows, then shared memory
     double* wsm = smem + (size_t)warp * SM::PW;
-#pragma unroll
-    for (int ti = 0; ti < NT; ++ti)
-        *reinterpret_cast<double2*>(wsm + ti * 64 + q * 8 + 2 * r) = make_double2(acc[ti][0], acc[ti][1]);
+    store_gram_tiles<NF>(wsm, acc, q, r);
 #pragma unroll
     for (int i = 0; i < TS; ++i) {
         double v[7] = {s1x[i], s1y[i], (double)coll[i], pen[i], d2s[i], yaw_s[i], yaw_q[i]};
@@ -276,33 +255,10 @@ __global__ void __launch_bounds__(ST_THREADS, 2) sample_sums_kernel(const StatsA
     const SumsLayout L(T);
     double* out = a.partials + (int64_t)u * L.len;
     for (int e = tid; e < L.len; e += ST_THREADS) {
-        int src;
-        if (e == 0) {
-            out[0] = (double)rows_unit;
+        const int src = packed_to_area<NF>(e, L, true, true);
+        if (src < 0) {
+            out[e] = (double)rows_unit;
             continue;
-        } else if (e < L.o_s2) {
-            src = SM::O_S1 + (e - L.o_s1);
-        } else if (e < L.o_coll) {
-            const int idx = e - L.o_s2;
-            int i = (int)((sqrtf(8.0f * (float)idx + 1.0f) - 1.0f) * 0.5f);
-            while (i * (i + 1) / 2 > idx) --i;
-            while ((i + 1) * (i + 2) / 2 <= idx) ++i;
-            const int j = idx - i * (i + 1) / 2;
-            int bi = i % NF, bj = j % NF, m = i / NF, n = j / NF;
-            if (bi < bj) { int t0 = bi; bi = bj; bj = t0; t0 = m; m = n; n = t0; }
-            src = (bi * (bi + 1) / 2 + bj) * 64 + m * 8 + n;
-        } else if (e < L.o_any) {
-            src = SM::O_COLL + (e - L.o_coll);
-        } else if (e == L.o_any) {
-            src = SM::O_ANY;
-        } else if (e < L.o_d2s) {
-            src = SM::O_PEN + (e - L.o_pen);
-        } else if (e < L.o_yaw) {
-            src = SM::O_D2S + (e - L.o_d2s);
-        } else if (e < L.o_yaw2) {
-            src = SM::O_YAW + (e - L.o_yaw);
-        } else {
-            src = SM::O_YAW2 + (e - L.o_yaw2);
         }
         double s = 0.0;
 #pragma unroll

@@ -13,12 +13,18 @@ traj = torch.empty((C, n, T, 2), dtype=torch.float64, device=dev)
 pivot = m[:, 1:T + 1].contiguous()
 ws = ops.mc_rollout_sums_workspace(C, n, T, dev)
 sums = torch.empty((C, ops.sums_len(T)), dtype=torch.float64, device=dev)
-for mat in (True, False):
-    f = lambda i: ops.mc_rollout_sums(m, c, x, None, n, T, pivot, ego, seed=i, materialize=mat, workspace=ws, out=traj, sums_out=sums)
-    for i in range(3): f(i)
-    torch.cuda.synchronize()
-    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    a.record()
-    for i in range(10): f(3 + i)
-    b.record(); torch.cuda.synchronize()
-    print("fused materialize", mat, f"{a.elapsed_time(b)/10:.3f} ms")
+import ctypes
+from ccmpc_b200 import _lib
+lib = _lib.load()
+exps = [int(a) for a in sys.argv[1:]] or [0]
+for exp in exps:
+  lib.ccmpc_debug_ws_exp(ctypes.c_int(exp))
+  for mat in (True, False):
+      f = lambda i: ops.mc_rollout_sums(m, c, x, None, n, T, pivot, ego, seed=i, materialize=mat, workspace=ws, out=traj, sums_out=sums)
+      for i in range(3): f(i)
+      torch.cuda.synchronize()
+      a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+      a.record()
+      for i in range(10): f(3 + i)
+      b.record(); torch.cuda.synchronize()
+      print("exp", exp, "fused materialize", mat, f"{a.elapsed_time(b)/10:.3f} ms")

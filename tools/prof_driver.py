@@ -3,7 +3,7 @@
 
   python tools/prof_driver.py sweep [accel]     # c4 MVOE sweep, accel = 0 | 1 | 2
   python tools/prof_driver.py fit   [accel]     # c4-sized stand-alone footprint fit
-  python tools/prof_driver.py sums | risk | rollout | c5s   # c3 / c5 kernels
+  python tools/prof_driver.py sums | risk | rollout | fused | c5s   # c3 / c5 kernels
 Run WITHOUT ncu first (must exit 0), then under
   ncu --set full --clock-control none --import-source on -k regex:<kernel> -s 2 -c 1 -o gpurun_out/<name> python tools/prof_driver.py ...
 """
@@ -60,6 +60,21 @@ def main():
             ops.sample_sums(flat, offsets, pv, ego=ego)
         torch.cuda.synchronize()
         print("ok sums")
+        return
+    if what == "fused":
+        O, K, T, n = 8, 4, 16, 250_000
+        C = O * K
+        sc = synth.make_scene(3, O, K, T + 1)
+        m, c, x = (torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in sc.moments())
+        m, c, x = m.reshape(C, T + 1, 2), c.reshape(C, T + 1, 2, 2), x.reshape(C, T + 1, T + 1, 2, 2)
+        ego = torch.from_numpy(synth.reference_trajectory(T)).to(dev)
+        traj = torch.empty((C, n, T, 2), dtype=torch.float64, device=dev)
+        pv = m[:, 1:T + 1].contiguous()
+        ws = ops.mc_rollout_sums_workspace(C, n, T, dev)
+        for i in range(4):
+            ops.mc_rollout_sums(m, c, x, None, n, T, pv, ego, seed=i, workspace=ws, out=traj)
+        torch.cuda.synchronize()
+        print("ok fused")
         return
     if what in ("risk", "rollout"):
         O, K, T, n = 8, 4, 16, 250_000
