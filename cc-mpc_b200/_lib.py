@@ -66,7 +66,8 @@ _lib = None
 
 
 def library_path() -> str:
-    return _build.LIB
+    # CCMPC_LIB: an alternative build of the SAME sources (tools/: compile-time experiment variants)
+    return os.environ.get("CCMPC_LIB") or _build.LIB
 
 
 def load(build_if_missing: bool = True):
@@ -79,7 +80,7 @@ def load(build_if_missing: bool = True):
         if not build_if_missing:
             raise CcmpcError(f"{path} not found (run `python -m ccmpc_b200._build`); there is no fallback path")
         _build.build_library()
-    elif _build.is_stale():
+    elif path == _build.LIB and _build.is_stale():
         # a .so older than csrc/ or include/ccmpc.h would be called with the NEW argument lists below:
         # rebuild when a compiler is here, refuse otherwise (no silent ABI mismatch)
         if _build.find_nvcc() is None:

@@ -49,15 +49,18 @@
 
 namespace ccmpc {
 
-constexpr int WS_CONS = 4;                            // consumer warps: one warpgroup, one warp per sub-partition
+#ifndef WS_CONS_DEF
+#define WS_CONS_DEF 4
+#endif
+constexpr int WS_CONS = WS_CONS_DEF;                  // consumer warps (whole warpgroups: 1 or 2 per sub-partition)
 #ifndef WS_PROD_DEF
 #define WS_PROD_DEF 20
 #endif
 constexpr int WS_PROD = WS_PROD_DEF;                  // producer warps (whole warpgroups)
 constexpr int WS_THREADS = 32 * (WS_CONS + WS_PROD);
-constexpr int WS_NB = 24;                             // tile buffers in the ring
-// launch allocation 80 registers x 768 threads; 128 x 128 + 640 x 64 fits it
-constexpr int WS_REGS_CONS = 128, WS_REGS_PROD = 64;
+constexpr int WS_NB = WS_PROD > 20 ? 26 : 24;         // tile buffers in the ring
+// launch allocation 80 registers x 768 threads; 128 x 112 + 640 x 72 fits it
+constexpr int WS_REGS_CONS = 112, WS_REGS_PROD = (WS_CONS == 4 && WS_PROD <= 20) ? 72 : 64;
 static_assert(WS_PROD % 4 == 0, "setmaxnreg works on whole warpgroups");
 
 // ---- mbarrier / bulk-copy PTX ----------------------------------------------------------------------------
@@ -111,11 +114,18 @@ struct WsLayout {                                     // dynamic shared memory o
     static constexpr size_t SUB = 32 * 128;           // [32 rows][8 double2], 128-byte swizzle
     static constexpr size_t TILE = H * SUB;
     static constexpr size_t O_RING = 0;               // 1024-byte aligned: the swizzle pattern is address based
-    static constexpr size_t O_AREA = O_RING + WS_NB * TILE;                     // consumer epilogue areas
+    // consumer epilogue areas: NOT aliased onto the ring - a consumed tile may still be read by its TMA store
+    static constexpr size_t O_AREA = O_RING + WS_NB * TILE;
     static constexpr size_t O_SP = O_AREA + (size_t)WS_CONS * SumsWarpArea<NF>::PW * 8;   // StepParams[TSH]
     static constexpr size_t O_BAR = O_SP + (size_t)TSH * sizeof(StepParams);   // full[NB], empty[NB]
     static constexpr size_t O_X0 = O_BAR + 2 * WS_NB * 8;
-    static constexpr size_t BYTES = O_X0 + 16;
+    static constexpr size_t O_PIV = O_X0 + 16;                                  // double2 pivot[TSH]
+    static constexpr size_t O_EGO = O_PIV + (size_t)TSH * 16;                   // double2 ego[TSH]
+    static constexpr size_t O_SCR = O_EGO + (size_t)TSH * 16;                   // uint4 screen[TSH]: kx, wx, ky, wy
+    static constexpr size_t O_PCNT = O_SCR + (size_t)TSH * 16;                  // producer counts [WS_PROD][PC_LEN]
+    static constexpr int PC_LEN = 2 * TSH + 2;                                  // coll[T], pen[T], any, pad
+    static constexpr size_t BYTES = O_PCNT + (size_t)WS_PROD * PC_LEN * 8;
+    static_assert(BYTES <= 227 * 1024, "shared memory of one CTA");
 };
 
 // grid G (<= number of SMs): CTA j handles global tiles [j TT / G, (j + 1) TT / G), TT = C ceil(n / 32).
@@ -140,6 +150,10 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
     uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + WL::O_BAR);
     uint64_t* empty = full + WS_NB;
     double* s_x0 = reinterpret_cast<double*>(smem_raw + WL::O_X0);
+    double2* s_piv = reinterpret_cast<double2*>(smem_raw + WL::O_PIV);
+    double2* s_ego = reinterpret_cast<double2*>(smem_raw + WL::O_EGO);
+    uint4* s_scr = reinterpret_cast<uint4*>(smem_raw + WL::O_SCR);
+    double* s_pcnt = reinterpret_cast<double*>(smem_raw + WL::O_PCNT);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
     if (tid == 0) {
@@ -155,6 +169,7 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
         // ================================================================== producers
         asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(WS_REGS_PROD));
         const int p = warp - WS_CONS;
+        const int sw = lane & 7;
         int prev_b = -1;
         auto retire_prev = [&]() {       // the previous tile's TMA store has read its rows: the buffer may be refilled
             if (prev_b >= 0) {
@@ -170,7 +185,10 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
             const int64_t c = gt / ntc, t0 = gt - c * ntc;
             const int cnt = (int)min(g_hi - gt, ntc - t0);
             cta_bar();                                                  // (S1) the previous segment is drained
-            cta_bar();                                                  // (S2) step parameters of cell c are built
+            cta_bar();                                                  // (S2) parameters of cell c are built
+            // A9 counts of this warp in this segment: lane t owns timestep t (lanes >= T idle)
+            int coll_mine = 0, any_cnt = 0;
+            double pen_mine = 0.0;
             const int first = (int)((p - seq0 % WS_PROD + WS_PROD) % WS_PROD);   // my first tile of this segment
             for (int s = first; s < cnt; s += WS_PROD) {
                 const int64_t seq = seq0 + s;
@@ -179,33 +197,55 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
                 retire_prev();                                          // hand my previous buffer back first
                 mbar_wait(empty + b, (use & 1) ^ 1);                    // use 0 passes at once
                 const int64_t i0 = (t0 + s) << 5;
-                const int rows = (int)min((int64_t)32, n - i0);
-                // element (row = lane, timestep t): sub-tile t >> 3, chunk (t & 7) ^ (lane & 7)
+                const bool valid = i0 + lane < n;
+                // sample (row = lane, timestep t): sub-tile t >> 3, chunk (t & 7) ^ (lane & 7)
                 unsigned char* row = ring + (size_t)b * WL::TILE + lane * 128;
-                const int sw = lane & 7;
-                auto put = [&](int t, double x, double y) {
-                    *reinterpret_cast<double2*>(row + (t >> 3) * WL::SUB + (((t & 7) ^ sw) << 4)) = make_double2(x, y);
-                };
-                if (lane < rows) {
-                    double x = s_x0[0], y = s_x0[1];
-                    const uint64_t gi = sample_offset + (uint64_t)(i0 + lane);
-                    const uint32_t gi_lo = (uint32_t)gi, gi_hi = (uint32_t)(gi >> 32);
+                double x = s_x0[0], y = s_x0[1];
+                const uint64_t gi = sample_offset + (uint64_t)(i0 + lane);
+                const uint32_t gi_lo = (uint32_t)gi, gi_hi = (uint32_t)(gi >> 32);
+                bool hit_mine = false;
+                // one step: chain, shifted copy for the Gram update, A9 screen (integer pipe) and, for warps that
+                // hold a sample within `box` of the ego in x and y, the exact predicate in the oracle's order
+                auto step = [&](int t, double zx, double zy) {
+                    if (!(exp_flags & 8)) rollout_step(sp[t], x, y, zx, zy);
+                    // absent rows hold the pivot: u = 0 in the Gram update (the tensor map clips them from the store)
+                    *reinterpret_cast<double2*>(row + (t >> 3) * WL::SUB + (((t & 7) ^ sw) << 4)) =
+                        valid ? make_double2(x, y) : s_piv[t];
+                    if (exp_flags & 2) return;
+                    const uint4 k = s_scr[t];
+                    const bool near = valid & (hi_key(x) - k.x <= k.y) & (hi_key(y) - k.z <= k.w);
+                    if (__any_sync(0xffffffffu, near)) {
+                        const double2 e = s_ego[t];
+                        const double dx = __dsub_rn(e.x, x), dy = __dsub_rn(e.y, y);
+                        const double d2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
+                        const bool hit = valid && d2 < r2;
+                        const unsigned bal = __ballot_sync(0xffffffffu, hit);
+                        if (bal) {
+                            hit_mine |= hit;
+                            double pn = hit ? r2 - d2 : 0.0;            // sum over the hit lanes, fixed order
 #pragma unroll
-                    for (int t2 = 0; t2 < TSH / 2; ++t2) {
-                        float za = 0.3f, zb = -0.2f, zc = 0.1f, zd = 0.7f;
-                        if (!(exp_flags & 4)) {
-                            Philox rr = philox4x32_10(gi_lo, gi_hi, (uint32_t)c, (uint32_t)t2, seed_lo, seed_hi);
-                            box_muller(rr.c[0], rr.c[1], za, zb);
-                            box_muller(rr.c[2], rr.c[3], zc, zd);
+                            for (int o = 16; o; o >>= 1) pn += __shfl_xor_sync(0xffffffffu, pn, o);
+                            if (lane == t) { coll_mine += __popc(bal); pen_mine += pn; }
                         }
-                        if (!(exp_flags & 8)) rollout_step(sp[2 * t2], x, y, (double)za, (double)zb);
-                        put(2 * t2, x, y);
-                        if (!(exp_flags & 8)) rollout_step(sp[2 * t2 + 1], x, y, (double)zc, (double)zd);
-                        put(2 * t2 + 1, x, y);
                     }
-                } else {                                // absent rows hold the pivot: u = 0 in the Gram update
-                    for (int t = 0; t < TSH; ++t) put(t, pivot[(c * TSH + t) * 2], pivot[(c * TSH + t) * 2 + 1]);
+                };
+#pragma unroll
+                for (int t2 = 0; t2 < TSH / 2; ++t2) {
+                    float za = 0.3f, zb = -0.2f, zc = 0.1f, zd = 0.7f;
+                    if (!(exp_flags & 4)) {
+                        Philox rr = philox4x32_10(gi_lo, gi_hi, (uint32_t)c, (uint32_t)t2, seed_lo, seed_hi);
+                        box_muller(rr.c[0], rr.c[1], za, zb);
+                        box_muller(rr.c[2], rr.c[3], zc, zd);
+                    }
+#ifdef WS_F2D_BITS
+                    step(2 * t2, f32_to_f64_bits(za), f32_to_f64_bits(zb));
+                    step(2 * t2 + 1, f32_to_f64_bits(zc), f32_to_f64_bits(zd));
+#else
+                    step(2 * t2, (double)za, (double)zb);
+                    step(2 * t2 + 1, (double)zc, (double)zd);
+#endif
                 }
+                any_cnt += __popc(__ballot_sync(0xffffffffu, hit_mine));
                 if (store_traj) fence_proxy_async();    // my generic-proxy writes -> visible to the TMA engine
                 __syncwarp();
                 if (lane == 0) {
@@ -220,6 +260,11 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
                 prev_b = b;
             }
             retire_prev();
+            // this warp's counts of the segment -> shared memory (the consumers fold them into the partial vector)
+            double* pc = s_pcnt + (size_t)p * WL::PC_LEN;
+            if (lane < TSH) { pc[lane] = (double)coll_mine; pc[TSH + lane] = pen_mine; }
+            if (lane == 0) pc[2 * TSH] = (double)any_cnt;
+            cta_bar();                                                  // (S3) counts visible to the consumers
             seq0 += cnt;
             gt += cnt;
         }
@@ -243,93 +288,61 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
         cta_bar();                                      // (S1) producers are done with the previous cell's parameters
         rollout_setup<32 * WS_CONS>(mean, cov, cross, Tm, x0, c, TSH, seed_lo, seed_hi, sp, s_x0, status, x0_out, tid,
                                     t0 == 0);
-        double pivx[TS], pivy[TS], ex[TS], ey[TS];
-        uint32_t kx[TS], wx[TS], ky[TS], wy[TS];        // integer screen: key(x) - kx <= wx  <=>  |ex - x| < box (+ ties)
-#pragma unroll
-        for (int i = 0; i < TS; ++i) {
-            const int t = TS * q + i;
-            pivx[i] = pivot[(c * TSH + t) * 2];
-            pivy[i] = pivot[(c * TSH + t) * 2 + 1];
-            ex[i] = ego[c * ego_cell_stride + 2 * t];
-            ey[i] = ego[c * ego_cell_stride + 2 * t + 1];
-            kx[i] = hi_key(ex[i] - box); wx[i] = hi_key(ex[i] + box) - kx[i];
-            ky[i] = hi_key(ey[i] - box); wy[i] = hi_key(ey[i] + box) - ky[i];
+        if (tid < TSH) {                                // what the producers need per timestep besides the chain
+            const int t = tid;
+            const double px = pivot[(c * TSH + t) * 2], py = pivot[(c * TSH + t) * 2 + 1];
+            const double ex = ego[c * ego_cell_stride + 2 * t], ey = ego[c * ego_cell_stride + 2 * t + 1];
+            s_piv[t] = make_double2(px, py);
+            s_ego[t] = make_double2(ex, ey);
+            // integer screen: key(x) - kx <= wx  <=>  |ex - x| < box (ties in the low word count as near)
+            uint4 k;
+            k.x = hi_key(ex - box); k.y = hi_key(ex + box) - k.x;
+            k.z = hi_key(ey - box); k.w = hi_key(ey + box) - k.z;
+            s_scr[t] = k;
         }
+        double piv[NF];                                 // pivot of my columns NF q .. NF q + NF - 1
+#pragma unroll
+        for (int i = 0; i < NF; ++i) piv[i] = pivot[c * 2 * TSH + NF * q + i];
         double acc[NT][2];
 #pragma unroll
         for (int i = 0; i < NT; ++i) acc[i][0] = acc[i][1] = 0.0;
-        double s1x[TS], s1y[TS], pen[TS];
-        int coll[TS];
+        double s1[NF];
 #pragma unroll
-        for (int i = 0; i < TS; ++i) { s1x[i] = s1y[i] = pen[i] = 0.0; coll[i] = 0; }
-        int any_cnt = 0;
-        int64_t rows_done = 0;
+        for (int i = 0; i < NF; ++i) s1[i] = 0.0;
         cta_bar();                                      // (S2) parameters visible to the producers
         const int first = (int)((warp - seq0 % WS_CONS + WS_CONS) % WS_CONS);
         for (int s = first; s < cnt; s += WS_CONS) {
             const int64_t seq = seq0 + s;
             const int b = (int)(seq % WS_NB);
             const uint32_t use = (uint32_t)(seq / WS_NB);
-            const int64_t i0 = (t0 + s) << 5;
-            const int rows = (int)min((int64_t)32, n - i0);
             mbar_wait(full + b, use & 1);
             // lane (r, q) reads timesteps TS q + i of row 4 g + r: sub-tile t >> 3, chunk (t & 7) ^ (row & 7);
             // row & 7 = 4 (g & 1) + r, so the two parities of g differ by bit 6 of the byte offset.
-            // Two groups per round, software pipelined: the next pair's loads are issued before this pair's
-            // 2 x NT DMMAs, so the in-order warp never waits for shared memory.
+            // Fragments = loads minus the pivot (the only vector FP64 work left in this warp besides S1).
             const unsigned char* tile = ring + (size_t)b * WL::TILE + ((TS * q) >> 3) * WL::SUB + r * 128;
-            double2 cur[2][TS];
-            auto load_pair = [&](int g2) {
-#pragma unroll
-                for (int h = 0; h < 2; ++h)
-#pragma unroll
-                    for (int i = 0; i < TS; ++i)
-                        cur[h][i] = *reinterpret_cast<const double2*>(tile + g2 * 1024 + h * 512 + (ld_off[i] ^ (h << 6)));
-            };
-            load_pair(0);
-#pragma unroll 1
-            for (int g2 = 0; g2 < 4; ++g2) {
-                double f[2][NF];
-                bool near_any = false;
+            double f[2][2][NF];                         // [buffer][group of the pair][fragment]
+            auto load_pair = [&](int g2, int buf) {
 #pragma unroll
                 for (int h = 0; h < 2; ++h)
 #pragma unroll
                     for (int i = 0; i < TS; ++i) {
-                        const double ux = cur[h][i].x - pivx[i], uy = cur[h][i].y - pivy[i];
-                        s1x[i] += ux;
-                        s1y[i] += uy;
-                        f[h][2 * i] = ux;
-                        f[h][2 * i + 1] = uy;
-                        if (exp_flags & 2) continue;
-                        // A9 screen on the INTEGER pipe (a vector FP64 instruction costs this warp a DMMA slot):
-                        // a sample whose x or y is at least `box` away from the ego cannot be a hit, and almost
-                        // every sample is; the exact fp64 predicate runs only for warps that hold a near sample.
-                        near_any |= (hi_key(cur[h][i].x) - kx[i] <= wx[i]) & (hi_key(cur[h][i].y) - ky[i] <= wy[i]);
+                        const double2 v = *reinterpret_cast<const double2*>(tile + g2 * 1024 + h * 512 + (ld_off[i] ^ (h << 6)));
+                        f[buf][h][2 * i] = v.x - piv[2 * i];
+                        f[buf][h][2 * i + 1] = v.y - piv[2 * i + 1];
                     }
-                if (__any_sync(0xffffffffu, near_any)) {        // warp-uniform
+            };
+            load_pair(0, 0);
 #pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        const bool rv = 8 * g2 + 4 * h + r < rows;
-                        bool hit_any = false;
+            for (int g2 = 0; g2 < 4; ++g2) {
+                const int buf = g2 & 1;
+                if (g2 < 3) load_pair(g2 + 1, buf ^ 1);  // in flight during this pair's 2 x NT DMMAs
 #pragma unroll
-                        for (int i = 0; i < TS; ++i) {
-                            // A9 predicate, fixed order, no FMA contraction (identical to stats.cu)
-                            const double dx = __dsub_rn(ex[i], cur[h][i].x), dy = __dsub_rn(ey[i], cur[h][i].y);
-                            const double d2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
-                            if (rv && d2 < r2) { ++coll[i]; pen[i] += r2 - d2; hit_any = true; }
-                        }
-                        const unsigned bal = __ballot_sync(0xffffffffu, hit_any);
+                for (int h = 0; h < 2; ++h) {
 #pragma unroll
-                        for (int rr = 0; rr < 4; ++rr) any_cnt += (bal & (0x11111111u << rr)) != 0;
-                    }
-                }
-                if (g2 < 3) load_pair(g2 + 1);
-                if (!(exp_flags & 1)) {
-                    gram_update<NF>(acc, f[0]);
-                    gram_update<NF>(acc, f[1]);
+                    for (int i = 0; i < NF; ++i) s1[i] += f[buf][h][i];
+                    if (!(exp_flags & 1)) gram_update<NF>(acc, f[buf][h]);
                 }
             }
-            rows_done += rows;
             __syncwarp();
             if (lane == 0) mbar_arrive(empty + b);
         }
@@ -337,33 +350,30 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
         double* wsm = area + (size_t)warp * SM::PW;
         store_gram_tiles<NF>(wsm, acc, q, r);
 #pragma unroll
-        for (int i = 0; i < TS; ++i) {
-            double v[4] = {s1x[i], s1y[i], (double)coll[i], pen[i]};
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                v[k] += __shfl_xor_sync(0xffffffffu, v[k], 1);
-                v[k] += __shfl_xor_sync(0xffffffffu, v[k], 2);
-            }
-            if (r == 0) {
-                const int t = TS * q + i;
-                wsm[SM::O_S1 + 2 * t] = v[0];
-                wsm[SM::O_S1 + 2 * t + 1] = v[1];
-                wsm[SM::O_COLL + t] = v[2];
-                wsm[SM::O_PEN + t] = v[3];
-            }
+        for (int i = 0; i < NF; ++i) {
+            double v = s1[i];
+            v += __shfl_xor_sync(0xffffffffu, v, 1);
+            v += __shfl_xor_sync(0xffffffffu, v, 2);
+            if (r == 0) wsm[SM::O_S1 + NF * q + i] = v;            // column NF q + i = 2 t + {x, y}
         }
-        if (lane == 0) { wsm[SM::O_ANY] = (double)any_cnt; wsm[SM::O_ANY + 1] = (double)rows_done; }
-        asm volatile("bar.sync 1, %0;" ::"n"(32 * WS_CONS) : "memory");
-        // ---- add the consumer warps in warp order into the partial vector of segment (CTA, cell)
+        cta_bar();                                      // (S3) consumer areas and producer counts are written
+        // ---- partial vector of segment (CTA, cell): consumer warps in warp order, then the producers' counts
         const int64_t slot = (int64_t)blockIdx.x + c;
         double* out = partials + slot * (int64_t)L.len;
+        // rows of this segment: whole tiles except the last one of the cell
+        const int64_t rows_seg = min((t0 + cnt) << 5, n) - (t0 << 5);
         for (int e = tid; e < L.len; e += 32 * WS_CONS) {
-            int src = packed_to_area<NF>(e, L, false, false);
-            if (src == -2) { out[e] = 0.0; continue; }      // d2s: from the Gram identity in the finalize kernel; no yaw
-            if (src == -1) src = SM::O_ANY + 1;
             double sum = 0.0;
+            if (e == 0) {
+                sum = (double)rows_seg;
+            } else if (e < L.o_coll) {
+                const int src = packed_to_area<NF>(e, L, false, false);
 #pragma unroll
-            for (int w = 0; w < WS_CONS; ++w) sum += area[(size_t)w * SM::PW + src];
+                for (int w = 0; w < WS_CONS; ++w) sum += area[(size_t)w * SM::PW + src];
+            } else if (e < L.o_d2s) {                   // coll[T], any, pen[T]: producer counts, warp order
+                const int k = e < L.o_any ? e - L.o_coll : (e == L.o_any ? 2 * TSH : TSH + (e - L.o_pen));
+                for (int w = 0; w < WS_PROD; ++w) sum += s_pcnt[(size_t)w * WL::PC_LEN + k];
+            }                                           // d2s: Gram identity in the finalize kernel; no yaw sums
             out[e] = sum;
         }
         if (tid == 0) slot_cell[slot] = (int32_t)c;
