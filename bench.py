@@ -3,11 +3,15 @@
 
 One JSON line.  Headline (BASELINE.json metric, first term): Monte Carlo sampled
 trajectory-steps/s of config c3 - per GPU 1M samples per obstacle, O = 8 obstacles x
-4 modes, ph16: Philox rollout -> ONE read of the trajectories for collision counts / soft
-cost / all (t, tau) moments -> one NCCL all-reduce of the packed sums when N > 1
-(weak scaling: every rank rolls its own 1M samples per obstacle, Philox sample_offset =
-rank * n).  The two other terms of the metric ride in the same line under "also":
-batched MVOE half-plane sweep fits/s (c4) and the p50 ms of the full c2 constraint build.
+4 modes, ph16 - through the FASTEST path the library has for that job: ONE kernel
+(ccmpc_mc_rollout_sums) rolls the samples out (Philox), stores the trajectory tensor and
+reduces it to collision counts / soft cost / all (t, tau) power sums; N > 1: one NCCL
+all-reduce of the packed sums on a side stream, overlapped with the next step's kernel;
+then the moments kernel.  Weak scaling by default (every rank rolls its own 1M samples per
+obstacle, Philox sample_offset = rank * n); --scaling strong splits BASELINE.json's 1M
+samples per obstacle over the ranks.  The two other terms of the metric ride in the same
+line under "also" and, as scalars, under "summary" (last key): batched MVOE fits/s (c4)
+and the p50 ms of the full c2 constraint build, plus c1 and c5.
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 """
@@ -32,8 +36,12 @@ C2 = dict(O=4, K=25, T=8, N=5000, seed=2)                       # one MPC step
 C5 = dict(O=8, K=4, T=16, N=20_000, steps=200, seed=5)          # closed-loop replay
 METRIC = "mc_traj_steps_per_sec"
 UNIT = "traj-steps/s"
-BYTES_PER_TRAJ_STEP_SUMS = 16        # sample_sums: x, y fp64 read once
-BYTES_PER_TRAJ_STEP_ROLLOUT = 16     # rollout: x, y fp64 written once
+BYTES_PER_TRAJ_STEP = 16             # x, y fp64 written once by the fused kernel (the two-kernel path moves 32)
+# FP64 work of one trajectory (ph16) in the fused kernel: the Gram update is 10 DMMA tiles
+# (m8n8k4, 256 FMAs each) per 4 samples; vector FP64 = chain 7 FMAs per step + pivot shift and S1 (2 + 2 adds per step)
+FP64_DMMA_FLOP_PER_TRAJ = 10 * 512 / 4
+FP64_VECTOR_FLOP_PER_TRAJ = 16 * (7 * 2 + 4)
+FP64_PEAKS = {"dmma_tflops": 37.1, "dfma_tflops": 33.7, "source": "profiles/r01_fp64_pipe_microbench.txt"}
 
 
 def _peaks():
@@ -138,7 +146,8 @@ def _cpu_mc_cell(args):
     """One (obstacle, mode) cell: predict_ideal body (v8ideal:2664-2706) + counts (A9) +
     save_moments (v8ideal:2586-2606) on the CPU oracle.  Returns traj-steps processed."""
     seed, n, T = args
-    from oracle import restate, synth
+    from ccmpc_b200 import synth
+    from oracle import restate
     sc = synth.make_scene(C3["seed"], 1, 1, T + 1)
     mean, cov, cross = sc.moments()
     rng = np.random.default_rng(seed)
@@ -198,12 +207,14 @@ def run_reference(args):
     return 0
 
 
-def _config(n_gpus):
-    return {"workload": "c3: MC collision-risk estimate, 1M samples/obstacle per GPU, O=8 x K=4 cells, ph16 "
-                        "(rollout -> counts/cost/moments -> count all-reduce)",
-            "O": C3["O"], "K": C3["K"], "T": C3["T"], "samples_per_cell_per_gpu": C3["n_per_cell"],
-            "sharding": f"samples x{n_gpus} (Philox sample_offset = rank * n)",
-            "l2": "inputs_exceed_l2 (2.05 GB trajectory tensor per step)"}
+def _config(n_gpus, scaling="weak", n_local=None):
+    n_local = C3["n_per_cell"] if n_local is None else n_local
+    per = "per GPU" if scaling == "weak" else f"in total, split over {n_gpus} GPUs"
+    return {"workload": f"c3: MC collision-risk estimate, 1M samples/obstacle {per}, O=8 x K=4 cells, ph16 "
+                        "(rollout + trajectory store + counts/cost/power sums in one kernel -> all-reduce -> moments)",
+            "O": C3["O"], "K": C3["K"], "T": C3["T"], "samples_per_cell_per_gpu": n_local,
+            "sharding": f"samples x{n_gpus} (Philox counter = global sample index)",
+            "l2": f"outputs_exceed_l2 ({n_local * 32 * 256 / 1e9:.2f} GB trajectory tensor written per step)"}
 
 
 # ---------------------------------------------------------------------------------------------
@@ -212,8 +223,7 @@ def _config(n_gpus):
 def run_ours(args):
     import torch
     import torch.distributed as dist
-    from ccmpc_b200 import _lib, midlevel, ops
-    from oracle import synth                      # input generators only (no reference arithmetic)
+    from ccmpc_b200 import _lib, midlevel, ops, sharding, synth   # synth: input generators only
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -233,14 +243,17 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    O, K, T, n = C3["O"], C3["K"], C3["T"], args.n_per_cell
+    O, K, T = C3["O"], C3["K"], C3["T"]
     C = O * K
+    if args.scaling == "strong":            # BASELINE.json configs[2]: 1M samples per obstacle, sharded over the ranks
+        sample_offset, n = sharding.sample_shard(args.n_per_cell, rank, world)
+        n_total = args.n_per_cell
+    else:                                   # weak: every rank rolls its own 1M samples per obstacle
+        sample_offset, n = rank * args.n_per_cell, args.n_per_cell
+        n_total = args.n_per_cell * world
     sc = synth.make_scene(C3["seed"], O, K, T + 1)
     mean_h, cov_h, cross_h = sc.moments()
     ego_h = synth.reference_trajectory(T)
-    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
-    mean_p, cov_p, cross_p, ego_p = (pin(mean_h.reshape(C, T + 1, 2)), pin(cov_h.reshape(C, T + 1, 2, 2)),
-                                     pin(cross_h.reshape(C, T + 1, T + 1, 2, 2)), pin(ego_h))
     # the step's host inputs live in ONE pinned arena (one H2D copy per step on the end-to-end leg)
     _parts = (mean_h.reshape(C, T + 1, 2), cov_h.reshape(C, T + 1, 2, 2), cross_h.reshape(C, T + 1, T + 1, 2, 2), ego_h)
     _sizes = [int(np.prod(a.shape)) for a in _parts]
@@ -253,54 +266,60 @@ def run_ours(args):
         dev_views.append(arena_d[_o:_o + sz].view(a.shape))
         _o += sz
     mean_p, cov_p, cross_p, ego_p = host_views
-    pivot_e2e = torch.empty((C, T, 2), dtype=torch.float64, device=dev)
     mean_d, cov_d, cross_d, ego_d = (t.to(dev) for t in (mean_p, cov_p, cross_p, ego_p))
     pivot = mean_d[:, 1:T + 1].contiguous()
     traj = torch.empty((C, n, T, 2), dtype=torch.float64, device=dev)
-    offsets = torch.arange(C + 1, dtype=torch.int64, device=dev) * n
-    ws = ops.sample_sums_workspace(C * n, C, T, dev)
-    sums = torch.empty((C, ops.sums_len(T)), dtype=torch.float64, device=dev)
-    flat = traj.view(C * n, T, 2)
-    mom_out = None
-    sums_host = torch.empty(sums.shape, dtype=torch.float64).pin_memory()
+    ws = ops.mc_rollout_sums_workspace(C, n, T, dev)
+    # double-buffered sums: the all-reduce + moments of step i run on a side stream under the kernel of step i + 1
+    sums2 = [torch.empty((C, ops.sums_len(T)), dtype=torch.float64, device=dev) for _ in range(2)]
+    mom2 = [None, None]
+    side = torch.cuda.Stream(device=dev)
+    done = [None, None]                       # event: buffer free again (its reduction and moments have finished)
+    sums_host = torch.empty(sums2[0].shape, dtype=torch.float64).pin_memory()
     ev = lambda: torch.cuda.Event(enable_timing=True)
+    main = torch.cuda.current_stream()
 
-    def step(i, events=None, from_host=False):
-        nonlocal mom_out
-        if from_host:
-            arena_d.copy_(arena_p, non_blocking=True)
-            m, c, x, e = dev_views
-            pv = pivot_e2e
-            pv.copy_(m[:, 1:T + 1])
-        else:
-            m, c, x, e, pv = mean_d, cov_d, cross_d, ego_d, pivot
+    def step(i, events=None):
+        """One c3 step, device resident: ONE kernel for rollout + store + sums, then (N > 1) the NCCL all-reduce of the
+        packed sums and the moments kernel on the side stream - step i + 1's kernel does not wait for them."""
+        b = i & 1
+        if done[b] is not None:
+            main.wait_event(done[b])                                   # buffer b is free again
         if events:
             events[0].record()
-        ops.mc_rollout(m, c, x, None, n, T, seed=1234 + i, sample_offset=rank * n, out=traj)
+        ops.mc_rollout_sums(mean_d, cov_d, cross_d, None, n, T, pivot, ego_d, seed=1234 + i,
+                            sample_offset=sample_offset, workspace=ws, out=traj, sums_out=sums2[b])
         if events:
             events[1].record()
-        ops.sample_sums(flat, offsets, pv, ego=e, R=ops.R_EV_OV, workspace=ws, out=sums)
-        if events:
-            events[2].record()
-        if pg is not None:
-            dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=pg)
-        mom_out = ops.moments_from_sums(sums, pv, want_yaw=False, out=mom_out)
-        if from_host:
-            sums_host.copy_(sums, non_blocking=True)
-            torch.cuda.current_stream().synchronize()
+        if pg is None:
+            mom2[b] = ops.moments_from_sums(sums2[b], pivot, want_yaw=False, out=mom2[b])
+            return
+        ready = torch.cuda.Event()
+        ready.record(main)
+        with torch.cuda.stream(side):
+            side.wait_event(ready)
+            sharding.allreduce_sums(sums2[b], group=pg)
+            mom2[b] = ops.moments_from_sums(sums2[b], pivot, want_yaw=False, out=mom2[b])
+            done[b] = torch.cuda.Event()
+            done[b].record(side)
+
+    def join():
+        main.wait_stream(side)
 
     # ---- device-resident timing --------------------------------------------------------------
     sampler = ClockSampler(local, enabled=(rank == 0 and os.environ.get("CCMPC_BENCH_NO_CLOCKS") != "1"))
     for i in range(args.warmup):
         step(i)
+    join()
     barrier()
     l0 = lib.ccmpc_launch_count()
-    evs = [[ev(), ev(), ev()] for _ in range(args.steps)]
+    evs = [[ev(), ev()] for _ in range(args.steps)]
     t_start, t_stop = ev(), ev()
     with sampler as clocks:
         t_start.record()
         for i in range(args.steps):
             step(args.warmup + i, evs[i])
+        join()
         t_stop.record()
         barrier()
     launches = int(lib.ccmpc_launch_count() - l0)
@@ -308,32 +327,49 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(ms_total, op=dist.ReduceOp.MAX)
     ms_step = float(ms_total.item()) / args.steps
-    units_step = C * n * T * world
+    units_step = C * n_total * T
     value = units_step / (ms_step * 1e-3)
-    roll_ms = float(np.mean([e[0].elapsed_time(e[1]) for e in evs]))
-    sums_ms = float(np.mean([e[1].elapsed_time(e[2]) for e in evs]))
+    fused_ms = float(np.mean([e[0].elapsed_time(e[1]) for e in evs]))
+    last = (args.warmup + args.steps - 1) & 1
+    sums, mom_out = sums2[last], mom2[last]
 
-    # ---- end-to-end through the host-facing call: H2D of the moments / ego, D2H of the sums ---
+    # ---- end-to-end through the planner-facing call (MidlevelConstraints.mc_collision_risk): the step's inputs
+    #      come from pinned HOST memory (one H2D copy of the moment tensors + ego plan), the packed sums go back to
+    #      the host (D2H) and the stream is synchronised, every step
+    mc = midlevel.MidlevelConstraints(T + 1, out_dir=None, device=dev)
+    m_, c_, x_, e_ = dev_views
+    mom_obj = midlevel.Moments(m_, c_, x_, np.repeat(np.arange(O), K), np.tile(np.arange(K), O), [K] * O, T + 1)
+
+    def step_e2e(i):
+        arena_d.copy_(arena_p, non_blocking=True)
+        res = mc.mc_collision_risk(mom_obj, [K] * O, T, e_, n_samples=n, seed=1234 + i, sample_offset=sample_offset,
+                                   process_group=pg, want_moments=True)
+        sums_host.copy_(res["sums"], non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return res
+
     for i in range(3):
-        step(i, from_host=True)
+        step_e2e(i)
     barrier()
     e0, e1 = ev(), ev()
     e0.record()
     for i in range(args.steps):
-        step(args.warmup + i, from_host=True)
+        res_e2e = step_e2e(args.warmup + i)
     e1.record()
     barrier()
     ms_e2e = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(ms_e2e, op=dist.ReduceOp.MAX)
     e2e_value = units_step / (float(ms_e2e.item()) / args.steps * 1e-3)
-    h2d = int(sum(t.numel() * t.element_size() for t in (mean_p, cov_p, cross_p, ego_p)))
+    h2d = int(arena_p.numel() * arena_p.element_size())
     d2h = int(sums_host.numel() * sums_host.element_size())
 
-    # sanity on the result of the last step (never silently time a no-op)
+    # sanity on the result of the last step (never silently time a no-op); both legs give the same counts
     counts = mom_out["counts"].cpu().numpy()
-    assert int(sums[0, 0].item()) == n * world, "sample count mismatch after all-reduce"
-    assert counts.min() >= 0 and counts[:, :T].max() <= n * world
+    assert int(sums[0, 0].item()) == n_total, "sample count mismatch after all-reduce"
+    assert counts.min() >= 0 and counts[:, :T].max() <= n_total
+    assert np.array_equal(res_e2e["counts"].cpu().numpy(), counts), "end-to-end leg and device leg disagree"
+    del res_e2e, mc
 
     also = {}
     if not args.skip_also:
@@ -346,16 +382,20 @@ def run_ours(args):
         return 0
 
     peak, peak_src = _peaks()
-    dom = "sample_sums_kernel" if sums_ms >= roll_ms else "rollout_kernel"
-    dom_ms = max(sums_ms, roll_ms)
-    ach = C * n * T * (BYTES_PER_TRAJ_STEP_SUMS if dom == "sample_sums_kernel" else BYTES_PER_TRAJ_STEP_ROLLOUT) \
-        / (dom_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": dom, "achieved": ach, "peak": peak, "peak_source": peak_src, "unit": "GB/s",
-                "frac": ach / peak, "traffic": _traffic(dom) if n == C3["n_per_cell"] else None,
-                "algorithmic_bytes": C * n * T * 16,
-                "kernels_ms": {"rollout_kernel": roll_ms, "sample_sums(scan+sums+finalize)": sums_ms},
-                "other_kernel": {"name": "rollout_kernel" if dom == "sample_sums_kernel" else "sample_sums_kernel",
-                                 "achieved": C * n * T * 16 / (min(sums_ms, roll_ms) * 1e-3) / 1e9}}
+    ach = C * n * T * BYTES_PER_TRAJ_STEP / (fused_ms * 1e-3) / 1e9
+    trajs = C * n
+    floor_ms = 1e3 * (trajs * FP64_DMMA_FLOP_PER_TRAJ / (FP64_PEAKS["dmma_tflops"] * 1e12)
+                      + trajs * FP64_VECTOR_FLOP_PER_TRAJ / (FP64_PEAKS["dfma_tflops"] * 1e12))
+    roofline = {"bound": "hbm", "kernel": "rollout_sums_ws_kernel", "achieved": ach, "peak": peak,
+                "peak_source": peak_src, "unit": "GB/s", "frac": ach / peak,
+                "traffic": _traffic("rollout_sums_ws_kernel") if n == C3["n_per_cell"] else None,
+                "algorithmic_bytes": C * n * T * BYTES_PER_TRAJ_STEP,
+                "kernels_ms": {"mc_rollout_sums (rollout_sums_ws_kernel + finalize)": fused_ms},
+                # the roof that actually binds this kernel: the shared FP64 / DMMA pipe (no tcgen05 kind for FP64)
+                "fp64_pipe": {"dmma_flop": trajs * FP64_DMMA_FLOP_PER_TRAJ, "vector_flop": trajs * FP64_VECTOR_FLOP_PER_TRAJ,
+                              "floor_ms": floor_ms, "frac": floor_ms / fused_ms, "peaks": FP64_PEAKS,
+                              "achieved_tflops": trajs * (FP64_DMMA_FLOP_PER_TRAJ + FP64_VECTOR_FLOP_PER_TRAJ)
+                              / (fused_ms * 1e-3) / 1e12}}
 
     cpu = None
     if not args.skip_cpu:
@@ -367,17 +407,47 @@ def run_ours(args):
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-        "data": "synthetic", "config": _config(world),
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "config": _config(world, args.scaling, n),
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "api": "MidlevelConstraints.mc_collision_risk"},
         "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks.summary(),
         "also": also,
+        "summary": _summary(value, ms_step, e2e_value, roofline, also, cpu),
     }
     emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
     return 0
+
+
+def _summary(value, ms_step, e2e_value, roofline, also, cpu):
+    """The three terms of BASELINE.json's metric (and what explains them) as flat scalars, LAST in the line so that
+    a reader of the tail sees them: M1 traj-steps/s, M2 MVOE fits/s, M3 c2 constraint-build p50 ms."""
+    g = lambda k, f, d=None: (also.get(k) or {}).get(f, d)
+    r = lambda k: ((also.get(k) or {}).get("roofline") or {}).get("frac")
+    out = {
+        "mc_traj_steps_per_sec": value, "mc_ms_per_step": ms_step, "mc_e2e_traj_steps_per_sec": e2e_value,
+        "mc_frac_hbm": roofline["frac"], "mc_frac_fp64_pipe": roofline["fp64_pipe"]["frac"],
+        "mc_two_kernel_ms": g("mc_step_two_kernels", "ms"), "mc_risk_only_ms": g("mc_risk_fused", "ms"),
+        "mvoe_fits_per_sec_ref_seq": g("mvoe_sweep", "value"), "mvoe_frac_hbm_ref_seq": r("mvoe_sweep"),
+        "mvoe_fits_per_sec_direct": g("mvoe_sweep_direct", "value"), "mvoe_frac_hbm_direct": r("mvoe_sweep_direct"),
+        "mvoe_full_minkowski_fits_per_sec_ref_seq": g("mvoe_minkowski_full", "value"),
+        "mvoe_full_minkowski_fits_per_sec_direct": g("mvoe_minkowski_full_direct", "value"),
+        "c2_build_p50_ms": g("constraint_build_c2", "p50_host_to_host"),
+        "c2_device_ms": g("constraint_build_c2", "p50_device_resident"),
+        "c2_planner_class_p50_ms": g("constraint_build_c2_planner_class", "p50_host_to_host"),
+        "c2_block_handover_ms": g("constraint_build_c2_planner_class", "block_ms"),
+        "c2_python_rows_ms": g("constraint_build_c2_planner_class", "python_rows_ms"),
+        "c1_two_step_p50_ms": g("shrinking_horizon_c1", "p50_two_steps"),
+        "c1_step2_p50_ms": g("shrinking_horizon_c1", "p50_step2"),
+        "c5_p50_ms": g("replay_c5_sampler", "p50_host_to_host"),
+        "strong_scaling_ms": g("mc_strong_scaling", "ms"), "strong_scaling_traj_steps_per_sec": g("mc_strong_scaling", "value"),
+        "cpu_mc_traj_steps_per_sec_1core": (cpu or {}).get("value"),
+        "cpu_c2_build_s": g("cpu_baselines", "c2_build_s"), "cpu_mvoe_fits_per_sec_1core": g("cpu_baselines", "mvoe_fits_per_sec"),
+    }
+    return {k: v for k, v in out.items() if v is not None}
 
 
 def bench_also(torch, ops, midlevel, synth, dev, args, world=1, rank=0, dist=None):
@@ -427,29 +497,37 @@ def bench_also(torch, ops, midlevel, synth, dev, args, world=1, rank=0, dist=Non
         "roofline": {"bound": "issue", "algorithmic_hbm_bytes": 0,
                      "note": "0 algorithmic HBM bytes: bound by instruction issue (Philox + Box-Muller + fp64 chain); "
                              "the materialising path moves 32 B per trajectory-step"}}
-    # ---- the headline step with rollout and sums FUSED (same outputs: trajectories materialised, packed sums,
-    #      moments; the trajectory tensor is written once and not read back)
+    # ---- the same c3 step on the TWO-KERNEL path (ccmpc_mc_rollout, then ccmpc_sample_sums reads the trajectory
+    #      tensor back: 32 B of HBM traffic per trajectory-step instead of 16) - round 1's headline, kept for reference
     traj3 = torch.empty((C3c, n3, T3, 2), dtype=torch.float64, device=dev)
     piv3 = m3[:, 1:T3 + 1].contiguous()
-    wsf = ops.mc_rollout_sums_workspace(C3c, n3, T3, dev)
+    off3 = torch.arange(C3c + 1, dtype=torch.int64, device=dev) * n3
+    wsp = ops.sample_sums_workspace(C3c * n3, C3c, T3, dev)
     sums3 = torch.empty((C3c, ops.sums_len(T3)), dtype=torch.float64, device=dev)
     mom3 = None
+    evp = [[ev(), ev(), ev()] for _ in range(reps)]
 
-    def fused_step(i):
+    def pair_step(i, e=None):
         nonlocal mom3
-        ops.mc_rollout_sums(m3, c3, x3, None, n3, T3, piv3, ego3, seed=1234 + i, sample_offset=rank * n3,
-                            workspace=wsf, out=traj3, sums_out=sums3)
+        if e:
+            e[0].record()
+        ops.mc_rollout(m3, c3, x3, None, n3, T3, seed=1234 + i, sample_offset=rank * n3, out=traj3)
+        if e:
+            e[1].record()
+        ops.sample_sums(traj3.view(C3c * n3, T3, 2), off3, piv3, ego=ego3, workspace=wsp, out=sums3)
+        if e:
+            e[2].record()
         if world > 1:
             dist.all_reduce(sums3, op=dist.ReduceOp.SUM)
         mom3 = ops.moments_from_sums(sums3, piv3, want_yaw=False, out=mom3)
 
     for i in range(3):
-        fused_step(i)
+        pair_step(i)
     torch.cuda.synchronize()
     a, b = ev(), ev()
     a.record()
     for i in range(reps):
-        fused_step(3 + i)
+        pair_step(3 + i, evp[i])
     b.record()
     torch.cuda.synchronize()
     ms = a.elapsed_time(b) / reps
@@ -458,17 +536,54 @@ def bench_also(torch, ops, midlevel, synth, dev, args, world=1, rank=0, dist=Non
         dist.all_reduce(mt, op=dist.ReduceOp.MAX)
         ms = float(mt.item())
     assert int(sums3[0, 0].item()) == n3 * world
-    out["mc_step_fused"] = {
+    r_ms = float(np.mean([e[0].elapsed_time(e[1]) for e in evp]))
+    s_ms = float(np.mean([e[1].elapsed_time(e[2]) for e in evp]))
+    gb = C3c * n3 * T3 * 16 / 1e9
+    out["mc_step_two_kernels"] = {
         "metric": "mc_traj_steps_per_sec", "value": C3c * n3 * T3 * world / (ms * 1e-3), "unit": "traj-steps/s",
         "ms": ms, "n_gpus": world,
-        "workload": "the headline c3 step (rollout -> trajectories in HBM -> counts / cost / all (t, tau) moments"
-                    f"{' -> all-reduce' if world > 1 else ''} -> moments) with rollout, store and sums in ONE kernel",
-        "roofline": {"bound": "fp64 pipe / latency", "algorithmic_hbm_bytes": C3c * n3 * T3 * 16,
-                     "achieved": C3c * n3 * T3 * 16 / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
-                     "frac": C3c * n3 * T3 * 16 / (ms * 1e-3) / 1e9 / peak,
-                     "note": "16 B per trajectory-step (written once) instead of 32 B; ncu: tensor (DMMA) pipe 34 % + "
-                             "FP64 22 %, issue 43 %, 16 warps / SM - neither HBM nor a pipe is saturated"}}
-    del m3, c3, x3, ws3, risk, traj3, wsf, sums3
+        "workload": "the c3 step as two kernels: rollout -> trajectories in HBM -> sample_sums reads them back"
+                    f"{' -> all-reduce' if world > 1 else ''} -> moments",
+        "kernels_ms": {"rollout_kernel": r_ms, "sample_sums": s_ms},
+        "roofline": {"bound": "hbm", "rollout_kernel": {"achieved": gb / (r_ms * 1e-3), "frac": gb / (r_ms * 1e-3) / peak},
+                     "sample_sums_kernel": {"achieved": gb / (s_ms * 1e-3), "frac": gb / (s_ms * 1e-3) / peak},
+                     "unit": "GB/s", "peak": peak}}
+    # ---- strong scaling of the headline step: BASELINE.json configs[2] as stated - 1M samples per obstacle IN TOTAL,
+    #      split over the ranks by sharding.sample_shard (Philox counter = global sample index), all-reduce exposed
+    if world > 1:
+        from ccmpc_b200 import sharding
+        lo, nl = sharding.sample_shard(C3["n_per_cell"], rank, world)
+        wss = ops.mc_rollout_sums_workspace(C3c, nl, T3, dev)
+        trs = traj3.view(-1)[:C3c * nl * T3 * 2].view(C3c, nl, T3, 2)
+
+        def strong_step(i):
+            nonlocal mom3
+            ops.mc_rollout_sums(m3, c3, x3, None, nl, T3, piv3, ego3, seed=1234 + i, sample_offset=lo, workspace=wss,
+                                out=trs, sums_out=sums3)
+            dist.all_reduce(sums3, op=dist.ReduceOp.SUM)
+            mom3 = ops.moments_from_sums(sums3, piv3, want_yaw=False, out=mom3)
+
+        for i in range(5):
+            strong_step(i)
+        torch.cuda.synchronize()
+        dist.barrier()
+        a, b = ev(), ev()
+        a.record()
+        for i in range(20):
+            strong_step(5 + i)
+        b.record()
+        torch.cuda.synchronize()
+        mt = torch.tensor([a.elapsed_time(b) / 20], dtype=torch.float64, device=dev)
+        dist.all_reduce(mt, op=dist.ReduceOp.MAX)
+        ms = float(mt.item())
+        assert int(sums3[0, 0].item()) == C3["n_per_cell"]
+        out["mc_strong_scaling"] = {
+            "metric": "mc_traj_steps_per_sec", "value": C3c * C3["n_per_cell"] * T3 / (ms * 1e-3), "unit": "traj-steps/s",
+            "ms": ms, "n_gpus": world, "samples_per_cell_per_gpu": nl, "scaling": "strong",
+            "workload": f"c3 as BASELINE.json states it: 1M samples per obstacle in total, {nl} per cell per GPU, one "
+                        f"exposed NCCL all-reduce of the 164 KB packed sums per step"}
+        del wss, trs
+    del m3, c3, x3, ws3, risk, traj3, wsp, sums3
     # ---- c4: batched MVOE footprint fit + tangent half-plane sweep ---------------------------
     S, O, T, K = C4["S"], C4["O"], C4["T"], C4["K"]
     rng = np.random.default_rng(C4["seed"])
@@ -621,6 +736,105 @@ def bench_also(torch, ops, midlevel, synth, dev, args, world=1, rank=0, dist=Non
                     "L4 polytopes -> violation counts; L2 flushed between iterations",
         "rows": int(step.C * step.P), "launches_per_step": step.launches_per_step}
     del step
+    # ---- c2 through the planner-facing CLASS (the call INTEGRATION.md tells a maintainer to make): OVehicle-like
+    #      objects in (per-mode sample arrays on the host), the reference's 9-tuple out; then the hand-over of the
+    #      2800 rows to the solver: one stacked (A, b) block built on the device vs one Python object per row
+    import types
+    pos_c2 = pos
+    ovs = []
+    for o in range(C2["O"]):
+        pp = [np.ascontiguousarray(pos_c2[o][z[o] == k]) for k in range(C2["K"])]
+        ovs.append(types.SimpleNamespace(pred_positions=pp, pred_yaws=[np.zeros(p.shape[:2]) for p in pp],
+                                         n_states=C2["K"], bbox=np.array([3.7, 1.79])))
+    mc = midlevel.MidlevelConstraints(C2["T"], out_dir=None, device=dev)
+    prm = types.SimpleNamespace(frame=100)
+    tc = []
+    for i in range(5 + 30):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        built = mc.compute_obstacle_constraints_GMM_Minkowski_idealprediction(prm, ovs, Tsh=C2["T"], ref_traj=ref_traj)
+        if i >= 5:
+            tc.append((time.perf_counter() - t0) * 1e3)
+    hp = built[0]
+    tb, tp = [], []
+    for _ in range(20):
+        t0 = time.perf_counter()
+        blk = hp.block()
+        tb.append((time.perf_counter() - t0) * 1e3)
+        t0 = time.perf_counter()
+        fn, ft, fr, fs = hp.n.reshape(-1, 2), hp.t.reshape(-1), hp.rhs.reshape(-1), hp.side.reshape(-1)
+        rows = [(fn[r], int(ft[r]), float(fr[r]), ">=" if fs[r] > 0 else "<=") for r in range(fn.shape[0])]
+        tp.append((time.perf_counter() - t0) * 1e3)
+    assert blk["A_x"].shape == (len(rows), 4 * C2["T"])
+    out["constraint_build_c2_planner_class"] = {
+        "metric": "mpc_step_constraint_build_p50_ms", "unit": "ms", "higher_is_better": False,
+        "p50_host_to_host": float(np.percentile(tc, 50)), "p95_host_to_host": float(np.percentile(tc, 95)),
+        "block_ms": float(np.percentile(tb, 50)), "python_rows_ms": float(np.percentile(tp, 50)),
+        "workload": "c2 through MidlevelConstraints.compute_obstacle_constraints_GMM_Minkowski_idealprediction: 100 "
+                    "per-mode host arrays packed + H2D, sums, Minkowski rows, L4, moments, nested containers of the "
+                    "reference's 9-tuple; block_ms = HalfPlanes.block() (A_x [2800, 32], b_x on the device + D2H), "
+                    "python_rows_ms = one Python tuple per row (a lower bound of the reference's per-row cvxpy "
+                    "expressions, v8ideal:927-936; cvxpy is not installed here)"}
+    del mc, built, hp, blk, rows
+    # ---- c1 (configs[0]: scene4_ov1_brake, O = 1, ph8, np5000) as the reference runs it: shrinking horizon.  Step 1
+    #      (Tsh = 8) builds rows from the predictions and keeps their moments; step 2 (Tsh = 7, frame + 10) rolls
+    #      n_samples = 1e6 ideal trajectories per mode out of those moments (predict_ideal, v8ideal:2640) and builds
+    #      the rows from them.  Moments stay on the device (out_dir = None: no pickle I/O in the timed region).
+    sc1 = synth.make_scene(1, 1, 3, 8)
+    z1, pos1 = synth.sample_scene(sc1, 5000, 1)
+    pp = [np.ascontiguousarray(pos1[0][z1[0] == k]) for k in range(3)]
+    ov1 = [types.SimpleNamespace(pred_positions=pp, pred_yaws=[np.zeros(p.shape[:2]) for p in pp], n_states=3,
+                                 bbox=np.array([3.7, 1.79]))]
+    mc = midlevel.MidlevelConstraints(8, out_dir=None, device=dev)
+    t12, t2s = [], []
+    for i in range(3 + 20):
+        f = 100 + 20 * i
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        mc.compute_obstacle_constraints_GMM_Minkowski_idealprediction(types.SimpleNamespace(frame=f), ov1, Tsh=8,
+                                                                      ref_traj=sc1.ref_traj)
+        t1 = time.perf_counter()
+        b2 = mc.compute_obstacle_constraints_GMM_Minkowski_idealprediction(types.SimpleNamespace(frame=f + 10), ov1,
+                                                                           Tsh=7, ref_traj=sc1.ref_traj)
+        t2 = time.perf_counter()
+        if i >= 3:
+            t12.append((t2 - t0) * 1e3)
+            t2s.append((t2 - t1) * 1e3)
+    assert b2[0].n.shape[:2] == (3, 21) and not b2[0].status.any()
+    out["shrinking_horizon_c1"] = {
+        "metric": "mpc_step_latency_ms", "unit": "ms", "higher_is_better": False,
+        "p50_two_steps": float(np.percentile(t12, 50)), "p50_step2": float(np.percentile(t2s, 50)),
+        "p95_two_steps": float(np.percentile(t12, 95)),
+        "workload": "c1: O=1, K=3, ph8, np5000; step 1 Tsh=8 (rows from the predictions, moments kept on the device), "
+                    "step 2 Tsh=7 (predict_ideal: 3 cells x 1e6 Philox samples from the step-1 moments, rows from the "
+                    "ideal trajectories), through MidlevelConstraints, host objects in -> 9-tuple out"}
+    del mc, b2
+    # ---- CPU baselines of the two other metric terms (oracle port, 1 core; bounded samples)
+    if not args.skip_cpu:
+        from oracle import restate, restate_planner
+        cells = [[pos_c2[o][z[o] == k] for k in range(C2["K"])] for o in range(C2["O"])]
+        yaws = [[np.zeros(p.shape[:2]) for p in co] for co in cells]
+        t0 = time.perf_counter()
+        restate_planner.minkowski_step(cells, yaws, [np.array([3.7, 1.79])] * C2["O"], ref_traj,
+                                       restate.eps_allocation([C2["K"]] * C2["O"]), C2["T"], C2["T"])
+        c2_s = time.perf_counter() - t0
+        rngc = np.random.default_rng(4)
+        M = C4["S"] * C4["O"] * C4["T"] * C4["K"] // 256
+        cv = synth.sym_to_full(synth.random_spd(rngc, (M,)))
+        mu_c = np.stack([rngc.uniform(150, 200, M), rngc.uniform(-100, -60, M)], axis=1)
+        chi_c = -2.0 * np.log(0.05 / C4["O"] / C4["T"])
+        refp = synth.reference_trajectory(C4["T"])[0] + np.array([0.0, 30.0])
+        t0 = time.perf_counter()
+        for i in range(M):
+            _, Q = restate.mvoe(cv[i] * chi_c, np.identity(2) * restate.R_EV_OV ** 2)
+            m_ = -(refp[0] - mu_c[i, 0]) / (refp[1] - mu_c[i, 1])
+            restate.closest_tangent(mu_c[i], Q, 1, m_, refp)
+        c4_s = time.perf_counter() - t0
+        out["cpu_baselines"] = {
+            "kind": "port", "cores": 1, "c2_build_s": c2_s, "mvoe_fits_per_sec": M / c4_s,
+            "sample": f"c2: the whole step once through oracle/restate_planner.minkowski_step ({c2_s:.1f} s: 2800 pairs "
+                      f"x (np.cov, 2 x MVOE, tangent, lower bound) + L4 + save_moments); c4: 1/256 of the sweep = {M} "
+                      f"footprint fits + tangents through oracle/restate.py ({c4_s:.1f} s)"}
     # c2 from the predictor's output distribution: 25 latent states per obstacle (flat pmf, all kept), GMM2D
     # parameters H2D, sampling + grouping + the same Minkowski build on the device, rows D2H
     gpmf, gmus, gls, grho = synth.gmm2d_params(sc, Z=C2["K"])
@@ -792,6 +1006,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--n-per-cell", type=int, default=C3["n_per_cell"])
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: every rank rolls --n-per-cell samples per cell; strong: they are split over the ranks")
     ap.add_argument("--skip-cpu", action="store_true")
     ap.add_argument("--skip-also", action="store_true")
     args = ap.parse_args()

@@ -27,6 +27,17 @@ int check_launch(const char* what) {
     return CCMPC_OK;
 }
 
+int sm_count() {
+    static int n = 0;
+    if (n == 0) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess ||
+            cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+            n = 148;
+    }
+    return n;
+}
+
 }  // namespace ccmpc
 
 extern "C" int ccmpc_version(void) { return CCMPC_VERSION; }

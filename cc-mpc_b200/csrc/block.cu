@@ -74,7 +74,7 @@ extern "C" int ccmpc_halfplanes_to_block(const double* nd, int nd_stride, const 
                       "ccmpc_halfplanes_to_block: the control-space block needs gamma [nx T, ldg >= nu T], x_bar, u_bar");
     }
     if (rows == 0) return CCMPC_OK;
-    const unsigned grid = (unsigned)(rows < 148 * 16 ? rows : 148 * 16);
+    const unsigned grid = (unsigned)(rows < (int64_t)sm_count() * 16 ? rows : (int64_t)sm_count() * 16);
     halfplanes_block_kernel<<<grid, 64, 0, (cudaStream_t)stream>>>(nd, nd_stride, rhs, rhs_stride, idx_side, t_of_row,
                                                                    rows, T, nx, nu, A_u ? gamma : nullptr, ldg, x_bar,
                                                                    u_bar, A_x, b_x, A_u, b_u);

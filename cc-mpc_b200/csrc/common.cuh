@@ -17,6 +17,8 @@ namespace ccmpc {
 
 void set_error(const char* fmt, ...);
 int check_launch(const char* what);
+// multiprocessors of the current device (cudaDevAttrMultiProcessorCount, queried once; 148 on B200): launch sizing
+int sm_count();
 
 #define CCMPC_REQUIRE(cond, ...)                \
     do {                                        \

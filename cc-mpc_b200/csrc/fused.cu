@@ -408,17 +408,6 @@ __global__ void fused_finalize_kernel(const double* __restrict__ partials, const
     }
 }
 
-static int sm_count() {
-    static int n = 0;
-    if (n == 0) {
-        int dev = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess ||
-            cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
-            n = 148;
-    }
-    return n;
-}
-
 static int fused_grid(int64_t n, int64_t C) {
     const int64_t tt = C * ((n + 31) / 32);
     const int64_t g = tt < sm_count() ? tt : sm_count();

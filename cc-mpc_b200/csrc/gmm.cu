@@ -303,7 +303,7 @@ extern "C" int ccmpc_gmm2d_sample(const double* latent_pmf, const float* log_pis
     const int pairs = (T % 4 == 0) ? 2 : 1;            // 4 timesteps (32 contiguous bytes) per thread when possible
     const int TQ = (TP + pairs - 1) / pairs;
     int64_t blocks = (N * TQ + GMM_THREADS - 1) / GMM_THREADS;
-    const int64_t cap = (148 * 8 + V - 1) / V;        // ~8 resident CTAs per SM over all vehicles; grid-stride beyond
+    const int64_t cap = ((int64_t)sm_count() * 8 + V - 1) / V;        // ~8 resident CTAs per SM over all vehicles; grid-stride beyond
     if (blocks > cap) blocks = cap;
     dim3 grid((unsigned)blocks, (unsigned)V);
     GmmNoise noise{u_z, u_c, eps};
@@ -342,7 +342,7 @@ extern "C" int ccmpc_gmm2d_sample_dynamics(const double* latent_pmf, const float
     CCMPC_REQUIRE(!any || all, "ccmpc_gmm2d_sample_dynamics: supply u_z, u_c and eps together or none of them");
     const int TP = (T + 1) / 2;
     int64_t blocks = (N + DYN_THREADS - 1) / DYN_THREADS;
-    const int64_t cap = (148 * 8 + V - 1) / V;
+    const int64_t cap = ((int64_t)sm_count() * 8 + V - 1) / V;
     if (blocks > cap) blocks = cap;
     dim3 grid((unsigned)blocks, (unsigned)V);
     GmmNoise noise{u_z, u_c, eps};

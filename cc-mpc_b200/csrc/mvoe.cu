@@ -540,7 +540,7 @@ __global__ void affine_kernel(const double* __restrict__ sums, const double* __r
 
 static int fit_grid(int64_t M) {
     int64_t tiles = (M + FIT_THREADS - 1) / FIT_THREADS;
-    const int64_t cap = 148 * 4;   // 148 SMs x 4 resident 256-thread CTAs (58 registers)
+    const int64_t cap = (int64_t)sm_count() * 4;   // SMs x 4 resident 256-thread CTAs (58 registers)
     return (int)(tiles < cap ? (tiles > 0 ? tiles : 1) : cap);
 }
 
@@ -622,7 +622,7 @@ extern "C" int ccmpc_minkowski_halfplanes(const double* sums, const double* pivo
     size_t smem = (size_t)(2 * ((L.o_coll + 1) & ~1) + T + 3) * sizeof(double);
     MinkOut out{nd, ab, q, q1, betas, cov_infer, cov_mu, prob_pair, prob_lower, mean, idx_side, status};
     CCMPC_REQUIRE(((uintptr_t)sums & 15) == 0, "ccmpc_minkowski_halfplanes: sums must be 16-byte aligned");
-    const int64_t cap = 148 * 5;                  // persistent: 5 resident 128-thread blocks per SM (92 registers)
+    const int64_t cap = (int64_t)sm_count() * 5;                  // persistent: 5 resident 128-thread blocks per SM (92 registers)
     const unsigned grid = (unsigned)(C < cap ? C : cap);
     if (accel == 2)
         minkowski_kernel<true><<<grid, threads, smem, (cudaStream_t)stream>>>(

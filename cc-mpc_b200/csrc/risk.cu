@@ -138,7 +138,7 @@ __global__ void risk_finalize_kernel(const double* __restrict__ partial, int npa
 static int risk_grid_x(int64_t n, int64_t C) {
     // one wave: 148 SMs x RK_CTAS_PER_SM resident 128-thread CTAs, split evenly over the cells, never more than
     // the samples need
-    int64_t want = (148 * RK_CTAS_PER_SM) / C;
+    int64_t want = ((int64_t)sm_count() * RK_CTAS_PER_SM) / C;
     int64_t need = (n + RK_THREADS - 1) / RK_THREADS;
     int64_t g = want < need ? want : need;
     return (int)(g < 1 ? 1 : g);

@@ -152,7 +152,7 @@ extern "C" int ccmpc_mc_rollout(const double* mean, const double* cov, const dou
     const size_t smem = (size_t)Tsh * sizeof(StepParams) + (size_t)RO_THREADS * (((Tsh == 16 || Tsh == 8) ? RO_FLUSH : Tsh) | 1) * 16;
     // one wave: at most 148 * RO_MIN_CTAS resident CTAs over all cells, each looping over its cell's tiles
     const int64_t ntiles = (n + RO_THREADS - 1) / RO_THREADS;
-    const int64_t cap = std::max<int64_t>(1, (148 * RO_MIN_CTAS) / C);
+    const int64_t cap = std::max<int64_t>(1, ((int64_t)sm_count() * RO_MIN_CTAS) / C);
     dim3 grid((unsigned)std::min(ntiles, cap), (unsigned)C);
 #define CCMPC_RO_LAUNCH(TSH, ZI, ZO)                                                                          \
     rollout_kernel<TSH, ZI, ZO><<<grid, RO_THREADS, smem, st>>>(mean, cov, cross, Tm, x0, n, Tsh, (uint32_t)seed, \

@@ -448,7 +448,7 @@ static int64_t max_units(int64_t n_total, int64_t C, int slab) { return n_total 
 // n_total / slab + C units fit the 296 resident CTA slots, so the per-unit prologue / epilogue (~3.6 us: unit
 // lookup, pipeline fill, CTA reduction, partial vector) is paid once per CTA instead of 13 times.
 static int pick_slab(int64_t n_total, int64_t C) {
-    const int64_t slots = 148 * 2;
+    const int64_t slots = (int64_t)sm_count() * 2;
     if (C <= slots / 2) {
         const int64_t one_wave = ((n_total + (slots - C) - 1) / (slots - C) + 3) & ~(int64_t)3;
         if (one_wave >= SS_SLAB && one_wave < ((int64_t)1 << 24)) return (int)one_wave;

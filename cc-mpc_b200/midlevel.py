@@ -426,17 +426,7 @@ class MidlevelConstraints:
         n = self.n_ideal_samples if n_samples is None else int(n_samples)
         if moments.T < T + 1:
             raise InSimulationException(f"moments cover {moments.T} steps; predict_ideal indexes [t+1] up to {T}")
-        sel, co, ck = [], [], []
-        Kmax_saved = max(moments.n_states) if moments.n_states else 0
-        for o, K_o in enumerate(n_states):
-            for k in range(int(K_o)):
-                data_idx = k if k < Kmax_saved else max(Kmax_saved - 1, 0)        # v8ideal:2652-2656
-                hit = np.nonzero((moments.cell_obstacle == o) & (moments.cell_mode == data_idx))[0]
-                if hit.size == 0:
-                    raise InSimulationException(f"saved moments have no entry for obstacle {o} mode {data_idx}")
-                sel.append(int(hit[0]))
-                co.append(o)
-                ck.append(k)
+        sel, co, ck = self._select_cells(n_states, moments)
         idx = torch.as_tensor(sel, dtype=torch.int64, device=self.device)
         mean = moments.mean.index_select(0, idx).contiguous()
         cov = moments.cov.index_select(0, idx).contiguous()
@@ -647,7 +637,7 @@ class MidlevelConstraints:
     # ------------------------------------------------------ MC risk estimate
     def mc_collision_risk(self, moments: Moments, n_states, T: int, ego_xy, n_samples: Optional[int] = None,
                           seed: Optional[int] = None, sample_offset: Optional[int] = None, process_group=None,
-                          want_moments: bool = True, x0=None, z=None):
+                          want_moments: bool = True, x0=None, z=None, want_trajectories: bool = True):
         """Stage 1 of the path: rollout n samples per (o, k) cell from the moments, then ONE read of
         the trajectories -> collision counts (A9), soft cost and the shifted power sums; with a
         ``process_group`` the packed sums are all-reduced (sum) across sample shards.
@@ -666,17 +656,57 @@ class MidlevelConstraints:
                 import torch.distributed as dist
                 sample_offset, n = sharding.sample_shard(n, dist.get_rank(process_group),
                                                          dist.get_world_size(process_group))
-        cells = self.predict_ideal_cells(n_states, T, moments, n_samples=n, seed=seed,
-                                         sample_offset=sample_offset, x0=x0, z=z)
         # common pivot on every rank: the moment means x_{t+1} ~ mean[t+1]  
-        idx = [int(np.nonzero((moments.cell_obstacle == o) & (moments.cell_mode == min(k, max(moments.n_states) - 1)))[0][0])
-               for o, k in zip(cells.cell_obstacle, cells.cell_mode)]
-        pivot = moments.mean.index_select(0, torch.as_tensor(idx, device=self.device))[:, 1:T + 1].contiguous()
-        sums, _ = self._sums(cells, ego=ego_xy, pivot=pivot)
+        sel, co, ck = self._select_cells(n_states, moments)
+        idx = torch.as_tensor(sel, dtype=torch.int64, device=self.device)
+        pivot = moments.mean.index_select(0, idx)[:, 1:T + 1].contiguous()
+        if z is None and T in (8, 16) and moments.T >= T + 1:
+            # one kernel: rollout, trajectory store, counts and power sums (ccmpc_mc_rollout_sums)
+            mean = moments.mean.index_select(0, idx).contiguous()
+            cov = moments.cov.index_select(0, idx).contiguous()
+            cross = moments.cross.index_select(0, idx).contiguous()
+            if seed is None:
+                self._calls += 1
+                seed = (self.seed << 20) + self._calls
+            ego_t = _h2d(np.asarray(ego_xy, dtype=np.float64), self.device) if not torch.is_tensor(ego_xy) else ego_xy
+            x0_t = None if x0 is None else _h2d(np.asarray(x0, dtype=np.float64).reshape(len(sel), 2), self.device)
+            traj, sums, status, x0_used = ops.mc_rollout_sums(mean, cov, cross, x0_t, n, T, pivot, ego_t, R=self.R,
+                                                              seed=seed, sample_offset=sample_offset,
+                                                              materialize=want_trajectories,
+                                                              workspace=self._fused_ws(len(sel), n, T))
+            cells = CellBatch.uniform(traj, co, ck, n_states) if traj is not None else None
+        else:
+            cells = self.predict_ideal_cells(n_states, T, moments, n_samples=n, seed=seed,
+                                             sample_offset=sample_offset, x0=x0, z=z)
+            sums, _ = self._sums(cells, ego=ego_xy, pivot=pivot)
+            status = cells.status
         if process_group is not None:
             sharding.allreduce_sums(sums, group=process_group)
         mom = ops.moments_from_sums(sums, pivot, want_cross=want_moments, want_counts=True, want_yaw=False)
-        return dict(sums=sums, counts=mom["counts"], pivot=pivot, cells=cells, moments=mom)
+        return dict(sums=sums, counts=mom["counts"], pivot=pivot, cells=cells, moments=mom, status=status)
+
+    def _fused_ws(self, C: int, n: int, T: int) -> torch.Tensor:
+        key = (C, n, T)
+        if getattr(self, "_fused_ws_key", None) != key:
+            self._fused_ws_buf = ops.mc_rollout_sums_workspace(C, n, T, self.device)
+            self._fused_ws_key = key
+        return self._fused_ws_buf
+
+    def _select_cells(self, n_states: Sequence[int], moments: Moments):
+        """Rows of ``moments`` for the cells (o, k < K_o), with predict_ideal's fallback to the last saved mode
+        when K grew (v8ideal:2652-2656)."""
+        sel, co, ck = [], [], []
+        Kmax_saved = max(moments.n_states) if moments.n_states else 0
+        for o, K_o in enumerate(n_states):
+            for k in range(int(K_o)):
+                data_idx = k if k < Kmax_saved else max(Kmax_saved - 1, 0)        # v8ideal:2652-2656
+                hit = np.nonzero((moments.cell_obstacle == o) & (moments.cell_mode == data_idx))[0]
+                if hit.size == 0:
+                    raise InSimulationException(f"saved moments have no entry for obstacle {o} mode {data_idx}")
+                sel.append(int(hit[0]))
+                co.append(o)
+                ck.append(k)
+        return sel, co, ck
 
 
 class StepPlan:
