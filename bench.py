@@ -336,7 +336,7 @@ def run_ours(args):
     # ---- end-to-end through the planner-facing call (MidlevelConstraints.mc_collision_risk): the step's inputs
     #      come from pinned HOST memory (one H2D copy of the moment tensors + ego plan), the packed sums go back to
     #      the host (D2H) and the stream is synchronised, every step
-    mc = midlevel.MidlevelConstraints(T + 1, out_dir=None, device=dev)
+    mc = midlevel.MidlevelConstraints(T, out_dir=None, device=dev)
     m_, c_, x_, e_ = dev_views
     mom_obj = midlevel.Moments(m_, c_, x_, np.repeat(np.arange(O), K), np.tile(np.arange(K), O), [K] * O, T + 1)
 

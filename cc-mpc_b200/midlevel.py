@@ -90,11 +90,14 @@ def raise_for_status(status: np.ndarray, populated: Optional[np.ndarray] = None,
 
 
 def _h2d(arr: np.ndarray, device, dtype=None) -> torch.Tensor:
-    """Host ndarray -> device through a pinned staging buffer (async on the current stream)."""
+    """Host ndarray -> device on the current stream.  Small arrays go from pageable memory (the driver stages them;
+    pinning a fresh buffer per call costs more than the copy), large ones through a pinned buffer."""
     t = torch.from_numpy(np.ascontiguousarray(arr))
     if dtype is not None and t.dtype != dtype:
         t = t.to(dtype)
-    return t.pin_memory().to(device, non_blocking=True)
+    if t.numel() * t.element_size() >= (16 << 20):
+        t = t.pin_memory()
+    return t.to(device, non_blocking=True)
 
 
 @dataclass
@@ -427,10 +430,7 @@ class MidlevelConstraints:
         if moments.T < T + 1:
             raise InSimulationException(f"moments cover {moments.T} steps; predict_ideal indexes [t+1] up to {T}")
         sel, co, ck = self._select_cells(n_states, moments)
-        idx = torch.as_tensor(sel, dtype=torch.int64, device=self.device)
-        mean = moments.mean.index_select(0, idx).contiguous()
-        cov = moments.cov.index_select(0, idx).contiguous()
-        cross = moments.cross.index_select(0, idx).contiguous()
+        mean, cov, cross = self._gather(moments, sel)
         x0_t = None if x0 is None else _h2d(np.asarray(x0, dtype=np.float64).reshape(len(sel), 2), self.device)
         if seed is None:
             self._calls += 1
@@ -658,13 +658,10 @@ class MidlevelConstraints:
                                                          dist.get_world_size(process_group))
         # common pivot on every rank: the moment means x_{t+1} ~ mean[t+1]  
         sel, co, ck = self._select_cells(n_states, moments)
-        idx = torch.as_tensor(sel, dtype=torch.int64, device=self.device)
-        pivot = moments.mean.index_select(0, idx)[:, 1:T + 1].contiguous()
+        mean, cov, cross = self._gather(moments, sel)
+        pivot = mean[:, 1:T + 1].contiguous()
         if z is None and T in (8, 16) and moments.T >= T + 1:
             # one kernel: rollout, trajectory store, counts and power sums (ccmpc_mc_rollout_sums)
-            mean = moments.mean.index_select(0, idx).contiguous()
-            cov = moments.cov.index_select(0, idx).contiguous()
-            cross = moments.cross.index_select(0, idx).contiguous()
             if seed is None:
                 self._calls += 1
                 seed = (self.seed << 20) + self._calls
@@ -695,6 +692,10 @@ class MidlevelConstraints:
     def _select_cells(self, n_states: Sequence[int], moments: Moments):
         """Rows of ``moments`` for the cells (o, k < K_o), with predict_ideal's fallback to the last saved mode
         when K grew (v8ideal:2652-2656)."""
+        key = tuple(int(k) for k in n_states)
+        cache = getattr(moments, "_sel_cache", None)
+        if cache is not None and cache[0] == key:
+            return cache[1]
         sel, co, ck = [], [], []
         Kmax_saved = max(moments.n_states) if moments.n_states else 0
         for o, K_o in enumerate(n_states):
@@ -706,7 +707,16 @@ class MidlevelConstraints:
                 sel.append(int(hit[0]))
                 co.append(o)
                 ck.append(k)
+        moments._sel_cache = (key, (sel, co, ck))
         return sel, co, ck
+
+    def _gather(self, moments: Moments, sel):
+        """(mean, cov, cross) rows ``sel`` of the moments; the tensors themselves when that is every row in order."""
+        if sel == list(range(moments.mean.shape[0])):
+            return moments.mean, moments.cov, moments.cross
+        idx = torch.as_tensor(sel, dtype=torch.int64, device=self.device)
+        return (moments.mean.index_select(0, idx).contiguous(), moments.cov.index_select(0, idx).contiguous(),
+                moments.cross.index_select(0, idx).contiguous())
 
 
 class StepPlan:
