@@ -388,12 +388,22 @@ __global__ void fused_finalize_kernel(const double* __restrict__ partials, const
                                       int G, int T, const double* __restrict__ pivot, const double* __restrict__ ego,
                                       int64_t ego_cell_stride, double* __restrict__ sums) {
     extern __shared__ double s_sum[];
+    __shared__ int s_list[256], s_cnt;                  // the cell's slots, ascending (G <= 256 SMs)
     const SumsLayout L(T);
     const int64_t c = blockIdx.x;
+    for (int g = threadIdx.x; g < G; g += blockDim.x) s_list[g] = slot_cell[c + g] == (int32_t)c ? 1 : 0;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int k = 0;
+        for (int g = 0; g < G; ++g)
+            if (s_list[g]) s_list[k++] = g;
+        s_cnt = k;
+    }
+    __syncthreads();
+    const int cnt = s_cnt;
     for (int j = threadIdx.x; j < L.len; j += blockDim.x) {
         double s = 0.0;
-        for (int g = 0; g < G; ++g)
-            if (slot_cell[c + g] == (int32_t)c) s += partials[(c + g) * (int64_t)L.len + j];
+        for (int k = 0; k < cnt; ++k) s += partials[(c + s_list[k]) * (int64_t)L.len + j];
         s_sum[j] = s;
     }
     __syncthreads();
@@ -410,7 +420,8 @@ __global__ void fused_finalize_kernel(const double* __restrict__ partials, const
 
 static int fused_grid(int64_t n, int64_t C) {
     const int64_t tt = C * ((n + 31) / 32);
-    const int64_t g = tt < sm_count() ? tt : sm_count();
+    const int64_t sms = sm_count() < 256 ? sm_count() : 256;        // fused_finalize_kernel lists at most 256 slots
+    const int64_t g = tt < sms ? tt : sms;
     return (int)(g < 1 ? 1 : g);
 }
 
