@@ -432,6 +432,8 @@ def _summary(value, ms_step, e2e_value, roofline, also, cpu):
         "mc_frac_hbm": roofline["frac"], "mc_frac_fp64_pipe": roofline["fp64_pipe"]["frac"],
         "mc_two_kernel_ms": g("mc_step_two_kernels", "ms"), "mc_risk_only_ms": g("mc_risk_fused", "ms"),
         "mvoe_fits_per_sec_ref_seq": g("mvoe_sweep", "value"), "mvoe_frac_hbm_ref_seq": r("mvoe_sweep"),
+        "mvoe_fits_per_sec_ref_map_warm_start": g("mvoe_sweep_accel", "value"),
+        "mvoe_frac_hbm_ref_map_warm_start": r("mvoe_sweep_accel"),
         "mvoe_fits_per_sec_direct": g("mvoe_sweep_direct", "value"), "mvoe_frac_hbm_direct": r("mvoe_sweep_direct"),
         "mvoe_full_minkowski_fits_per_sec_ref_seq": g("mvoe_minkowski_full", "value"),
         "mvoe_full_minkowski_fits_per_sec_direct": g("mvoe_minkowski_full_direct", "value"),
@@ -621,7 +623,9 @@ def bench_also(torch, ops, midlevel, synth, dev, args, world=1, rank=0, dist=Non
             "metric": "mvoe_fits_per_sec", "value": M / (ms * 1e-3), "unit": "fits/s", "ms": ms, "fits": M,
             "workload": f"c4: S={S} x O={O} x T={T} x K={K} footprint fit + tangent half-plane per GPU "
                         f"(scenarios sharded x{world}, no exchange)", "n_gpus": world,
-            "iterate": ("reference sequence from beta = 1", "float32 warm start + fp64 map",
+            "iterate": ("reference sequence from beta = 1 (same iterates, same iteration count)",
+                        "reference map and stopping rule (|delta beta| < 1e-8) started from a float32 solve of the "
+                        "stationarity cubic instead of beta = 1",
                         "Newton on the stationarity cubic, accepted by one reference-map step at tol 1e-8")[accel],
             "roofline": {"bound": "hbm", "achieved": M / world * bytes_per / (ms * 1e-3) / 1e9, "peak": peak,
                          "unit": "GB/s", "frac": M / world * bytes_per / (ms * 1e-3) / 1e9 / peak,

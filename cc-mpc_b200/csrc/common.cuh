@@ -143,6 +143,27 @@ __device__ __forceinline__ float rsqrt_approx_f32(float x) {
 // evaluation of the reference map, accepted under the reference's own rule |F(b) - b| < tol.
 // Returns F(b) and 1/F(b) (both ~1 ulp: a rsqrt(ab) and b rsqrt(ab)), or -1 when the rule fails
 // (the caller then runs the reference sequence from beta = 1).  MUFU-only float32: no IEEE slow paths.
+// float32 estimate of the fixed point: seed det^(-1/4) (exact when lam_1 = lam_2), two map steps (exact in both
+// limits det -> 0, inf), three Newton steps on the stationarity cubic.  ~1e-6 relative.
+__device__ __forceinline__ float mvoe_beta_seed_f32(double tr, double dt2) {
+    const float trf = (float)tr, dtf = (float)dt2;
+    float b = rsqrt_approx_f32(0.5f * dtf);
+    b = b * rsqrt_approx_f32(b);                   // sqrt(rsqrt(dt)) = dt^-1/4
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        const float num = fmaf(b, trf, 2.0f), den = fmaf(b, dtf, trf);
+        b = num * rsqrt_approx_f32(num * den);
+    }
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float g = fmaf(fmaf(fmaf(dtf, b, trf), b, -trf), b, -2.0f);
+        const float gp = fmaf(fmaf(3.0f * dtf, b, 2.0f * trf), b, -trf);
+        const float nb = fmaf(-g, rcp_approx_f32(gp), b);
+        b = (gp > 0.0f && nb > 0.0f) ? nb : b;
+    }
+    return b;
+}
+
 __device__ __forceinline__ double mvoe_beta_direct(double tr, double dt2, double tol, double& inv_beta) {
     const float trf = (float)tr, dtf = (float)dt2;
     float b = rsqrt_approx_f32(0.5f * dtf);
@@ -186,15 +207,9 @@ __device__ __forceinline__ double mvoe_beta(const MvoeSpectrum& sp, double tol, 
     const double tr = sp.tr, dt2 = 2.0 * sp.dt;
     int it = 0;
     if (accel == 1) {
-        // float32 warm start: same map, stopped at a float-level tolerance.
-        float b = 1.0f;
-        const float trf = (float)tr, dtf = (float)dt2;
-        for (int k = 0; k < 64; ++k) {
-            float nb = sqrtf(__fdividef(fmaf(b, trf, 2.0f), fmaf(b, dtf, trf)));
-            bool close = fabsf(nb - b) < 1e-5f * nb;
-            b = nb;
-            if (close) break;
-        }
+        // the reference's map and stopping rule, started next to the fixed point instead of at 1: a float32 solve of
+        // the stationarity cubic (~1e-6 relative), then the fp64 loop below to |delta| < tol (2-4 iterations)
+        const float b = mvoe_beta_seed_f32(tr, dt2);
         if (isfinite(b) && b > 0.0f) beta = (double)b;
     }
     if (accel == 2 && maxiter > 0) {

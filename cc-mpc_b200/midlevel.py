@@ -54,8 +54,9 @@ def eps_allocation(K_per_obstacle: Sequence[int], eps: float = EPS_TOTAL) -> np.
 
 
 def _accel_mode(accel) -> int:
-    """0: the reference's iterate sequence (makeconstraint:24-32); 1: float32 warm start, same fp64 map and
-    stopping rule; 2: direct solve of the stationarity cubic accepted under the reference's rule."""
+    """0: the reference's iterate sequence from beta = 1 (makeconstraint:24-32; same iterates, same count);
+    1: the same fp64 map and stopping rule started from a float32 solve of the stationarity cubic (2-4 iterations);
+    2: fp64 Newton on the cubic, accepted by one evaluation of the reference map under its stopping rule."""
     a = int(accel)
     if a not in (0, 1, 2) or (not isinstance(accel, (bool, int, np.integer))):
         raise ValueError(f"accel must be 0, 1 or 2 (got {accel!r})")
