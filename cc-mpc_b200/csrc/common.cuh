@@ -8,6 +8,7 @@
 #pragma once
 
 #include <cuda_runtime.h>
+#include <initializer_list>
 #include <stdint.h>
 #include <stdio.h>
 
@@ -27,6 +28,15 @@ int sm_count();
             return CCMPC_E_ARG;                 \
         }                                       \
     } while (0)
+
+// every pointer the kernels move as double2 / float4 / 16-byte staged records: a misaligned address would fault,
+// and a CUDA fault is sticky (it takes the planner's whole context with it)
+#define CCMPC_ALIGNED16(...) ccmpc::all_aligned16({__VA_ARGS__})
+inline bool all_aligned16(std::initializer_list<const void*> ps) {
+    for (const void* p : ps)
+        if (reinterpret_cast<uintptr_t>(p) & 15) return false;
+    return true;
+}
 
 struct Sym2 {
     double xx, xy, yy;

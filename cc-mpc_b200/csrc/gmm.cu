@@ -296,6 +296,7 @@ extern "C" int ccmpc_gmm2d_sample(const double* latent_pmf, const float* log_pis
     CCMPC_REQUIRE(Z <= 4096 && V <= 65535, "ccmpc_gmm2d_sample: need Z <= 4096 and V <= 65535");
     if (V == 0 || N == 0) return CCMPC_OK;
     CCMPC_REQUIRE(latent_pmf && mus && log_sigmas && corrs && predictions, "ccmpc_gmm2d_sample: null pointer");
+    CCMPC_REQUIRE(CCMPC_ALIGNED16(predictions), "ccmpc_gmm2d_sample: predictions must be 16-byte aligned");
     CCMPC_REQUIRE(G == 1 || log_pis, "ccmpc_gmm2d_sample: G > 1 needs log_pis");
     const bool any = u_z || u_c || eps, all = u_z && u_c && eps;
     CCMPC_REQUIRE(!any || all, "ccmpc_gmm2d_sample: supply u_z, u_c and eps together or none of them");

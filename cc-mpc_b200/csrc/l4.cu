@@ -136,6 +136,7 @@ extern "C" int ccmpc_l4_outer(const double* samples, const double* yaws, const i
                               double* At, double* b0, void* stream) {
     CCMPC_REQUIRE(T >= 1 && T <= CCMPC_MAX_T && C >= 0 && n_total >= 0, "ccmpc_l4_outer: bad dims");
     CCMPC_REQUIRE(samples && yaws && offsets && yaw_mean && At && b0, "ccmpc_l4_outer: null pointer");
+    CCMPC_REQUIRE(CCMPC_ALIGNED16(samples), "ccmpc_l4_outer: samples must be 16-byte aligned");
     if (C == 0) return CCMPC_OK;
     cudaStream_t st = (cudaStream_t)stream;
     // 0xFF bytes = the identity of atomic_max_double (see common.cuh)

@@ -555,6 +555,7 @@ extern "C" int ccmpc_mvoe_fit(const double* sigma1, const double* sigma2, double
     CCMPC_REQUIRE(maxiter >= 0, "ccmpc_mvoe_fit: maxiter < 0");
     if (M == 0) return CCMPC_OK;
     CCMPC_REQUIRE(sigma1 && beta && q, "ccmpc_mvoe_fit: null sigma1/beta/q");
+    CCMPC_REQUIRE(CCMPC_ALIGNED16(sigma1, sigma2, q), "ccmpc_mvoe_fit: sigma1 / sigma2 / q must be 16-byte aligned");
     cudaStream_t st = (cudaStream_t)stream;
     if (sigma2) {
         mvoe_fit_kernel<false><<<fit_grid(M), FIT_THREADS, 0, st>>>(sigma1, sigma2, 0.0, M, tol, maxiter, accel,
@@ -574,6 +575,7 @@ extern "C" int ccmpc_mvoe_halfplane_sweep(const double* cov, const double* mu, c
     const int64_t M = S * O * T * K;
     if (M == 0) return CCMPC_OK;
     CCMPC_REQUIRE(cov && mu && ref && q && nd && idx_side, "ccmpc_mvoe_halfplane_sweep: null pointer");
+    CCMPC_REQUIRE(CCMPC_ALIGNED16(cov, mu, ref, q, nd), "ccmpc_mvoe_halfplane_sweep: cov / mu / ref / q / nd must be 16-byte aligned");
     CCMPC_REQUIRE((int64_t)O * T * K < ((int64_t)1 << 31) - FIT_THREADS, "ccmpc_mvoe_halfplane_sweep: O*T*K too large");
     sweep_kernel<<<fit_grid(M), FIT_THREADS, 0, (cudaStream_t)stream>>>(
         cov, mu, ref, M, make_fastdiv((uint32_t)((int64_t)O * T * K)), make_fastdiv((uint32_t)K),

@@ -162,6 +162,7 @@ extern "C" int ccmpc_mc_risk(const double* mean, const double* cov, const double
     CCMPC_REQUIRE(C >= 0 && n >= 0 && C < 65536, "ccmpc_mc_risk: bad C / n");
     if (C == 0) return CCMPC_OK;
     CCMPC_REQUIRE(mean && cov && cross && ego && risk, "ccmpc_mc_risk: null pointer");
+    CCMPC_REQUIRE(CCMPC_ALIGNED16(ego), "ccmpc_mc_risk: ego must be 16-byte aligned");
     CCMPC_REQUIRE(ego_cell_stride == 0 || ego_cell_stride == 2 * Tsh, "ccmpc_mc_risk: ego stride must be 0 or 2 Tsh");
     cudaStream_t st = (cudaStream_t)stream;
     const int L = 3 * Tsh + 2;

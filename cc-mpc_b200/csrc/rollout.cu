@@ -143,6 +143,7 @@ extern "C" int ccmpc_mc_rollout(const double* mean, const double* cov, const dou
     CCMPC_REQUIRE(Tm >= Tsh + 1, "ccmpc_mc_rollout: moments must cover Tsh + 1 steps (Tm = %d, Tsh = %d)", Tm, Tsh);
     CCMPC_REQUIRE(C >= 0 && n >= 0 && C < 65536, "ccmpc_mc_rollout: bad C / n");
     CCMPC_REQUIRE(mean && cov && cross && traj, "ccmpc_mc_rollout: null pointer");
+    CCMPC_REQUIRE(CCMPC_ALIGNED16(traj, z, z_out), "ccmpc_mc_rollout: traj / z / z_out must be 16-byte aligned");
     if (C == 0 || n == 0) return CCMPC_OK;
     cudaStream_t st = (cudaStream_t)stream;
     if (status) {

@@ -536,6 +536,7 @@ extern "C" int ccmpc_violation_counts(const double* samples, const int64_t* offs
                                       void* stream) {
     CCMPC_REQUIRE(T >= 1 && T <= CCMPC_MAX_T && C >= 0 && n_total >= 0, "ccmpc_violation_counts: bad dims");
     CCMPC_REQUIRE(offsets && nd && idx_side && viol, "ccmpc_violation_counts: null pointer");
+    CCMPC_REQUIRE(CCMPC_ALIGNED16(samples), "ccmpc_violation_counts: samples must be 16-byte aligned");
     const int P = T * (T - 1) / 2;
     if (C == 0 || P == 0) return CCMPC_OK;
     cudaStream_t st = (cudaStream_t)stream;

@@ -312,7 +312,7 @@ class MidlevelConstraints:
     def __init__(self, prediction_horizon: int, ego_vehicle_id: int = 0, out_dir: Optional[str] = "out/data",
                  device=None, R: float = ops.R_EV_OV, target_p: float = ops.TARGET_P,
                  n_ideal_samples: int = N_IDEAL_SAMPLES, seed: int = 0, accel: int = 0,
-                 frame_stride: int = 10):
+                 frame_stride: int = 10, road_boundary_constraints: bool = False):
         if not 1 <= prediction_horizon <= ops.MAX_T:
             raise ValueError(f"prediction_horizon must be in 1..{ops.MAX_T}")
         self.accel = _accel_mode(accel)
@@ -325,6 +325,9 @@ class MidlevelConstraints:
         self.n_ideal_samples = int(n_ideal_samples)
         self.seed = int(seed)
         self.frame_stride = int(frame_stride)          # predict_ideal reads frame - 10 (v8ideal:2626)
+        # the reference's flag (v8ideal:797, :1395): with it set every row carries the road-boundary slack
+        # S_big_repeated[0, t], a cvxpy variable that lives in the solver - the builders refuse instead of dropping it
+        self.road_boundary_constraints = bool(road_boundary_constraints)
         self._moments: Dict[int, Moments] = {}
         self._calls = 0
         self.prob_lower_save = None
@@ -549,7 +552,7 @@ class MidlevelConstraints:
             eps_ura = eps_allocation(cells.n_states)
         if cells.T != Tpred:
             raise ValueError(f"cells carry horizon {cells.T}; the planner's prediction_horizon is {Tpred}")
-        if getattr(self, "road_boundary_constraints", False) and (Omicron is not None or segments is not None):
+        if self.road_boundary_constraints:
             raise NotImplementedError("road-boundary slack S_big (v8ideal:797-818) is not part of this path")
         # sums of the raw predictions: L4 polytopes, [tau+1|tau] bookkeeping, and the rows when T == Tpred
         if T < Tpred:
@@ -604,7 +607,7 @@ class MidlevelConstraints:
             eps_ura = eps_allocation(cells.n_states)
         if cells.T != Tpred:
             raise ValueError(f"cells carry horizon {cells.T}; the planner's prediction_horizon is {Tpred}")
-        if getattr(self, "road_boundary_constraints", False) and (Omicron is not None or segments is not None):
+        if self.road_boundary_constraints:
             # the reference adds the slack S_big_repeated[0, t] to every row here (:1505, :1511)
             raise NotImplementedError("road-boundary slack S_big (v8ideal:1395-1416) is not part of this path")
         ref_np = np.zeros((Tpred, 2))

@@ -166,6 +166,12 @@ def test_error_convention_argument_checks():
     assert rc == -3 and "workspace" in _lib.last_error()                     # CCMPC_E_WORKSPACE
     with pytest.raises(_lib.CcmpcError, match="workspace"):
         _lib.check(rc, "ccmpc_sample_sums")
+    # 16-byte alignment of vector-accessed pointers is checked before anything is launched (a misaligned address
+    # would be a sticky CUDA fault)
+    rc = lib.ccmpc_mvoe_fit(p + 8, None, 11.56, 4, 1e-8, 1000, 0, p, p, None, None, None)
+    assert rc == -1 and "aligned" in _lib.last_error()
+    rc = lib.ccmpc_mc_rollout(p, p, p, 9, None, 1, 4, 8, 0, 0, None, p + 8, None, None, None, None)
+    assert rc == -1 and "aligned" in _lib.last_error()
     # empty problems are accepted without touching the device
     assert lib.ccmpc_gmm2d_sample(None, None, None, None, None, 0, 0, 1, 1, 1, 0, None, 0, None, None, None, None,
                                   None, None) == 0

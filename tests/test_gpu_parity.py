@@ -957,3 +957,50 @@ def test_step_plan_sampler_mode_with_unicycle_dynamics(dev):
         prev = res
     with pytest.raises(ValueError):
         midlevel.StepPlan.from_gmm(V, N, T, pos_last, prediction_horizon=T, Z=Z).run_gmm(pmf, mus, ls, rho, ref_traj=ref, x0=x0)
+
+
+@pytest.mark.parametrize("Tsh", [16, 8])
+def test_mc_rollout_sums_is_independent_of_the_world_size(dev, Tsh):
+    """Eight sample shards (sharding.sample_shard, Philox counter = global sample index) rolled out and reduced
+    separately, packed sums added: counts bit-exact and trajectories identical to the one-shard launch, power sums
+    equal to round-off - what the NCCL all-reduce of the packed sums relies on at 2, 4 and 8 GPUs.  Also: more
+    cells than SMs and a cell boundary inside a CTA's share of the tile list (the kernel's cross-cell split)."""
+    from ccmpc_b200 import ops, sharding
+    O, K = 3, 2
+    sc, mean, cov, cross = _scene_moments(12, O, K, Tsh + 1)
+    C, n = O * K, 9973                                    # prime: ragged shards, partial last tiles
+    rng = np.random.default_rng(4)
+    ego = mean[:, 1:Tsh + 1] + rng.normal(size=(C, Tsh, 2)) * 1.5
+    args = (T_(mean, dev), T_(cov, dev), T_(cross, dev))
+    pivot, ego_t = T_(mean[:, 1:Tsh + 1], dev), T_(ego, dev)
+    traj, whole, st, x0 = ops.mc_rollout_sums(*args, None, n, Tsh, pivot, ego_t, seed=5)
+    assert not st.any()
+    L = ops.sums_layout(Tsh)
+    for world in (2, 8):
+        total = torch.zeros_like(whole)
+        parts = []
+        for rank in range(world):
+            lo, nl = sharding.sample_shard(n, rank, world)
+            t_r, s_r, _, x0_r = ops.mc_rollout_sums(*args, None, nl, Tsh, pivot, ego_t, seed=5, sample_offset=lo)
+            assert torch.equal(x0_r, x0)                  # the one x0 draw per cell does not depend on the shard
+            total += s_r
+            parts.append(t_r)
+        assert torch.equal(torch.cat(parts, dim=1), traj)
+        w, s = whole.cpu().numpy(), total.cpu().numpy()
+        np.testing.assert_array_equal(s[:, 0], w[:, 0])
+        np.testing.assert_array_equal(s[:, L["coll"]:L["pen"]], w[:, L["coll"]:L["pen"]])
+        np.testing.assert_allclose(s[:, :L["coll"]], w[:, :L["coll"]], rtol=1e-10, atol=1e-7)
+        np.testing.assert_allclose(s[:, L["pen"]:L["d2s"]], w[:, L["pen"]:L["d2s"]], rtol=1e-10, atol=1e-9)
+    # many small cells: several cells per CTA
+    Cm = 200
+    idx = np.arange(Cm) % C
+    big = tuple(T_(a[idx], dev) for a in (mean, cov, cross))
+    _, sums_m, st_m, _ = ops.mc_rollout_sums(*big, T_(x0.cpu().numpy()[idx], dev), 70, Tsh, T_(mean[idx, 1:Tsh + 1], dev),
+                                             T_(ego[idx], dev), seed=5, materialize=False)
+    _, sums_1, _, _ = ops.mc_rollout_sums(*args, x0, 70, Tsh, pivot, ego_t, seed=5, materialize=False)
+    # cell index enters the Philox counter, so copies of a cell at other indices draw other samples: compare the
+    # cells that sit at their own index, and the sample counts of all
+    a, b = sums_m[:C].cpu().numpy(), sums_1.cpu().numpy()
+    np.testing.assert_array_equal(a[:, L["coll"]:L["pen"]], b[:, L["coll"]:L["pen"]])     # counts: exact
+    np.testing.assert_allclose(a, b, rtol=1e-10, atol=1e-8)                                # sums: other partition
+    assert (sums_m[:, 0] == 70).all() and not st_m.any()
