@@ -53,6 +53,32 @@ def eps_allocation(K_per_obstacle: Sequence[int], eps: float = EPS_TOTAL) -> np.
     return out
 
 
+def _to_host(tensors: Dict[str, torch.Tensor]) -> Dict[str, np.ndarray]:
+    """Small device results -> host with ONE synchronising copy (a `.cpu()` per tensor is a stream sync each)."""
+    names = [k for k, v in tensors.items() if v is not None]
+    if not names:
+        return {}
+    flat = [tensors[k].contiguous().view(torch.uint8).reshape(-1) for k in names]
+    sizes = [int(f.numel()) for f in flat]
+    pad = [(-n) % 16 for n in sizes]                       # keep every piece 16-byte aligned for the dtype views
+    pieces = []
+    for f, p in zip(flat, pad):
+        pieces.append(f)
+        if p:
+            pieces.append(torch.zeros(p, dtype=torch.uint8, device=f.device))
+    host = torch.cat(pieces).cpu().numpy()
+    out, off = {}, 0
+    for k, n, p in zip(names, sizes, pad):
+        t = tensors[k]
+        out[k] = host[off:off + n].view(_NP_OF[t.dtype]).reshape(tuple(t.shape))
+        off += n + p
+    return out
+
+
+_NP_OF = {torch.float64: np.float64, torch.float32: np.float32, torch.int64: np.int64, torch.int32: np.int32,
+          torch.int8: np.int8, torch.uint8: np.uint8}
+
+
 def _accel_mode(accel) -> int:
     """0: the reference's iterate sequence from beta = 1 (makeconstraint:24-32; same iterates, same count);
     1: the same fp64 map and stopping rule started from a float32 solve of the stationarity cubic (2-4 iterations);
@@ -490,6 +516,11 @@ class MidlevelConstraints:
     def _nested_tko(cells: CellBatch, arr: np.ndarray, T: int):
         """[C, T, ...] -> nested list [t][k][o] sized (T, max K, O) (v8ideal:631, :714-716)."""
         O, Kmax = cells.O, max(cells.n_states)
+        if cells.C == O * Kmax and min(cells.n_states) == Kmax:
+            # every obstacle has Kmax modes, cells obstacle-major: [C, T, ...] -> [T, K, O, ...] views, no Python
+            # loop over the cells (100 x 8 assignments at c2)
+            tko = np.moveaxis(arr.reshape((O, Kmax) + arr.shape[1:]), (0, 1, 2), (2, 1, 0))
+            return [[list(tko[t, k]) for k in range(Kmax)] for t in range(T)]
         out = np.empty((T, Kmax, O), dtype=object).tolist()
         for c, (o, k) in enumerate(zip(cells.cell_obstacle, cells.cell_mode)):
             for t in range(T):
@@ -505,11 +536,8 @@ class MidlevelConstraints:
         return out
 
     def _ov_state(self, cells: CellBatch, mom: dict):
-        """ovStateMean_tau_1 / ovStateCov_tau_1 tuples (v8ideal:871-876)."""
-        mean = mom["mean"].cpu().numpy()
-        cov = mom["cov"].cpu().numpy()
-        ym = mom["yaw_mean"].cpu().numpy()
-        yv = mom["yaw_var"].cpu().numpy()
+        """ovStateMean_tau_1 / ovStateCov_tau_1 tuples (v8ideal:871-876); ``mom``: host arrays (_mean, ...)."""
+        mean, cov, ym, yv = mom["_mean"], mom["_cov"], mom["_yaw_mean"], mom["_yaw_var"]
         f = lambda v: self._nested_ok(cells, v)
         ov_mean = (f(mean[:, 0, 0]), f(mean[:, 0, 1]), f(ym[:, 0]))
         ov_cov = (f(cov[:, 0, 0, 0]), f(cov[:, 0, 1, 1]), f(yv[:, 0]))
@@ -567,11 +595,13 @@ class MidlevelConstraints:
         At, b0, mom = self._l4(cells, sums_c, pivot_c)                               # :951-954
         moments = self.moments_of(work, sums_w, pivot_w)
         # ---- one synchronising copy of the small results
-        host = {k: v.cpu().numpy() for k, v in out.items()}
+        allh = _to_host({**out, "_At": At, "_b0": b0, "_mean": mom["mean"], "_cov": mom["cov"],
+                         "_yaw_mean": mom["yaw_mean"], "_yaw_var": mom["yaw_var"]})
+        host = {k: v for k, v in allh.items() if not k.startswith("_")}
         raise_for_status(host["status"], what="Minkowski builder")                   # :907, :924-926
-        A_union = self._nested_tko(cells, At.cpu().numpy(), Tpred)
-        b_union = self._nested_tko(cells, b0.cpu().numpy(), Tpred)
-        ov_mean, ov_cov, inj = self._ov_state(cells, mom)
+        A_union = self._nested_tko(cells, allh["_At"], Tpred)
+        b_union = self._nested_tko(cells, allh["_b0"], Tpred)
+        ov_mean, ov_cov, inj = self._ov_state(cells, allh)
         OVconstraint = any(bool(v) for v in inj)                                     # :849-851
         direct = [None] * cells.O
         side = np.where(host["idx_side"] & 2, -1, 1).astype(np.int32)
@@ -617,11 +647,13 @@ class MidlevelConstraints:
         out = ops.affine_halfplanes(sums, pivot, _h2d(ref_np, self.device), self._eps_cells(cells, eps_ura), Tpred,
                                     R=self.R)
         At, b0, mom = self._l4(cells, sums, pivot)
-        host = {k: v.cpu().numpy()[:, :T] for k, v in out.items()}
+        allh = _to_host({**out, "_At": At, "_b0": b0, "_mean": mom["mean"], "_cov": mom["cov"],
+                         "_yaw_mean": mom["yaw_mean"], "_yaw_var": mom["yaw_var"]})
+        host = {k: v[:, :T] for k, v in allh.items() if not k.startswith("_")}
         raise_for_status(host["status"], what="affine builder")                       # :1499-1503
-        A_union = self._nested_tko(cells, At.cpu().numpy(), Tpred)
-        b_union = self._nested_tko(cells, b0.cpu().numpy(), Tpred)
-        ov_mean, ov_cov, _ = self._ov_state(cells, mom)
+        A_union = self._nested_tko(cells, allh["_At"], Tpred)
+        b_union = self._nested_tko(cells, allh["_b0"], Tpred)
+        ov_mean, ov_cov, _ = self._ov_state(cells, allh)
         side = np.where(host["idx_side"] & 2, -1, 1).astype(np.int32)
         C = side.shape[0]
         t_rows = np.broadcast_to(np.arange(T, dtype=np.int32), (C, T)).copy()
