@@ -446,6 +446,7 @@ def _summary(value, ms_step, e2e_value, roofline, also, cpu):
         "c1_step2_p50_ms": g("shrinking_horizon_c1", "p50_step2"),
         "c5_p50_ms": g("replay_c5_sampler", "p50_host_to_host"),
         "strong_scaling_ms": g("mc_strong_scaling", "ms"), "strong_scaling_traj_steps_per_sec": g("mc_strong_scaling", "value"),
+        "strong_scaling_overlapped_ms": g("mc_strong_scaling", "ms_overlapped"),
         "cpu_mc_traj_steps_per_sec_1core": (cpu or {}).get("value"),
         "cpu_c2_build_s": g("cpu_baselines", "c2_build_s"), "cpu_mvoe_fits_per_sec_1core": g("cpu_baselines", "mvoe_fits_per_sec"),
     }
@@ -558,32 +559,72 @@ def bench_also(torch, ops, midlevel, synth, dev, args, world=1, rank=0, dist=Non
         wss = ops.mc_rollout_sums_workspace(C3c, nl, T3, dev)
         trs = traj3.view(-1)[:C3c * nl * T3 * 2].view(C3c, nl, T3, 2)
 
-        def strong_step(i):
-            nonlocal mom3
+        def strong_step(i, sums_buf, mom_buf):
             ops.mc_rollout_sums(m3, c3, x3, None, nl, T3, piv3, ego3, seed=1234 + i, sample_offset=lo, workspace=wss,
-                                out=trs, sums_out=sums3)
-            dist.all_reduce(sums3, op=dist.ReduceOp.SUM)
-            mom3 = ops.moments_from_sums(sums3, piv3, want_yaw=False, out=mom3)
+                                out=trs, sums_out=sums_buf)
+            dist.all_reduce(sums_buf, op=dist.ReduceOp.SUM)
+            return ops.moments_from_sums(sums_buf, piv3, want_yaw=False, out=mom_buf)
 
-        for i in range(5):
-            strong_step(i)
-        torch.cuda.synchronize()
-        dist.barrier()
-        a, b = ev(), ev()
-        a.record()
-        for i in range(20):
-            strong_step(5 + i)
-        b.record()
-        torch.cuda.synchronize()
-        mt = torch.tensor([a.elapsed_time(b) / 20], dtype=torch.float64, device=dev)
-        dist.all_reduce(mt, op=dist.ReduceOp.MAX)
-        ms = float(mt.item())
+        def timed(fn, reps_):
+            for i in range(5):
+                fn(i)
+            torch.cuda.synchronize()
+            dist.barrier()
+            a, b = ev(), ev()
+            a.record()
+            for i in range(reps_):
+                fn(5 + i)
+            b.record()
+            torch.cuda.synchronize()
+            mt = torch.tensor([a.elapsed_time(b) / reps_], dtype=torch.float64, device=dev)
+            dist.all_reduce(mt, op=dist.ReduceOp.MAX)
+            return float(mt.item())
+
+        mom_s = [None]
+
+        def exposed(i):
+            mom_s[0] = strong_step(i, sums3, mom_s[0])
+
+        ms = timed(exposed, 20)
         assert int(sums3[0, 0].item()) == C3["n_per_cell"]
+        # the same with the reduction of step i under the kernel of step i + 1 (double-buffered sums, side stream):
+        # what a stream of risk estimates costs per estimate
+        side_s = torch.cuda.Stream(device=dev)
+        main_s = torch.cuda.current_stream()
+        sums_2 = [sums3, torch.empty_like(sums3)]
+        mom_2, done_2 = [None, None], [None, None]
+
+        def overlapped(i):
+            b_ = i & 1
+            if done_2[b_] is not None:
+                main_s.wait_event(done_2[b_])
+            ops.mc_rollout_sums(m3, c3, x3, None, nl, T3, piv3, ego3, seed=1234 + i, sample_offset=lo, workspace=wss,
+                                out=trs, sums_out=sums_2[b_])
+            ready = torch.cuda.Event()
+            ready.record(main_s)
+            with torch.cuda.stream(side_s):
+                side_s.wait_event(ready)
+                dist.all_reduce(sums_2[b_], op=dist.ReduceOp.SUM)
+                mom_2[b_] = ops.moments_from_sums(sums_2[b_], piv3, want_yaw=False, out=mom_2[b_])
+                done_2[b_] = torch.cuda.Event()
+                done_2[b_].record(side_s)
+
+        def overlapped_joined(i):
+            overlapped(i)
+            if i == 5 + 39:
+                main_s.wait_stream(side_s)
+
+        ms_ov = timed(overlapped_joined, 40)
+        main_s.wait_stream(side_s)
+        torch.cuda.synchronize()
+        assert int(sums_2[1][0, 0].item()) == C3["n_per_cell"]
         out["mc_strong_scaling"] = {
             "metric": "mc_traj_steps_per_sec", "value": C3c * C3["n_per_cell"] * T3 / (ms * 1e-3), "unit": "traj-steps/s",
-            "ms": ms, "n_gpus": world, "samples_per_cell_per_gpu": nl, "scaling": "strong",
-            "workload": f"c3 as BASELINE.json states it: 1M samples per obstacle in total, {nl} per cell per GPU, one "
-                        f"exposed NCCL all-reduce of the 164 KB packed sums per step"}
+            "ms": ms, "ms_overlapped": ms_ov, "value_overlapped": C3c * C3["n_per_cell"] * T3 / (ms_ov * 1e-3),
+            "n_gpus": world, "samples_per_cell_per_gpu": nl, "scaling": "strong",
+            "workload": f"c3 as BASELINE.json states it: 1M samples per obstacle in total, {nl} per cell per GPU; ms = one "
+                        f"exposed NCCL all-reduce of the 164 KB packed sums per step, ms_overlapped = the reduction of "
+                        f"step i on a side stream under the kernel of step i + 1"}
         del wss, trs
     del m3, c3, x3, ws3, risk, traj3, wsp, sums3
     # ---- c4: batched MVOE footprint fit + tangent half-plane sweep ---------------------------
