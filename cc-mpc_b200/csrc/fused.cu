@@ -96,12 +96,6 @@ __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wa
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void cta_bar() { asm volatile("bar.sync 2, %0;" ::"n"(WS_THREADS) : "memory"); }
 
-// hi word of a double -> unsigned key ordered like the value (ties in the low word compare equal)
-__device__ __forceinline__ uint32_t hi_key(double v) {
-    const int h = __double2hiint(v);
-    return (uint32_t)h ^ ((uint32_t)(h >> 31) | 0x80000000u);
-}
-
 // EXP: compile-time experiment switches (tools/fused_time.py <exp>): which part of the kernel binds?
 //   bit0 no Gram update, bit1 no A9 predicate, bit2 no Philox / Box-Muller, bit3 no chain.  0 in production.
 static int g_ws_exp = 0;          // read only when built with -DCCMPC_WS_EXPERIMENTS

@@ -102,7 +102,10 @@ __global__ void __launch_bounds__(ST_THREADS, 2) sample_sums_kernel(const StatsA
 
     // ---- per-lane constants: its TS timesteps ------------------------------
     const double r2 = a.r2;
+    // screening box 2^k > R: |dx| >= 2^k or |dy| >= 2^k implies d2 >= r2 (see fused.cu)
+    const double box = __hiloint2double((__double2hiint(sqrt(r2)) & 0x7ff00000) + 0x00100000, 0);
     double pivx[TS], pivy[TS], ex[TS], ey[TS];
+    uint32_t kx[TS], wx[TS], ky[TS], wy[TS];       // integer screen: key(x) - kx <= wx  <=>  |ex - x| < box (+ ties)
     bool tv[TS];
 #pragma unroll
     for (int i = 0; i < TS; ++i) {
@@ -112,15 +115,17 @@ __global__ void __launch_bounds__(ST_THREADS, 2) sample_sums_kernel(const StatsA
         pivy[i] = tv[i] ? a.pivot[(c * T + t) * 2 + 1] : 0.0;
         ex[i] = (tv[i] && COUNT) ? a.ego[c * a.ego_cell_stride + 2 * t] : 0.0;
         ey[i] = (tv[i] && COUNT) ? a.ego[c * a.ego_cell_stride + 2 * t + 1] : 0.0;
+        kx[i] = hi_key(ex[i] - box); wx[i] = hi_key(ex[i] + box) - kx[i];
+        ky[i] = hi_key(ey[i] - box); wy[i] = hi_key(ey[i] + box) - ky[i];
     }
 
     double acc[NT][2];
 #pragma unroll
     for (int i = 0; i < NT; ++i) acc[i][0] = acc[i][1] = 0.0;
-    double s1x[TS], s1y[TS], pen[TS], d2s[TS], yaw_s[TS], yaw_q[TS];
+    double s1x[TS], s1y[TS], pen[TS], yaw_s[TS], yaw_q[TS];
     int coll[TS];
 #pragma unroll
-    for (int i = 0; i < TS; ++i) { s1x[i] = s1y[i] = pen[i] = d2s[i] = yaw_s[i] = yaw_q[i] = 0.0; coll[i] = 0; }
+    for (int i = 0; i < TS; ++i) { s1x[i] = s1y[i] = pen[i] = yaw_s[i] = yaw_q[i] = 0.0; coll[i] = 0; }
     int any_cnt = 0;
 
     // lane's element (double2 index) inside the unit for group 0 of warp 0; groups advance by 4 T
@@ -132,7 +137,7 @@ __global__ void __launch_bounds__(ST_THREADS, 2) sample_sums_kernel(const StatsA
 #define CCMPC_SS_PROCESS(cur, ycur, rv, MASKED)                                                             \
     do {                                                                                                    \
         double f[NF];                                                                                       \
-        bool hit_any = false;                                                                               \
+        bool near_any = false;                                                                              \
         _Pragma("unroll") for (int i = 0; i < TS; ++i) {                                                    \
             const bool ok = (MASKED) ? ((rv) && tv[i]) : true;                                              \
             const double x = (cur)[i].x, y = (cur)[i].y;                                                    \
@@ -141,24 +146,26 @@ __global__ void __launch_bounds__(ST_THREADS, 2) sample_sums_kernel(const StatsA
             s1y[i] += uy;                                                                                   \
             f[2 * i] = ux;                                                                                  \
             f[2 * i + 1] = uy;                                                                              \
-            if (COUNT && ok) {                                                                              \
+            /* A9 screen on the integer pipe: a sample at least `box` away from the ego in x or y cannot */ \
+            /* be a hit; the exact fp64 predicate runs only for warps that hold a near sample            */ \
+            if (COUNT) near_any |= ok & (hi_key(x) - kx[i] <= wx[i]) & (hi_key(y) - ky[i] <= wy[i]);        \
+            if (YAW) { yaw_s[i] += (ycur)[i]; yaw_q[i] = fma((ycur)[i], (ycur)[i], yaw_q[i]); }             \
+        }                                                                                                   \
+        if (COUNT && __any_sync(0xffffffffu, near_any)) {                                                   \
+            bool hit_any = false;                                                                           \
+            _Pragma("unroll") for (int i = 0; i < TS; ++i) {                                                \
+                const bool ok = (MASKED) ? ((rv) && tv[i]) : true;                                          \
                 /* A9 predicate, fixed order, no FMA contraction */                                         \
-                const double dx = __dsub_rn(ex[i], x), dy = __dsub_rn(ey[i], y);                            \
+                const double dx = __dsub_rn(ex[i], (cur)[i].x), dy = __dsub_rn(ey[i], (cur)[i].y);          \
                 const double d2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));                          \
-                d2s[i] += d2;                                                                               \
-                if (d2 < r2) {                                                                              \
+                if (ok && d2 < r2) {                                                                        \
                     ++coll[i];                                                                              \
                     pen[i] += r2 - d2;                                                                      \
                     hit_any = true;                                                                         \
                 }                                                                                           \
             }                                                                                               \
-            if (YAW) { yaw_s[i] += (ycur)[i]; yaw_q[i] = fma((ycur)[i], (ycur)[i], yaw_q[i]); }             \
-        }                                                                                                   \
-        if (COUNT) {                                                                                        \
             const unsigned bal = __ballot_sync(0xffffffffu, hit_any);                                       \
-            if (bal) {                                                                                      \
-                _Pragma("unroll") for (int rr = 0; rr < 4; ++rr) any_cnt += (bal & (0x11111111u << rr)) != 0; \
-            }                                                                                               \
+            _Pragma("unroll") for (int rr = 0; rr < 4; ++rr) any_cnt += (bal & (0x11111111u << rr)) != 0;   \
         }                                                                                                   \
         gram_update<NF>(acc, f);                                                                            \
     } while (0)
@@ -231,7 +238,7 @@ __global__ void __launch_bounds__(ST_THREADS, 2) sample_sums_kernel(const StatsA
     store_gram_tiles<NF>(wsm, acc, q, r);
 #pragma unroll
     for (int i = 0; i < TS; ++i) {
-        double v[7] = {s1x[i], s1y[i], (double)coll[i], pen[i], d2s[i], yaw_s[i], yaw_q[i]};
+        double v[7] = {s1x[i], s1y[i], (double)coll[i], pen[i], 0.0, yaw_s[i], yaw_q[i]};
 #pragma unroll
         for (int k = 0; k < 7; ++k) {
             v[k] += __shfl_xor_sync(0xffffffffu, v[k], 1);
@@ -310,15 +317,30 @@ __global__ void unit_scan_kernel(const int64_t* __restrict__ offsets, int64_t C,
 }
 
 // sums[c] = sum over the cell's units, in unit order
-__global__ void sums_finalize_kernel(const double* __restrict__ partials, const int32_t* __restrict__ cub,
-                                     int len, double* __restrict__ sums) {
+// The d2s slots (sum of squared ego distances, a cost term) follow from the power sums (d2s_from_sums) instead of two
+// FP64-pipe instructions per trajectory-step in the main loop.
+__global__ void sums_finalize_kernel(const double* __restrict__ partials, const int32_t* __restrict__ cub, int T,
+                                     const double* __restrict__ pivot, const double* __restrict__ ego,
+                                     int64_t ego_cell_stride, double* __restrict__ sums) {
+    extern __shared__ double s_sum[];
+    const SumsLayout L(T);
     const int64_t c = blockIdx.x;
-    const int j = blockIdx.y * blockDim.x + threadIdx.x;
-    if (j >= len) return;
     const int u0 = cub[c], u1 = cub[c + 1];
-    double s = 0.0;
-    for (int u = u0; u < u1; ++u) s += partials[(int64_t)u * len + j];
-    sums[c * len + j] = s;
+    for (int j = threadIdx.x; j < L.len; j += blockDim.x) {
+        double s = 0.0;
+        for (int u = u0; u < u1; ++u) s += partials[(int64_t)u * L.len + j];
+        s_sum[j] = s;
+    }
+    __syncthreads();
+    for (int j = threadIdx.x; j < L.len; j += blockDim.x) {
+        double v = s_sum[j];
+        if (ego && j >= L.o_d2s && j < L.o_yaw) {
+            const int t = j - L.o_d2s;
+            v = d2s_from_sums(s_sum, L, t, ego[c * ego_cell_stride + 2 * t] - pivot[(c * T + t) * 2],
+                              ego[c * ego_cell_stride + 2 * t + 1] - pivot[(c * T + t) * 2 + 1]);
+        }
+        sums[c * (int64_t)L.len + j] = v;
+    }
 }
 
 // ---------------------------------------------------------------------------
@@ -516,8 +538,8 @@ extern "C" int ccmpc_sample_sums(const double* samples, const int64_t* offsets, 
     }
     rc = check_launch("sample_sums_kernel");
     if (rc) return rc;
-    dim3 fg((unsigned)C, (unsigned)((L.len + 127) / 128));
-    sums_finalize_kernel<<<fg, 128, 0, st>>>(partials, cub, L.len, sums);
+    sums_finalize_kernel<<<(unsigned)C, 256, (size_t)L.len * sizeof(double), st>>>(partials, cub, T, pivot, ego,
+                                                                                   ego_cell_stride, sums);
     return check_launch("sums_finalize_kernel");
 }
 

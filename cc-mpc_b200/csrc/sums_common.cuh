@@ -77,6 +77,12 @@ __device__ __forceinline__ int packed_to_area(int e, const SumsLayout& L, bool h
     return SM::O_YAW2 + (e - L.o_yaw2);
 }
 
+// hi word of a double -> unsigned key ordered like the value (ties in the low word compare equal)
+__device__ __forceinline__ uint32_t hi_key(double v) {
+    const int h = __double2hiint(v);
+    return (uint32_t)h ^ ((uint32_t)(h >> 31) | 0x80000000u);
+}
+
 // d2s[t] = sum_n |ego_t - p_{n,t}|^2 from the shifted power sums (a = ego - pivot, u = p - pivot):
 //   sum |a - u|^2 = n |a|^2 - 2 a . S1 + S2xx + S2yy.
 // Used where the per-sample accumulation of d2s is not worth two FP64-pipe instructions per trajectory-step
