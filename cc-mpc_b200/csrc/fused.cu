@@ -39,7 +39,7 @@
 // it over the lanes: 18 % of all warp instructions); one TMA tensor store per tile 0.735 ms; two CTAs per SM
 // (two consumer warps per sub-partition) could not get below 0.74 ms for the reason above.
 //
-// Restrictions of this fast path: Philox noise, horizon 8 or 16, no yaw sums.
+// Restrictions of this fast path: Philox noise, no yaw sums.  Any horizon 1..16 (tiles are padded to 8 or 16 steps).
 #include <stdlib.h>
 #include <string.h>
 #include <cuda.h>          // CUtensorMap (types only: the encoder is fetched through cudaGetDriverEntryPoint)
@@ -132,7 +132,10 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
                        const double* __restrict__ pivot, const double* __restrict__ ego, int64_t ego_cell_stride,
                        double r2, const __grid_constant__ CUtensorMap traj_map, int store_traj,
                        double* __restrict__ partials, int32_t* __restrict__ slot_cell, uint8_t* __restrict__ status,
-                       double* __restrict__ x0_out, int64_t C) {
+                       double* __restrict__ x0_out, int64_t C, int T) {
+    // T <= TSH = 4 NF timesteps are live (the shrinking horizon runs predict_ideal at T = ph - 1, ph - 2, ...):
+    // the columns past 2 T of every tile stay zero (cleared once below, never written), so they add nothing to
+    // the Gram update, and the tensor map clips them from the store.
     using WL = WsLayout<NF>;
     using SM = SumsWarpArea<NF>;
     constexpr int TSH = WL::TSH, TS = NF / 2, NT = SM::NT;
@@ -154,6 +157,8 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
         for (int b = 0; b < WS_NB; ++b) { mbar_init(full + b, 1); mbar_init(empty + b, 2); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    for (int i = tid; i < (int)(WS_NB * WL::TILE / 16); i += WS_THREADS)
+        reinterpret_cast<double2*>(ring)[i] = make_double2(0.0, 0.0);
     const int64_t ntc = (n + 31) >> 5;                                  // tiles per cell
     const int64_t TT = C * ntc;
     const int64_t g_lo = (TT * blockIdx.x) / gridDim.x, g_hi = (TT * (blockIdx.x + 1)) / gridDim.x;
@@ -225,6 +230,7 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
                 };
 #pragma unroll
                 for (int t2 = 0; t2 < TSH / 2; ++t2) {
+                    if (2 * t2 >= T) break;
                     float za = 0.3f, zb = -0.2f, zc = 0.1f, zd = 0.7f;
                     if (!(exp_flags & 4)) {
                         Philox rr = philox4x32_10(gi_lo, gi_hi, (uint32_t)c, (uint32_t)t2, seed_lo, seed_hi);
@@ -246,7 +252,8 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
                     if (store_traj) {
 #pragma unroll
                         for (int h = 0; h < WL::H; ++h)
-                            tma_store_box(&traj_map, ring + (size_t)b * WL::TILE + h * WL::SUB, 16 * h, (int)i0, (int)c);
+                            if (8 * h < T)
+                                tma_store_box(&traj_map, ring + (size_t)b * WL::TILE + h * WL::SUB, 16 * h, (int)i0, (int)c);
                         bulk_commit();
                     }
                     mbar_arrive(full + b);
@@ -256,7 +263,7 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
             retire_prev();
             // this warp's counts of the segment -> shared memory (the consumers fold them into the partial vector)
             double* pc = s_pcnt + (size_t)p * WL::PC_LEN;
-            if (lane < TSH) { pc[lane] = (double)coll_mine; pc[TSH + lane] = pen_mine; }
+            if (lane < TSH) { pc[lane] = (double)coll_mine; pc[TSH + lane] = pen_mine; }      // zero for lanes >= T
             if (lane == 0) pc[2 * TSH] = (double)any_cnt;
             cta_bar();                                                  // (S3) counts visible to the consumers
             seq0 += cnt;
@@ -274,17 +281,17 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
     for (int i = 0; i < TS; ++i) ld_off[i] = (((TS * q + i) & 7) ^ r) << 4;
     // screening box 2^k > R: |dx| >= 2^k or |dy| >= 2^k implies d2 >= r2
     const double box = __hiloint2double((__double2hiint(sqrt(r2)) & 0x7ff00000) + 0x00100000, 0);
-    const SumsLayout L(TSH);
+    const SumsLayout L(T);
     int64_t seq0 = 0;
     for (int64_t gt = g_lo; gt < g_hi;) {
         const int64_t c = gt / ntc, t0 = gt - c * ntc;
         const int cnt = (int)min(g_hi - gt, ntc - t0);
         cta_bar();                                      // (S1) producers are done with the previous cell's parameters
-        rollout_setup<32 * WS_CONS>(mean, cov, cross, Tm, x0, c, TSH, seed_lo, seed_hi, sp, s_x0, status, x0_out, tid,
+        rollout_setup<32 * WS_CONS>(mean, cov, cross, Tm, x0, c, T, seed_lo, seed_hi, sp, s_x0, status, x0_out, tid,
                                     t0 == 0);
-        if (tid < TSH) {                                // what the producers need per timestep besides the chain
+        if (tid < T) {                                  // what the producers need per timestep besides the chain
             const int t = tid;
-            const double px = pivot[(c * TSH + t) * 2], py = pivot[(c * TSH + t) * 2 + 1];
+            const double px = pivot[(c * T + t) * 2], py = pivot[(c * T + t) * 2 + 1];
             const double ex = ego[c * ego_cell_stride + 2 * t], ey = ego[c * ego_cell_stride + 2 * t + 1];
             s_piv[t] = make_double2(px, py);
             s_ego[t] = make_double2(ex, ey);
@@ -296,7 +303,7 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
         }
         double piv[NF];                                 // pivot of my columns NF q .. NF q + NF - 1
 #pragma unroll
-        for (int i = 0; i < NF; ++i) piv[i] = pivot[c * 2 * TSH + NF * q + i];
+        for (int i = 0; i < NF; ++i) piv[i] = NF * q + i < 2 * T ? pivot[c * 2 * T + NF * q + i] : 0.0;
         double acc[NT][2];
 #pragma unroll
         for (int i = 0; i < NT; ++i) acc[i][0] = acc[i][1] = 0.0;
@@ -473,7 +480,7 @@ template <int NF>
 static int launch_ws(int G, cudaStream_t st, const double* mean, const double* cov, const double* cross, int Tm,
                      const double* x0, int64_t C, int64_t n, uint64_t seed, uint64_t sample_offset,
                      const double* pivot, const double* ego, int64_t ego_cell_stride, double R, double* traj,
-                     double* partials, int32_t* slot_cell, uint8_t* status, double* x0_out) {
+                     double* partials, int32_t* slot_cell, uint8_t* status, double* x0_out, int Tsh) {
     auto kernel = rollout_sums_ws_kernel<NF, 0>;
 #ifdef CCMPC_WS_EXPERIMENTS
     if (g_ws_exp == 1) kernel = rollout_sums_ws_kernel<NF, 1>;
@@ -489,12 +496,12 @@ static int launch_ws(int G, cudaStream_t st, const double* mean, const double* c
     CUtensorMap map;
     memset(&map, 0, sizeof(map));
     if (traj) {
-        int rc = make_traj_map(&map, traj, C, n, 4 * NF);
+        int rc = make_traj_map(&map, traj, C, n, Tsh);
         if (rc != CCMPC_OK) return rc;
     }
     kernel<<<(unsigned)G, WS_THREADS, WsLayout<NF>::BYTES, st>>>(
         mean, cov, cross, Tm, x0, n, (uint32_t)seed, (uint32_t)(seed >> 32), sample_offset, pivot, ego,
-        ego_cell_stride, R * R, map, traj ? 1 : 0, partials, slot_cell, status, x0_out, C);
+        ego_cell_stride, R * R, map, traj ? 1 : 0, partials, slot_cell, status, x0_out, C, Tsh);
     return check_launch("rollout_sums_ws_kernel");
 }
 
@@ -503,7 +510,7 @@ extern "C" int ccmpc_mc_rollout_sums(const double* mean, const double* cov, cons
                                      uint64_t sample_offset, const double* pivot, const double* ego,
                                      int64_t ego_cell_stride, double R, double* traj, double* sums, uint8_t* status,
                                      double* x0_out, void* workspace, size_t workspace_bytes, void* stream) {
-    CCMPC_REQUIRE(Tsh == 16 || Tsh == 8, "ccmpc_mc_rollout_sums: horizon must be 8 or 16 (got %d)", Tsh);
+    CCMPC_REQUIRE(Tsh >= 1 && Tsh <= CCMPC_MAX_T, "ccmpc_mc_rollout_sums: need 1 <= Tsh <= %d", CCMPC_MAX_T);
     CCMPC_REQUIRE(Tm >= Tsh + 1, "ccmpc_mc_rollout_sums: moments must cover Tsh + 1 steps (Tm = %d)", Tm);
     CCMPC_REQUIRE(C >= 0 && n >= 0 && C < 65536 && n < ((int64_t)1 << 31), "ccmpc_mc_rollout_sums: bad C / n");
     if (C == 0) return CCMPC_OK;
@@ -531,10 +538,10 @@ extern "C" int ccmpc_mc_rollout_sums(const double* mean, const double* cov, cons
         cudaError_t e = cudaMemsetAsync(slot_cell, 0xFF, (size_t)slots * sizeof(int32_t), st);      // -1: empty slot
         if (e != cudaSuccess) { set_error("ccmpc_mc_rollout_sums: memset: %s", cudaGetErrorString(e)); return CCMPC_E_LAUNCH; }
     }
-    int rc = Tsh == 16 ? launch_ws<4>(G, st, mean, cov, cross, Tm, x0, C, n, seed, sample_offset, pivot, ego,
-                                      ego_cell_stride, R, traj, partials, slot_cell, status, x0_out)
-                       : launch_ws<2>(G, st, mean, cov, cross, Tm, x0, C, n, seed, sample_offset, pivot, ego,
-                                      ego_cell_stride, R, traj, partials, slot_cell, status, x0_out);
+    int rc = Tsh > 8 ? launch_ws<4>(G, st, mean, cov, cross, Tm, x0, C, n, seed, sample_offset, pivot, ego,
+                                    ego_cell_stride, R, traj, partials, slot_cell, status, x0_out, Tsh)
+                     : launch_ws<2>(G, st, mean, cov, cross, Tm, x0, C, n, seed, sample_offset, pivot, ego,
+                                    ego_cell_stride, R, traj, partials, slot_cell, status, x0_out, Tsh);
     if (rc != CCMPC_OK) return rc;
     fused_finalize_kernel<<<(unsigned)C, 256, (size_t)L.len * sizeof(double), st>>>(partials, slot_cell, G, Tsh, pivot,
                                                                                    ego, ego_cell_stride, sums);

@@ -493,13 +493,44 @@ class MidlevelConstraints:
             out.setdefault(int(o), {})[int(k)] = traj[c].cpu().numpy() if as_numpy else traj[c]
         return out
 
+    def _predict_ideal_fused(self, cells: CellBatch, T: int, params, ego_xy, x0=None, n_samples=None, seed=None):
+        """predict_ideal (v8ideal:2620-2711) + the sums the builder needs, in one kernel (ccmpc_mc_rollout_sums).
+        -> (CellBatch of the ideal trajectories, packed sums, pivot).  Raises like :meth:`predict_ideal`."""
+        frame = int(getattr(params, "frame", 0)) - self.frame_stride
+        moments = self._load_moments(frame, self.ego_vehicle_id)
+        if moments.T < T + 1:
+            raise InSimulationException(f"moments cover {moments.T} steps; predict_ideal indexes [t+1] up to {T}")
+        n = self.n_ideal_samples if n_samples is None else int(n_samples)
+        sel, co, ck = self._select_cells(cells.n_states, moments)
+        mean, cov, cross = self._gather(moments, sel)
+        pivot = mean[:, 1:T + 1].contiguous()              # x_{t+1} ~ mean[t+1]: a pivot every rank could compute
+        if seed is None:
+            self._calls += 1
+            seed = (self.seed << 20) + self._calls
+        ego_t = ego_xy if torch.is_tensor(ego_xy) else _h2d(np.asarray(ego_xy, dtype=np.float64)[:T, :2], self.device)
+        x0_t = None if x0 is None else _h2d(np.asarray(x0, dtype=np.float64).reshape(len(sel), 2), self.device)
+        traj, sums, status, x0_used = ops.mc_rollout_sums(mean, cov, cross, x0_t, n, T, pivot, ego_t, R=self.R,
+                                                          seed=seed, workspace=self._fused_ws(len(sel), n, T))
+        st = status.cpu().numpy()
+        if st.any():
+            bad = int(np.nonzero(st)[0][0])
+            raise np.linalg.LinAlgError("Singular matrix" if st[bad] == ops.ST_SINGULAR
+                                        else "Matrix is not positive definite")
+        work = CellBatch.uniform(traj, co, ck, cells.n_states)
+        work.status, work.x0 = status, x0_used
+        self.last_ideal = work
+        return work, sums, pivot
+
     # --------------------------------------------------------------- builders
     def minkowski(self, cells: CellBatch, ref_traj, eps_ura, ego=None, want_violations: bool = False,
-                  fields=ops.MINK_FIELDS):
-        """Device core of v8ideal:881-947 on one CellBatch -> (out dict of device tensors, sums, pivot)."""
+                  fields=ops.MINK_FIELDS, sums=None, pivot=None):
+        """Device core of v8ideal:881-947 on one CellBatch -> (out dict of device tensors, sums, pivot).
+        ``sums`` / ``pivot``: the packed sums of the cells when something already produced them (the fused
+        rollout)."""
         T = cells.T
         ref = _h2d(np.asarray(ref_traj, dtype=np.float64)[:T, :2], self.device)
-        sums, pivot = self._sums(cells, ego=ego)
+        if sums is None:
+            sums, pivot = self._sums(cells, ego=ego)
         out = ops.minkowski_alloc(cells.C, T, self.device, fields=fields)
         ops.minkowski_halfplanes(sums, pivot, ref, self._eps_cells(cells, eps_ura), self.prediction_horizon,
                                  R=self.R, target_p=self.target_p, accel=self.accel, out=out)
@@ -584,9 +615,18 @@ class MidlevelConstraints:
             raise NotImplementedError("road-boundary slack S_big (v8ideal:797-818) is not part of this path")
         # sums of the raw predictions: L4 polytopes, [tau+1|tau] bookkeeping, and the rows when T == Tpred
         if T < Tpred:
-            self.predict_ideal(cells, T, self.ego_vehicle_id, params, **(ideal_noise or {}))   # :824-825
-            work = self.last_ideal
-            out, sums_w, pivot_w = self.minkowski(work, ref_traj, eps_ura, ego=ego, want_violations=want_violations)
+            if (ideal_noise or {}).get("z") is None:
+                # Philox noise: ONE kernel rolls the ideal trajectories out, stores them and reduces them (:824-825
+                # + the moment reads of :893-904 and :960)
+                work, sums_w, pivot_w = self._predict_ideal_fused(cells, T, params, ref_traj if ego is None else ego,
+                                                                 **(ideal_noise or {}))
+                out, _, _ = self.minkowski(work, ref_traj, eps_ura, want_violations=want_violations, sums=sums_w,
+                                           pivot=pivot_w)
+            else:
+                self.predict_ideal(cells, T, self.ego_vehicle_id, params, **ideal_noise)       # :824-825
+                work = self.last_ideal
+                out, sums_w, pivot_w = self.minkowski(work, ref_traj, eps_ura, ego=ego,
+                                                      want_violations=want_violations)
             sums_c, pivot_c = self._sums(cells)
         else:
             work = cells
@@ -696,7 +736,7 @@ class MidlevelConstraints:
         sel, co, ck = self._select_cells(n_states, moments)
         mean, cov, cross = self._gather(moments, sel)
         pivot = mean[:, 1:T + 1].contiguous()
-        if z is None and T in (8, 16) and moments.T >= T + 1:
+        if z is None and 1 <= T <= ops.MAX_T and moments.T >= T + 1:
             # one kernel: rollout, trajectory store, counts and power sums (ccmpc_mc_rollout_sums)
             if seed is None:
                 self._calls += 1

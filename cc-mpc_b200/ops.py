@@ -476,7 +476,7 @@ def mc_rollout_sums_workspace(C: int, n: int, Tsh: int, device) -> torch.Tensor:
 def mc_rollout_sums(mean, cov, cross, x0, n: int, Tsh: int, pivot, ego, R: float = R_EV_OV, seed: int = 0,
                     sample_offset: int = 0, materialize: bool = True, workspace=None, out=None, sums_out=None):
     """mc_rollout + sample_sums in one kernel (the trajectory tensor is written once and not read back).
-    Arguments as mc_rollout plus pivot [C,Tsh,2] and ego [Tsh,2] | [C,Tsh,2]; Tsh in (8, 16), Philox noise.
+    Arguments as mc_rollout plus pivot [C,Tsh,2] and ego [Tsh,2] | [C,Tsh,2]; any Tsh <= 16, Philox noise.
     -> traj [C,n,Tsh,2] | None (materialize=False), sums [C, sums_len(Tsh)], status [C] uint8, x0_used [C,2]."""
     lib = _lib.load()
     _chk(mean, F64, "mean", (2,)); _chk(cov, F64, "cov", (2, 2)); _chk(cross, F64, "cross", (2, 2))

@@ -366,11 +366,12 @@ int ccmpc_mc_risk(const double* mean, const double* cov, const double* cross, in
                   void* workspace, size_t workspace_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------
- * K1+K2+K6 fused  ccmpc_mc_rollout followed by ccmpc_sample_sums in ONE kernel: the CTA that
- * rolls 128 samples out (v8ideal:2662-2709, same Philox stream as ccmpc_mc_rollout) writes
- * them to traj once and reduces them from shared memory (np.mean / np.cov of every (t, tau)
- * pair, makeconstraint:55, v8ideal:2586-2606; A9 counts) - the trajectory tensor is not read
- * back.  Philox noise only; Tsh = 8 or 16; no yaw sums (those entries of the layout are 0).
+ * K1+K2+K6 fused  ccmpc_mc_rollout followed by ccmpc_sample_sums in ONE kernel: producer warps
+ * roll the samples out (v8ideal:2662-2709, same Philox stream as ccmpc_mc_rollout: sample i of
+ * cell c is bit-identical) into shared-memory tiles, a TMA tensor store writes each tile to traj
+ * once and consumer warps reduce the same tile (np.mean / np.cov of every (t, tau) pair,
+ * makeconstraint:55, v8ideal:2586-2606; A9 counts) - the trajectory tensor is not read back.
+ * Philox noise only; 1 <= Tsh <= 16; no yaw sums (those entries of the layout are 0).
  *   pivot [C,Tsh,2] (shift of the power sums; the moment means are a good choice),
  *   ego [Tsh,2] (stride 0) or [C,Tsh,2] (stride 2 Tsh).
  *   out: traj [C,n,Tsh,2] (NULL: do not materialise), sums [C, ccmpc_sums_len(Tsh)] in the

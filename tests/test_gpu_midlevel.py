@@ -465,3 +465,41 @@ def test_mc_collision_risk_two_ranks_equals_one(dev):
     for p in procs:
         p.join(timeout=60)
     assert sorted(res) == [(0, True), (1, True)]
+
+
+def test_shrinking_step_with_philox_noise_is_consistent(dev, golden, tmp_path):
+    """Without supplied noise the shrinking-horizon branch runs predict_ideal, the trajectory store and the sums in
+    ONE kernel (ccmpc_mc_rollout_sums at T = 7): the rows it returns must be the rows of the ideal trajectories it
+    stored - rebuilt here from those trajectories with the two-kernel path and with the oracle."""
+    from ccmpc_b200 import midlevel, ops
+    from oracle import restate
+    g, K, ovs, _, _ = _c1(golden)
+    T, n = 8, 50_000
+    mc = midlevel.MidlevelConstraints(T, out_dir=str(tmp_path), device=dev, n_ideal_samples=n, seed=3)
+    mc.compute_obstacle_constraints_GMM_Minkowski_idealprediction(
+        params_of(ovs, 100), ovs, None, None, None, g["s1_eps_ura"], None, T, g["ref_traj"])
+    l0 = ops._lib.load().ccmpc_launch_count()
+    built = mc.compute_obstacle_constraints_GMM_Minkowski_idealprediction(
+        params_of(ovs, 110), ovs, None, None, None, g["s2_eps_ura"], None, T - 1, g["ref_traj"])
+    hp, work = built[0], mc.last_ideal
+    assert work.T == T - 1 and work.N == sum(K) * n and not hp.status.any()
+    # the same rows from the stored trajectories through sample_sums (other summation order: 1e-9)
+    out2, _, _ = mc.minkowski(work, g["ref_traj"], g["s2_eps_ura"])
+    h2 = {k: v.cpu().numpy() for k, v in out2.items()}
+    np.testing.assert_array_equal(hp.idx, h2["idx_side"] & 1)
+    np.testing.assert_array_equal(hp.side, np.where(h2["idx_side"] & 2, -1, 1))
+    np.testing.assert_allclose(hp.n, h2["nd"][..., :2], rtol=1e-8)
+    np.testing.assert_allclose(hp.rhs, h2["nd"][..., 2], rtol=1e-8)
+    # ... and through the oracle on one cell
+    traj = work.samples.reshape(sum(K), n, T - 1, 2)[1].cpu().numpy()
+    ref = restate.minkowski_cell(traj, g["ref_traj"], g["s2_eps_ura"][0, 1], T)
+    np.testing.assert_array_equal(hp.side[1], ref["side"])
+    np.testing.assert_allclose(hp.rhs[1], ref["d"], rtol=1e-7)
+    # the moments it saved for the next step are the moments of those trajectories
+    with open(os.path.join(str(tmp_path), "agent0_frame110_moments"), "rb") as f:
+        d = pickle.load(f)
+    m, cv, cr = restate.cell_moments(traj)
+    np.testing.assert_allclose(np.stack(d["mean_p0p1"][0][1]), m, rtol=1e-10)
+    np.testing.assert_allclose(np.stack(d["cov_p0p1"][0][1]), cv, rtol=1e-8, atol=1e-12)
+    np.testing.assert_allclose(d["cross_cov"][0][1][5][2], cr[5, 2], rtol=1e-8, atol=1e-12)
+    del l0

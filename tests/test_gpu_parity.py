@@ -796,7 +796,7 @@ def test_group_by_mode_fused_yaws_equal_yaws_from_positions(dev):
 
 
 # --------------------------------------------------------- fused rollout + store + sums
-@pytest.mark.parametrize("Tsh,n", [(16, 100_003), (8, 5000), (16, 130), (8, 1)])
+@pytest.mark.parametrize("Tsh,n", [(16, 100_003), (8, 5000), (16, 130), (8, 1), (7, 4099), (13, 1000), (1, 100), (9, 33)])
 def test_mc_rollout_sums_equals_rollout_then_sample_sums(dev, Tsh, n):
     """ccmpc_mc_rollout_sums = ccmpc_mc_rollout followed by ccmpc_sample_sums: the trajectories are bit-identical,
     the counts bit-exact, the power sums equal to fp64 round-off (different partition of the same additions)."""
