@@ -17,18 +17,21 @@
 //     instruction-level parallelism of that warp, while the DMMA stream loses only ~7 %;
 //   * two DMMA warps on one sub-partition halve each other, and the vector FP64 of one (shift, S1, predicate)
 //     waits for the other's DMMAs.
-// So: exactly ONE consumer warp per sub-partition owns the Gram update (warps 0-3, `setmaxnreg.inc` to 128
-// registers), its own vector FP64 instructions are the only ones on its critical path and are kept to the
-// pivot shift and S1 (the A9 predicate is screened on the integer pipe, below), and the rollout - a long
-// dependent chain of Philox (integer), Box-Muller (MUFU) and 7 FMAs per step that does not mind waiting for
-// DMMA gaps - runs in 20 producer warps (`setmaxnreg.dec` to 64).  A tile = 32 samples x T timesteps, one
-// sample per producer lane, kept as T/8 sub-tiles of [32 rows][128 B] in the TMA 128-byte swizzle (16-byte
-// chunk j of row i sits at chunk j ^ (i & 7)): the lane-per-row writes of one timestep spread over all banks
-// AND the tile is the image a TMA tensor store un-swizzles into the row-major (C, n, T, 2) trajectory tensor.
-// Tiles travel through a ring of 24 shared-memory buffers guarded by mbarriers (full: producer -> consumer;
-// empty: consumer + the producer's own "TMA finished reading" -> next producer).  ONE lane per producer warp
-// stores the finished tile with T/8 cp.async.bulk.tensor instructions (4 KB each; rows past the end of the
-// cell are clipped by the tensor map).
+// So: exactly ONE consumer warp per sub-partition owns the Gram update (warps 0-3, `setmaxnreg.inc` to 112
+// registers); the only vector FP64 instructions in its in-order stream are the pivot shift and S1.  Everything
+// else runs in 20 producer warps (`setmaxnreg.dec` to 72): the rollout - a long dependent chain of Philox
+// (integer), Box-Muller (MUFU) and 7 FMAs per step that does not mind waiting for DMMA gaps - and the A9
+// predicate, behind a screen on the INTEGER pipe: a sample whose x or y is at least 4 m (2^k > R) away from the
+// ego cannot be a hit, which the hi words of the doubles decide as unsigned keys; the exact fp64 predicate (the
+// oracle's operation order, no FMA) runs only for the warp-steps that hold a near sample, and the counts live in
+// producer registers (lane t owns timestep t).  A tile = 32 samples x 8 or 16 timesteps, one sample per
+// producer lane, kept as sub-tiles of [32 rows][128 B] in the TMA 128-byte swizzle (16-byte chunk j of row i
+// sits at chunk j ^ (i & 7)): the lane-per-row writes of one timestep spread over all banks AND the tile is the
+// image a TMA tensor store un-swizzles into the row-major (C, n, T, 2) trajectory tensor.  Tiles travel through
+// a ring of 24 shared-memory buffers guarded by mbarriers (full: producer -> consumer; empty: consumer + the
+// producer's own "TMA finished reading" -> next producer).  ONE lane per producer warp stores the finished tile
+// with one cp.async.bulk.tensor (UTMASTG) per 4 KB sub-tile; rows past the end of the cell and columns past the
+// horizon are clipped by the tensor map.
 //
 // Work split: the tiles of all cells form one list, CTA j takes the j-th contiguous share of it; where a share
 // crosses a cell boundary the CTA finishes the cell (partial sums vector out, accumulators cleared, step
@@ -36,8 +39,9 @@
 //
 // Measured on the way (c3, one B200; profiles/r02_fused_notes.txt): round-1 kernel 0.817 ms; warp-specialised
 // with one cp.async.bulk per LANE 0.977 ms (the instruction takes uniform operands, the compiler serialises
-// it over the lanes: 18 % of all warp instructions); one TMA tensor store per tile 0.735 ms; two CTAs per SM
-// (two consumer warps per sub-partition) could not get below 0.74 ms for the reason above.
+// it over the lanes: 18 % of all warp instructions); one TMA tensor store per tile, two CTAs per SM 0.735 ms;
+// this form 0.74 ms with even tile shares for any number of cells.  Storing the trajectories straight from
+// registers (no raw tile) caps the kernel at 0.63 ms of scattered 32-byte stores: they have to leave through TMA.
 //
 // Restrictions of this fast path: Philox noise, no yaw sums.  Any horizon 1..16 (tiles are padded to 8 or 16 steps).
 #include <stdlib.h>
