@@ -128,7 +128,7 @@ struct WsLayout {                                     // dynamic shared memory o
 
 // grid G (<= number of SMs): CTA j handles global tiles [j TT / G, (j + 1) TT / G), TT = C ceil(n / 32).
 // partial sums of the segment (CTA j, cell c) go to slot j + c of `partials`, `slot_cell[j + c] = c`.
-template <int NF, int EXP = 0>
+template <int NF, bool FULLT, int EXP = 0>
 __global__ void __launch_bounds__(WS_THREADS, 1)
 rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict__ cov,
                        const double* __restrict__ cross, int Tm, const double* __restrict__ x0, int64_t n,
@@ -136,7 +136,7 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
                        const double* __restrict__ pivot, const double* __restrict__ ego, int64_t ego_cell_stride,
                        double r2, const __grid_constant__ CUtensorMap traj_map, int store_traj,
                        double* __restrict__ partials, int32_t* __restrict__ slot_cell, uint8_t* __restrict__ status,
-                       double* __restrict__ x0_out, int64_t C, int T) {
+                       double* __restrict__ x0_out, int64_t C, int T_rt) {
     // T <= TSH = 4 NF timesteps are live (the shrinking horizon runs predict_ideal at T = ph - 1, ph - 2, ...):
     // the columns past 2 T of every tile stay zero (cleared once below, never written), so they add nothing to
     // the Gram update, and the tensor map clips them from the store.
@@ -144,6 +144,7 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
     using SM = SumsWarpArea<NF>;
     constexpr int TSH = WL::TSH, TS = NF / 2, NT = SM::NT;
     constexpr int exp_flags = EXP;
+    const int T = FULLT ? TSH : T_rt;               // FULLT: the horizon is a compile-time constant (ph8 / ph16)
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     unsigned char* ring = smem_raw + WL::O_RING;
     double* area = reinterpret_cast<double*>(smem_raw + WL::O_AREA);
@@ -485,12 +486,12 @@ static int launch_ws(int G, cudaStream_t st, const double* mean, const double* c
                      const double* x0, int64_t C, int64_t n, uint64_t seed, uint64_t sample_offset,
                      const double* pivot, const double* ego, int64_t ego_cell_stride, double R, double* traj,
                      double* partials, int32_t* slot_cell, uint8_t* status, double* x0_out, int Tsh) {
-    auto kernel = rollout_sums_ws_kernel<NF, 0>;
+    auto kernel = Tsh == 4 * NF ? rollout_sums_ws_kernel<NF, true, 0> : rollout_sums_ws_kernel<NF, false, 0>;
 #ifdef CCMPC_WS_EXPERIMENTS
-    if (g_ws_exp == 1) kernel = rollout_sums_ws_kernel<NF, 1>;
-    if (g_ws_exp == 2) kernel = rollout_sums_ws_kernel<NF, 2>;
-    if (g_ws_exp == 3) kernel = rollout_sums_ws_kernel<NF, 3>;
-    if (g_ws_exp == 12) kernel = rollout_sums_ws_kernel<NF, 12>;
+    if (g_ws_exp == 1) kernel = rollout_sums_ws_kernel<NF, true, 1>;
+    if (g_ws_exp == 2) kernel = rollout_sums_ws_kernel<NF, true, 2>;
+    if (g_ws_exp == 3) kernel = rollout_sums_ws_kernel<NF, true, 3>;
+    if (g_ws_exp == 12) kernel = rollout_sums_ws_kernel<NF, true, 12>;
 #endif
     {
         cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,

@@ -53,26 +53,32 @@ def eps_allocation(K_per_obstacle: Sequence[int], eps: float = EPS_TOTAL) -> np.
     return out
 
 
+_HOST_STAGE: Dict[int, torch.Tensor] = {}
+
+
 def _to_host(tensors: Dict[str, torch.Tensor]) -> Dict[str, np.ndarray]:
-    """Small device results -> host with ONE synchronising copy (a `.cpu()` per tensor is a stream sync each)."""
+    """Small device results -> host with ONE stream synchronisation: every tensor is copied asynchronously into its
+    slice of a reusable pinned buffer (a `.cpu()` per tensor is a sync each), then the stream is synchronised and the
+    slices are copied out (the pinned buffer is reused by the next call)."""
     names = [k for k, v in tensors.items() if v is not None]
     if not names:
         return {}
-    flat = [tensors[k].contiguous().view(torch.uint8).reshape(-1) for k in names]
-    sizes = [int(f.numel()) for f in flat]
-    pad = [(-n) % 16 for n in sizes]                       # keep every piece 16-byte aligned for the dtype views
-    pieces = []
-    for f, p in zip(flat, pad):
-        pieces.append(f)
-        if p:
-            pieces.append(torch.zeros(p, dtype=torch.uint8, device=f.device))
-    host = torch.cat(pieces).cpu().numpy()
-    out, off = {}, 0
-    for k, n, p in zip(names, sizes, pad):
-        t = tensors[k]
-        out[k] = host[off:off + n].view(_NP_OF[t.dtype]).reshape(tuple(t.shape))
-        off += n + p
-    return out
+    sizes = [int(tensors[k].numel() * tensors[k].element_size()) for k in names]
+    offs, total = [], 0
+    for n in sizes:
+        offs.append(total)
+        total += (n + 15) // 16 * 16
+    cap = 1 << max(12, (total - 1).bit_length())
+    stage = _HOST_STAGE.get(cap)
+    if stage is None:
+        stage = _HOST_STAGE[cap] = torch.empty(cap, dtype=torch.uint8).pin_memory()
+    for k, n, o in zip(names, sizes, offs):
+        t = tensors[k].contiguous()
+        stage[o:o + n].view(t.dtype).view(t.shape).copy_(t, non_blocking=True)
+    torch.cuda.current_stream().synchronize()
+    host = stage[:total].numpy().copy()
+    return {k: host[o:o + n].view(_NP_OF[tensors[k].dtype]).reshape(tuple(tensors[k].shape))
+            for k, n, o in zip(names, sizes, offs)}
 
 
 _NP_OF = {torch.float64: np.float64, torch.float32: np.float32, torch.int64: np.int64, torch.int32: np.int32,
