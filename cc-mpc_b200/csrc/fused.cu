@@ -210,17 +210,21 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
                 bool hit_mine = false;
                 // one step: chain, shifted copy for the Gram update, A9 screen (integer pipe) and, for warps that
                 // hold a sample within `box` of the ego in x and y, the exact predicate in the oracle's order
-                auto step = [&](int t, double zx, double zy) {
+                // one step = chain + tile write (`advance`), then the A9 screen (integer pipe) and, for warps that
+                // hold a sample within `box` of the ego in x and y, the exact predicate in the oracle's order (`screen`)
+                auto advance = [&](int t, double zx, double zy) {
                     if (!(exp_flags & 8)) rollout_step(sp[t], x, y, zx, zy);
                     // absent rows hold the pivot: u = 0 in the Gram update (the tensor map clips them from the store)
                     *reinterpret_cast<double2*>(row + (t >> 3) * WL::SUB + (((t & 7) ^ sw) << 4)) =
                         valid ? make_double2(x, y) : s_piv[t];
+                };
+                auto screen = [&](int t, double xs, double ys) {
                     if (exp_flags & 2) return;
                     const uint4 k = s_scr[t];
-                    const bool near = valid & (hi_key(x) - k.x <= k.y) & (hi_key(y) - k.z <= k.w);
+                    const bool near = valid & (hi_key(xs) - k.x <= k.y) & (hi_key(ys) - k.z <= k.w);
                     if (__any_sync(0xffffffffu, near)) {
                         const double2 e = s_ego[t];
-                        const double dx = __dsub_rn(e.x, x), dy = __dsub_rn(e.y, y);
+                        const double dx = __dsub_rn(e.x, xs), dy = __dsub_rn(e.y, ys);
                         const double d2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
                         const bool hit = valid && d2 < r2;
                         const unsigned bal = __ballot_sync(0xffffffffu, hit);
@@ -233,22 +237,30 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
                         }
                     }
                 };
-#pragma unroll
-                for (int t2 = 0; t2 < TSH / 2; ++t2) {
-                    if (2 * t2 >= T) break;
-                    float za = 0.3f, zb = -0.2f, zc = 0.1f, zd = 0.7f;
+                auto noise = [&](int t2, float& za, float& zb, float& zc, float& zd) {
+                    za = 0.3f; zb = -0.2f; zc = 0.1f; zd = 0.7f;
                     if (!(exp_flags & 4)) {
                         Philox rr = philox4x32_10(gi_lo, gi_hi, (uint32_t)c, (uint32_t)t2, seed_lo, seed_hi);
                         box_muller(rr.c[0], rr.c[1], za, zb);
                         box_muller(rr.c[2], rr.c[3], zc, zd);
                     }
-#ifdef WS_F2D_BITS
-                    step(2 * t2, f32_to_f64_bits(za), f32_to_f64_bits(zb));
-                    step(2 * t2 + 1, f32_to_f64_bits(zc), f32_to_f64_bits(zd));
-#else
-                    step(2 * t2, (double)za, (double)zb);
-                    step(2 * t2 + 1, (double)zc, (double)zd);
-#endif
+                };
+                // software pipeline: the Philox block + Box-Muller of step pair t2 + 1 (integer / MUFU, no dependence
+                // on the chain) sits in the SAME basic block as the two chain steps of pair t2, whose FP64
+                // instructions each wait for a gap in the consumer's DMMA stream - the scheduler can fill those
+                // waits; the warp votes of the screen (basic-block boundaries) come after both
+                float za, zb, zc, zd;
+                noise(0, za, zb, zc, zd);
+#pragma unroll
+                for (int t2 = 0; t2 < TSH / 2; ++t2) {
+                    if (2 * t2 >= T) break;
+                    const int ta = 2 * t2, tb = 2 * t2 + 1;
+                    advance(ta, (double)za, (double)zb);
+                    const double xa = x, ya = y;
+                    if (tb < T) advance(tb, (double)zc, (double)zd);
+                    if (2 * t2 + 2 < T) noise(t2 + 1, za, zb, zc, zd);
+                    screen(ta, xa, ya);
+                    if (tb < T) screen(tb, x, y);
                 }
                 any_cnt += __popc(__ballot_sync(0xffffffffu, hit_mine));
                 if (store_traj) fence_proxy_async();    // my generic-proxy writes -> visible to the TMA engine
@@ -333,8 +345,8 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
 #pragma unroll
                     for (int i = 0; i < TS; ++i) {
                         const double2 v = *reinterpret_cast<const double2*>(tile + g2 * 1024 + h * 512 + (ld_off[i] ^ (h << 6)));
-                        f[buf][h][2 * i] = v.x - piv[2 * i];
-                        f[buf][h][2 * i + 1] = v.y - piv[2 * i + 1];
+                        f[buf][h][2 * i] = (exp_flags & 16) ? v.x : v.x - piv[2 * i];
+                        f[buf][h][2 * i + 1] = (exp_flags & 16) ? v.y : v.y - piv[2 * i + 1];
                     }
             };
             load_pair(0, 0);
@@ -492,6 +504,8 @@ static int launch_ws(int G, cudaStream_t st, const double* mean, const double* c
     if (g_ws_exp == 2) kernel = rollout_sums_ws_kernel<NF, true, 2>;
     if (g_ws_exp == 3) kernel = rollout_sums_ws_kernel<NF, true, 3>;
     if (g_ws_exp == 12) kernel = rollout_sums_ws_kernel<NF, true, 12>;
+    if (g_ws_exp == 16) kernel = rollout_sums_ws_kernel<NF, true, 16>;
+    if (g_ws_exp == 28) kernel = rollout_sums_ws_kernel<NF, true, 28>;
 #endif
     {
         cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
