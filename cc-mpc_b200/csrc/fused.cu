@@ -62,9 +62,12 @@ constexpr int WS_CONS = WS_CONS_DEF;                  // consumer warps (whole w
 #endif
 constexpr int WS_PROD = WS_PROD_DEF;                  // producer warps (whole warpgroups)
 constexpr int WS_THREADS = 32 * (WS_CONS + WS_PROD);
-constexpr int WS_NB = WS_PROD > 20 ? 26 : 24;         // tile buffers in the ring
+constexpr int WS_NB = 24;                             // tile buffers in the ring
 // launch allocation 80 registers x 768 threads; 128 x 112 + 640 x 72 fits it
-constexpr int WS_REGS_CONS = 112, WS_REGS_PROD = (WS_CONS == 4 && WS_PROD <= 20) ? 72 : 64;
+#ifndef WS_REGS_PROD_DEF
+#define WS_REGS_PROD_DEF ((WS_CONS == 4 && WS_PROD <= 20) ? 72 : 64)
+#endif
+constexpr int WS_REGS_CONS = 112, WS_REGS_PROD = WS_REGS_PROD_DEF;
 static_assert(WS_PROD % 4 == 0, "setmaxnreg works on whole warpgroups");
 
 // ---- mbarrier / bulk-copy PTX ----------------------------------------------------------------------------
@@ -210,21 +213,47 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
                 bool hit_mine = false;
                 // one step: chain, shifted copy for the Gram update, A9 screen (integer pipe) and, for warps that
                 // hold a sample within `box` of the ego in x and y, the exact predicate in the oracle's order
-                // one step = chain + tile write (`advance`), then the A9 screen (integer pipe) and, for warps that
-                // hold a sample within `box` of the ego in x and y, the exact predicate in the oracle's order (`screen`)
+                // the chain: one straight-line block per tile (8 Philox blocks + Box-Muller on the integer / MUFU
+                // pipes, 16 x 7 FMAs that each wait for a gap in the consumer's DMMA stream) - no votes or branches
+                // in it, so the scheduler is free to fill the FP64 waits with the next steps' noise
+                unsigned near_mask = 0;                 // bit t: this sample is within `box` of the ego at step t
                 auto advance = [&](int t, double zx, double zy) {
                     if (!(exp_flags & 8)) rollout_step(sp[t], x, y, zx, zy);
-                    // absent rows hold the pivot: u = 0 in the Gram update (the tensor map clips them from the store)
-                    *reinterpret_cast<double2*>(row + (t >> 3) * WL::SUB + (((t & 7) ^ sw) << 4)) =
-                        valid ? make_double2(x, y) : s_piv[t];
+                    *reinterpret_cast<double2*>(row + (t >> 3) * WL::SUB + (((t & 7) ^ sw) << 4)) = make_double2(x, y);
+                    if (!(exp_flags & 2)) {             // A9 screen: integer pipe, no branch (see below)
+                        const uint4 k = s_scr[t];
+                        near_mask |= (unsigned)((hi_key(x) - k.x <= k.y) & (hi_key(y) - k.z <= k.w)) << t;
+                    }
                 };
-                auto screen = [&](int t, double xs, double ys) {
-                    if (exp_flags & 2) return;
-                    const uint4 k = s_scr[t];
-                    const bool near = valid & (hi_key(xs) - k.x <= k.y) & (hi_key(ys) - k.z <= k.w);
-                    if (__any_sync(0xffffffffu, near)) {
+#pragma unroll
+                for (int t2 = 0; t2 < TSH / 2; ++t2) {
+                    if (2 * t2 >= T) break;
+                    float za = 0.3f, zb = -0.2f, zc = 0.1f, zd = 0.7f;
+                    if (!(exp_flags & 4)) {
+                        Philox rr = philox4x32_10(gi_lo, gi_hi, (uint32_t)c, (uint32_t)t2, seed_lo, seed_hi);
+                        box_muller(rr.c[0], rr.c[1], za, zb);
+                        box_muller(rr.c[2], rr.c[3], zc, zd);
+                    }
+                    advance(2 * t2, (double)za, (double)zb);
+                    if (2 * t2 + 1 < T) advance(2 * t2 + 1, (double)zc, (double)zd);
+                }
+                // absent rows (last tile of a cell) hold the pivot: u = 0 in the Gram update; the tensor map clips them
+                // from the store
+                if (!valid) {
+                    for (int t = 0; t < T; ++t)
+                        *reinterpret_cast<double2*>(row + (t >> 3) * WL::SUB + (((t & 7) ^ sw) << 4)) = s_piv[t];
+                }
+                // A9: the chain screened every step on the integer pipe (a sample at least `box` away from the ego in
+                // x or y cannot be a hit); one warp-wide OR of the per-step flags, then the exact fp64 predicate (the
+                // oracle's operation order) only for the flagged steps, on the values this lane wrote to its row
+                if (!(exp_flags & 2)) {
+                    unsigned m = __reduce_or_sync(0xffffffffu, valid ? near_mask : 0u);
+                    while (m) {
+                        const int t = __ffs(m) - 1;
+                        m &= m - 1;
+                        const double2 v = *reinterpret_cast<const double2*>(row + (t >> 3) * WL::SUB + (((t & 7) ^ sw) << 4));
                         const double2 e = s_ego[t];
-                        const double dx = __dsub_rn(e.x, xs), dy = __dsub_rn(e.y, ys);
+                        const double dx = __dsub_rn(e.x, v.x), dy = __dsub_rn(e.y, v.y);
                         const double d2 = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
                         const bool hit = valid && d2 < r2;
                         const unsigned bal = __ballot_sync(0xffffffffu, hit);
@@ -236,31 +265,6 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
                             if (lane == t) { coll_mine += __popc(bal); pen_mine += pn; }
                         }
                     }
-                };
-                auto noise = [&](int t2, float& za, float& zb, float& zc, float& zd) {
-                    za = 0.3f; zb = -0.2f; zc = 0.1f; zd = 0.7f;
-                    if (!(exp_flags & 4)) {
-                        Philox rr = philox4x32_10(gi_lo, gi_hi, (uint32_t)c, (uint32_t)t2, seed_lo, seed_hi);
-                        box_muller(rr.c[0], rr.c[1], za, zb);
-                        box_muller(rr.c[2], rr.c[3], zc, zd);
-                    }
-                };
-                // software pipeline: the Philox block + Box-Muller of step pair t2 + 1 (integer / MUFU, no dependence
-                // on the chain) sits in the SAME basic block as the two chain steps of pair t2, whose FP64
-                // instructions each wait for a gap in the consumer's DMMA stream - the scheduler can fill those
-                // waits; the warp votes of the screen (basic-block boundaries) come after both
-                float za, zb, zc, zd;
-                noise(0, za, zb, zc, zd);
-#pragma unroll
-                for (int t2 = 0; t2 < TSH / 2; ++t2) {
-                    if (2 * t2 >= T) break;
-                    const int ta = 2 * t2, tb = 2 * t2 + 1;
-                    advance(ta, (double)za, (double)zb);
-                    const double xa = x, ya = y;
-                    if (tb < T) advance(tb, (double)zc, (double)zd);
-                    if (2 * t2 + 2 < T) noise(t2 + 1, za, zb, zc, zd);
-                    screen(ta, xa, ya);
-                    if (tb < T) screen(tb, x, y);
                 }
                 any_cnt += __popc(__ballot_sync(0xffffffffu, hit_mine));
                 if (store_traj) fence_proxy_async();    // my generic-proxy writes -> visible to the TMA engine
@@ -292,10 +296,11 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
 
     // ====================================================================== consumers
     asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(WS_REGS_CONS));
-    const int r = lane & 3, q = lane >> 2;
+    constexpr int PERM = NF == 4 ? 1 : 2;               // lane group -> column group (sums_common.cuh: bank spreading)
+    const int r = lane & 3, q = lane >> 2, cg = col_group<PERM>(q);
     int ld_off[TS];                                     // byte offset of my chunk inside its 128-byte row (even g)
 #pragma unroll
-    for (int i = 0; i < TS; ++i) ld_off[i] = (((TS * q + i) & 7) ^ r) << 4;
+    for (int i = 0; i < TS; ++i) ld_off[i] = (((TS * cg + i) & 7) ^ r) << 4;
     // screening box 2^k > R: |dx| >= 2^k or |dy| >= 2^k implies d2 >= r2
     const double box = __hiloint2double((__double2hiint(sqrt(r2)) & 0x7ff00000) + 0x00100000, 0);
     const SumsLayout L(T);
@@ -320,7 +325,7 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
         }
         double piv[NF];                                 // pivot of my columns NF q .. NF q + NF - 1
 #pragma unroll
-        for (int i = 0; i < NF; ++i) piv[i] = NF * q + i < 2 * T ? pivot[c * 2 * T + NF * q + i] : 0.0;
+        for (int i = 0; i < NF; ++i) piv[i] = NF * cg + i < 2 * T ? pivot[c * 2 * T + NF * cg + i] : 0.0;
         double acc[NT][2];
 #pragma unroll
         for (int i = 0; i < NT; ++i) acc[i][0] = acc[i][1] = 0.0;
@@ -334,10 +339,10 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
             const int b = (int)(seq % WS_NB);
             const uint32_t use = (uint32_t)(seq / WS_NB);
             mbar_wait(full + b, use & 1);
-            // lane (r, q) reads timesteps TS q + i of row 4 g + r: sub-tile t >> 3, chunk (t & 7) ^ (row & 7);
+            // lane (r, q) reads timesteps TS cg + i of row 4 g + r: sub-tile t >> 3, chunk (t & 7) ^ (row & 7);
             // row & 7 = 4 (g & 1) + r, so the two parities of g differ by bit 6 of the byte offset.
             // Fragments = loads minus the pivot (the only vector FP64 work left in this warp besides S1).
-            const unsigned char* tile = ring + (size_t)b * WL::TILE + ((TS * q) >> 3) * WL::SUB + r * 128;
+            const unsigned char* tile = ring + (size_t)b * WL::TILE + ((TS * cg) >> 3) * WL::SUB + r * 128;
             double f[2][2][NF];                         // [buffer][group of the pair][fragment]
             auto load_pair = [&](int g2, int buf) {
 #pragma unroll
@@ -372,7 +377,7 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
             double v = s1[i];
             v += __shfl_xor_sync(0xffffffffu, v, 1);
             v += __shfl_xor_sync(0xffffffffu, v, 2);
-            if (r == 0) wsm[SM::O_S1 + NF * q + i] = v;            // column NF q + i = 2 t + {x, y}
+            if (r == 0) wsm[SM::O_S1 + NF * cg + i] = v;           // column NF cg + i = 2 t + {x, y}
         }
         cta_bar();                                      // (S3) consumer areas and producer counts are written
         // ---- partial vector of segment (CTA, cell): consumer warps in warp order, then the producers' counts
@@ -385,7 +390,7 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
             if (e == 0) {
                 sum = (double)rows_seg;
             } else if (e < L.o_coll) {
-                const int src = packed_to_area<NF>(e, L, false, false);
+                const int src = packed_to_area<NF, PERM>(e, L, false, false);
 #pragma unroll
                 for (int w = 0; w < WS_CONS; ++w) sum += area[(size_t)w * SM::PW + src];
             } else if (e < L.o_d2s) {                   // coll[T], any, pen[T]: producer counts, warp order

@@ -46,13 +46,4 @@ __device__ __forceinline__ void box_muller(uint32_t r0, uint32_t r1, float& z0, 
     z1 = rad * __sinf(ang);
 }
 
-// float -> double through the integer pipe (exact for zeros and normal floats, which is all a flush-to-zero
-// Box-Muller produces): the F2F.F64.F32 conversion competes with the FP64 chain for the FP64 pipe.
-__device__ __forceinline__ double f32_to_f64_bits(float f) {
-    const uint32_t b = __float_as_uint(f);
-    uint32_t hi = (b & 0x80000000u) | (((b & 0x7fffffffu) >> 3) + 0x38000000u);
-    if ((b & 0x7f800000u) == 0) hi = b & 0x80000000u;
-    return __hiloint2double((int)hi, (int)(b << 29));
-}
-
 }  // namespace ccmpc

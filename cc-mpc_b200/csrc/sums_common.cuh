@@ -51,20 +51,31 @@ __device__ __forceinline__ void store_gram_tiles(double* wsm, const double (&acc
         *reinterpret_cast<double2*>(wsm + ti * 64 + q * 8 + 2 * r) = make_double2(acc[ti][0], acc[ti][1]);
 }
 
+// Lane group q <-> column group (which NF columns of a sample lane group q holds).  stats.cu: identity (a lane
+// loads NF contiguous columns from global memory).  fused.cu reads its fragments from the 128-byte-swizzled
+// shared-memory tile, where the identity makes the two lane groups of a quarter-warp hit the same banks; swapping
+// two bits of q (an involution) spreads them: PERM 1 = bits 0 and 1 (NF = 4), PERM 2 = bits 0 and 2 (NF = 2).
+template <int PERM>
+__device__ __forceinline__ int col_group(int q) {
+    if (PERM == 1) return (q & 4) | ((q & 1) << 1) | ((q >> 1) & 1);
+    if (PERM == 2) return (q & 2) | ((q & 1) << 2) | ((q >> 2) & 1);
+    return q;
+}
+
 // Where element e of the packed sums vector lives inside a SumsWarpArea; -1: e == 0 (the sample count),
 // -2: a slot this kernel does not produce (HAS_YAW / HAS_D2S false).
-template <int NF>
+template <int NF, int PERM = 0>
 __device__ __forceinline__ int packed_to_area(int e, const SumsLayout& L, bool has_yaw, bool has_d2s) {
     using SM = SumsWarpArea<NF>;
     if (e == 0) return -1;
-    if (e < L.o_s2) return SM::O_S1 + (e - L.o_s1);
+    if (e < L.o_s2) return SM::O_S1 + (e - L.o_s1);         // S1 is stored by column, whatever the lane mapping
     if (e < L.o_coll) {
         const int idx = e - L.o_s2;
         int i = (int)((sqrtf(8.0f * (float)idx + 1.0f) - 1.0f) * 0.5f);
         while (i * (i + 1) / 2 > idx) --i;
         while ((i + 1) * (i + 2) / 2 <= idx) ++i;
         const int j = idx - i * (i + 1) / 2;
-        int bi = i % NF, bj = j % NF, m = i / NF, n = j / NF;
+        int bi = i % NF, bj = j % NF, m = col_group<PERM>(i / NF), n = col_group<PERM>(j / NF);
         if (bi < bj) { int t0 = bi; bi = bj; bj = t0; t0 = m; m = n; n = t0; }
         return (bi * (bi + 1) / 2 + bj) * 64 + m * 8 + n;
     }
