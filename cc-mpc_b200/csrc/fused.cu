@@ -414,19 +414,30 @@ __global__ void fused_finalize_kernel(const double* __restrict__ partials, const
     __shared__ int s_list[256], s_cnt;                  // the cell's slots, ascending (G <= 256 SMs)
     const SumsLayout L(T);
     const int64_t c = blockIdx.x;
-    for (int g = threadIdx.x; g < G; g += blockDim.x) s_list[g] = slot_cell[c + g] == (int32_t)c ? 1 : 0;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        int k = 0;
-        for (int g = 0; g < G; ++g)
-            if (s_list[g]) s_list[k++] = g;
-        s_cnt = k;
+    __shared__ unsigned s_bal[8];
+    {                                                   // ordered compaction of the matching slots (warps 0-7 cover G)
+        const int g = threadIdx.x, w = g >> 5, ln = g & 31;
+        const bool flag = g < G && slot_cell[c + g] == (int32_t)c;
+        const unsigned bal = __ballot_sync(0xffffffffu, flag);
+        if (w < 8 && ln == 0) s_bal[w] = bal;
+        __syncthreads();
+        if (w < 8) {
+            int pos = __popc(bal & ((1u << ln) - 1u));
+            for (int k = 0; k < w; ++k) pos += __popc(s_bal[k]);
+            if (flag) s_list[pos] = g;
+        }
+        if (g == 0) {
+            int tot = 0;
+            for (int k = 0; k < 8; ++k) tot += __popc(s_bal[k]);
+            s_cnt = tot;
+        }
     }
     __syncthreads();
     const int cnt = s_cnt;
     for (int j = threadIdx.x; j < L.len; j += blockDim.x) {
         double s = 0.0;
-        for (int k = 0; k < cnt; ++k) s += partials[(c + s_list[k]) * (int64_t)L.len + j];
+#pragma unroll 4
+        for (int k = 0; k < cnt; ++k) s += __ldcs(partials + (c + s_list[k]) * (int64_t)L.len + j);
         s_sum[j] = s;
     }
     __syncthreads();
@@ -567,7 +578,7 @@ extern "C" int ccmpc_mc_rollout_sums(const double* mean, const double* cov, cons
                      : launch_ws<2>(G, st, mean, cov, cross, Tm, x0, C, n, seed, sample_offset, pivot, ego,
                                     ego_cell_stride, R, traj, partials, slot_cell, status, x0_out, Tsh);
     if (rc != CCMPC_OK) return rc;
-    fused_finalize_kernel<<<(unsigned)C, 256, (size_t)L.len * sizeof(double), st>>>(partials, slot_cell, G, Tsh, pivot,
+    fused_finalize_kernel<<<(unsigned)C, 704, (size_t)L.len * sizeof(double), st>>>(partials, slot_cell, G, Tsh, pivot,
                                                                                    ego, ego_cell_stride, sums);
     return check_launch("fused_finalize_kernel");
 }
