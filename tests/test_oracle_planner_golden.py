@@ -178,3 +178,43 @@ def test_episode_cost_matches_reference_cost_final(golden):
         cost, costU = restate.episode_cost(list(g["X"][e, :L]), list(g["U"][e, :L]))
         assert cost == pytest.approx(g["cost"][e], rel=1e-14)
         assert costU == pytest.approx(g["costU"][e], rel=1e-14)
+
+
+def test_reference_predict_ideal_reads_a_pickle_written_by_the_repo(tmp_path, monkeypatch):
+    """The other direction of the `_moments` hand-off, with the reference's OWN reader: ``Moments.nested()`` (the
+    product's writer, run here on CPU tensors) -> pickle -> the reference's unmodified ``predict_ideal``
+    (v8ideal:2620-2711, compiled out of /root/reference by oracle/ref_loader.extract) indexes it as
+    [o][k][t+1] / cross_cov[o][k][t+1][t] and rolls out; the rows it produces equal the restated rollout on the
+    same (replayed) noise.  Needs /root/reference: runs in the build container, skipped on the GPU box."""
+    import torch
+    from oracle import ref_loader
+    if not ref_loader.available():
+        pytest.skip("/root/reference is not present here")
+    from ccmpc_b200 import midlevel, synth
+    from oracle import ref_planner as rp
+    O, K, T = 2, 2, 5
+    sc = synth.make_scene(7, O, K, T)
+    z, pos = synth.sample_scene(sc, 300, 7)
+    flat, offs, co, ck = synth.cells_from_samples(z, pos, K)
+    C = len(co)
+    mean = np.zeros((C, T, 2)); cov = np.zeros((C, T, 2, 2)); cross = np.zeros((C, T, T, 2, 2))
+    for c in range(C):
+        mean[c], cov[c], cross[c] = restate.cell_moments(flat[offs[c]:offs[c + 1]])
+    mom = midlevel.Moments(torch.from_numpy(mean), torch.from_numpy(cov), torch.from_numpy(cross), np.asarray(co),
+                           np.asarray(ck), [K] * O, T)
+    monkeypatch.chdir(tmp_path)
+    os.makedirs("out/data")
+    with open("out/data/agent0_frame40_moments", "wb") as f:
+        pickle.dump(mom.nested(), f)
+    ovs = [rp.FakeOVehicle([np.zeros((1, T, 2))] * K, [np.zeros((1, T))] * K, (3.7, 1.79)) for _ in range(O)]
+    agent = rp.make_agent(T, 0, seed=11)
+    Tsh = T - 1
+    traj_all = agent.predict_ideal(ovs, Tsh, 0, rp.make_params(ovs, 50))          # reads frame 50 - 10
+    x0 = np.concatenate(agent.rnd.x0_draws, axis=0)
+    rs = np.random.RandomState(11)
+    keep = 64
+    for c in range(C):
+        rs.standard_normal((1, 2))
+        Z = np.stack([rs.standard_normal((1_000_000, 2))[:keep] for _ in range(Tsh)], axis=1)
+        ref = restate.ideal_rollout(mean[c], cov[c], cross[c], Tsh, Z, x0[c])
+        np.testing.assert_allclose(traj_all[co[c]][ck[c]][:keep], ref, rtol=1e-14, atol=1e-12)
