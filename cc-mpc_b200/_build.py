@@ -14,7 +14,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libccmpc.so")
 HASH_FILE = os.path.join(HERE, "libccmpc.srchash")
 SOURCES = ["abi.cu", "mvoe.cu", "stats.cu", "rollout.cu", "l4.cu", "cost.cu", "group.cu", "gmm.cu", "risk.cu", "fused.cu", "block.cu"]
-HEADERS = ["common.cuh", "philox.cuh", "rollout.cuh", os.path.join("..", "..", "include", "ccmpc.h")]
+HEADERS = ["common.cuh", "philox.cuh", "rollout.cuh", "sums_common.cuh", "tma.cuh", os.path.join("..", "..", "include", "ccmpc.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

@@ -46,10 +46,9 @@
 // Restrictions of this fast path: Philox noise, no yaw sums.  Any horizon 1..16 (tiles are padded to 8 or 16 steps).
 #include <stdlib.h>
 #include <string.h>
-#include <cuda.h>          // CUtensorMap (types only: the encoder is fetched through cudaGetDriverEntryPoint)
-
 #include "rollout.cuh"
 #include "sums_common.cuh"
+#include "tma.cuh"
 
 namespace ccmpc {
 
@@ -70,37 +69,6 @@ constexpr int WS_NB = 24;                             // tile buffers in the rin
 constexpr int WS_REGS_CONS = 112, WS_REGS_PROD = WS_REGS_PROD_DEF;
 static_assert(WS_PROD % 4 == 0, "setmaxnreg works on whole warpgroups");
 
-// ---- mbarrier / bulk-copy PTX ----------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-    asm volatile("{\n .reg .b64 st;\n mbarrier.arrive.shared::cta.b64 st, [%0];\n}" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-    asm volatile(
-        "{\n .reg .pred p;\n"
-        "WAIT_%=:\n"
-        " mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        " @p bra DONE_%=;\n"
-        " bra WAIT_%=;\n"
-        "DONE_%=:\n}" ::"r"(smem_u32(bar)), "r"(parity)
-        : "memory");
-}
-// one [32 rows][16 doubles] box of the (2 T doubles, n samples, C cells) view of the trajectory tensor
-__device__ __forceinline__ void tma_store_box(const CUtensorMap* map, const void* ssrc, int c0, int c1, int c2) {
-    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"(map),
-                 "r"(smem_u32(ssrc)), "r"(c0), "r"(c1), "r"(c2)
-                 : "memory");
-}
-__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void bulk_wait_read() {
-    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
-}
-__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void cta_bar() { asm volatile("bar.sync 2, %0;" ::"n"(WS_THREADS) : "memory"); }
 
 // EXP: compile-time experiment switches (tools/fused_time.py <exp>): which part of the kernel binds?
@@ -479,7 +447,7 @@ extern "C" size_t ccmpc_mc_rollout_sums_workspace_bytes(int64_t C, int64_t n, in
 // (2 T doubles, n samples, C cells) view of the row-major trajectory tensor, boxes of [32 samples][16 doubles] in
 // the 128-byte swizzle.  cuTensorMapEncodeTiled is a host-side encoder of the driver: fetched through the runtime
 // (no link against libcuda), called once per launch (the map holds the tensor's address and extents).
-static int make_traj_map(CUtensorMap* map, double* traj, int64_t C, int64_t n, int Tsh) {
+int ccmpc::make_traj_map(CUtensorMap* map, double* traj, int64_t C, int64_t n, int Tsh) {
     typedef CUresult (*encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -489,7 +457,7 @@ static int make_traj_map(CUtensorMap* map, double* traj, int64_t C, int64_t n, i
         cudaDriverEntryPointQueryResult q;
         cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q);
         if (e != cudaSuccess || q != cudaDriverEntryPointSuccess || !fn) {
-            set_error("ccmpc_mc_rollout_sums: cuTensorMapEncodeTiled is not available (%s)", cudaGetErrorString(e));
+            set_error("cuTensorMapEncodeTiled is not available (%s)", cudaGetErrorString(e));
             return CCMPC_E_LAUNCH;
         }
         encode = reinterpret_cast<encode_fn>(fn);
@@ -502,7 +470,7 @@ static int make_traj_map(CUtensorMap* map, double* traj, int64_t C, int64_t n, i
                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
-        set_error("ccmpc_mc_rollout_sums: cuTensorMapEncodeTiled failed (CUresult %d; C = %lld, n = %lld)", (int)r,
+        set_error("cuTensorMapEncodeTiled failed (CUresult %d; C = %lld, n = %lld)", (int)r,
                   (long long)C, (long long)n);
         return CCMPC_E_LAUNCH;
     }

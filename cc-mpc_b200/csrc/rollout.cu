@@ -17,7 +17,11 @@
 // once per CTA in shared memory; the (128, Tsh, 2) fp64 output tile is
 // transposed through shared memory so global stores are contiguous 16-byte
 // lanes.  Algorithmic HBM bytes: 16 per (sample, timestep) written.
+#include <stdlib.h>
+#include <string.h>
+
 #include "rollout.cuh"
+#include "tma.cuh"
 
 namespace ccmpc {
 
@@ -30,13 +34,17 @@ constexpr int RO_THREADS = 128;
 #define RO_MIN_CTAS 8
 #endif
 // TSH > 0: compile-time horizon (fully unrolled step loop, shift/mask index math); TSH = 0: runtime Tsh.
-template <int TSH, bool ZIN, bool ZOUT>
+// TMA (TSH = 8 / 16 only): the warp stages its 32 rows x 8 timesteps as ONE [32][128 B] sub-tile in the TMA
+// 128-byte swizzle (conflict-free lane-per-row writes) and one lane stores it with a single cp.async.bulk.tensor -
+// no LDS + STG flush loop through the LSU; the buffer is reused after the bulk copy has read it.
+template <int TSH, bool ZIN, bool ZOUT, bool TMA = false>
 __global__ void __launch_bounds__(RO_THREADS, RO_MIN_CTAS)
 rollout_kernel(const double* __restrict__ mean, const double* __restrict__ cov, const double* __restrict__ cross,
                int Tm, const double* __restrict__ x0, int64_t n, int Tsh_rt, uint32_t seed_lo, uint32_t seed_hi,
                uint64_t sample_offset, const double* __restrict__ z_in, double* __restrict__ traj,
-               double* __restrict__ z_out, uint8_t* __restrict__ status, double* __restrict__ x0_out) {
-    extern __shared__ __align__(16) double smem[];
+               double* __restrict__ z_out, uint8_t* __restrict__ status, double* __restrict__ x0_out,
+               const __grid_constant__ CUtensorMap traj_map) {
+    extern __shared__ __align__(1024) double smem[];
     const int Tsh = TSH > 0 ? TSH : Tsh_rt;
     // timesteps staged between two flushes: half the horizon at TSH = 16 (128 B per row and flush - still whole
     // lines - for half the shared memory, so registers, not the tile, bound the resident warps)
@@ -57,6 +65,9 @@ rollout_kernel(const double* __restrict__ mean, const double* __restrict__ cov, 
     const int lane = tid & 31, w0 = tid & ~31;
     double2* my_stage = stage + tid * stride2;
     const double2* wstage = stage + w0 * stride2;
+    // TMA: per-warp 4 KB sub-tile, 1024-byte aligned (the swizzle pattern is address based)
+    unsigned char* tma_tile = reinterpret_cast<unsigned char*>(smem) + ((Tsh * SP_D * 8 + 1023) / 1024) * 1024 + (tid >> 5) * 4096;
+    unsigned char* tma_row = tma_tile + lane * 128;
     const int64_t ntiles = (n + RO_THREADS - 1) / RO_THREADS;
     for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
     const int64_t i0 = tile * RO_THREADS;
@@ -69,6 +80,17 @@ rollout_kernel(const double* __restrict__ mean, const double* __restrict__ cov, 
 
     // the warp stores the timesteps [tb, tb + cnt) of the 32 rows it staged: contiguous cnt * 16 B per row
     auto flush = [&](int tb, int cnt) {
+        if (TMA) {
+            fence_proxy_async();                 // my generic-proxy writes -> visible to the TMA engine
+            __syncwarp();
+            if (lane == 0) {
+                tma_store_box(&traj_map, tma_tile, 2 * tb, (int)(i0 + w0), (int)c);   // rows past n are clipped
+                bulk_commit();
+                bulk_wait_read<0>();             // the sub-tile is overwritten by the next 8 steps
+            }
+            __syncwarp();
+            return;
+        }
         __syncwarp();
         if (FL > 0 && (32 % (FL > 0 ? FL : 1)) == 0) {
             constexpr int TT = FL > 0 ? FL : 1;
@@ -95,7 +117,8 @@ rollout_kernel(const double* __restrict__ mean, const double* __restrict__ cov, 
     auto step = [&](int t, double zx, double zy) {
         if (ZOUT && valid) zout2[t] = make_double2(zx, zy);
         rollout_step(sp[t], x, y, zx, zy);
-        my_stage[FL > 0 ? (t % FL) : t] = make_double2(x, y);
+        if (TMA) *reinterpret_cast<double2*>(tma_row + (((t & 7) ^ (lane & 7)) << 4)) = make_double2(x, y);
+        else my_stage[FL > 0 ? (t % FL) : t] = make_double2(x, y);
     };
 #pragma unroll
     for (int t2 = 0; t2 < (TSH > 0 ? (TSH + 1) / 2 : (Tsh + 1) / 2); ++t2) {
@@ -121,6 +144,7 @@ rollout_kernel(const double* __restrict__ mean, const double* __restrict__ cov, 
     if (FL > 0) flush(TSH - FL, FL);
     else flush(0, Tsh);
     }   // tiles of this CTA
+    if (TMA && lane == 0) bulk_wait_all();       // every sub-tile has landed before the CTA retires
 }
 
 __global__ void philox_kernel(const uint32_t* __restrict__ ctr, const uint32_t* __restrict__ key, int64_t M,
@@ -150,15 +174,30 @@ extern "C" int ccmpc_mc_rollout(const double* mean, const double* cov, const dou
         cudaError_t e = cudaMemsetAsync(status, 0, (size_t)C, st);
         if (e != cudaSuccess) { set_error("ccmpc_mc_rollout: memset: %s", cudaGetErrorString(e)); return CCMPC_E_LAUNCH; }
     }
-    const size_t smem = (size_t)Tsh * sizeof(StepParams) + (size_t)RO_THREADS * (((Tsh == 16 || Tsh == 8) ? RO_FLUSH : Tsh) | 1) * 16;
+    const bool tma = (Tsh == 16 || Tsh == 8) && RO_FLUSH == 8 && n < ((int64_t)1 << 31) && !getenv("CCMPC_ROLLOUT_NO_TMA");
+    CUtensorMap map;
+    memset(&map, 0, sizeof(map));
+    if (tma) {
+        int rc = make_traj_map(&map, traj, C, n, Tsh);
+        if (rc != CCMPC_OK) return rc;
+    }
+    const size_t smem = tma ? ((size_t)Tsh * sizeof(StepParams) + 1023) / 1024 * 1024 + (RO_THREADS / 32) * 4096
+                            : (size_t)Tsh * sizeof(StepParams) + (size_t)RO_THREADS * (((Tsh == 16 || Tsh == 8) ? RO_FLUSH : Tsh) | 1) * 16;
     // one wave: at most 148 * RO_MIN_CTAS resident CTAs over all cells, each looping over its cell's tiles
     const int64_t ntiles = (n + RO_THREADS - 1) / RO_THREADS;
     const int64_t cap = std::max<int64_t>(1, ((int64_t)sm_count() * RO_MIN_CTAS) / C);
     dim3 grid((unsigned)std::min(ntiles, cap), (unsigned)C);
 #define CCMPC_RO_LAUNCH(TSH, ZI, ZO)                                                                          \
-    rollout_kernel<TSH, ZI, ZO><<<grid, RO_THREADS, smem, st>>>(mean, cov, cross, Tm, x0, n, Tsh, (uint32_t)seed, \
-                                                                (uint32_t)(seed >> 32), sample_offset, z, traj,   \
-                                                                z_out, status, x0_out)
+    do {                                                                                                      \
+        if (tma && TSH > 0)                                                                                   \
+            rollout_kernel<TSH, ZI, ZO, (TSH > 0)><<<grid, RO_THREADS, smem, st>>>(                           \
+                mean, cov, cross, Tm, x0, n, Tsh, (uint32_t)seed, (uint32_t)(seed >> 32), sample_offset, z, traj, \
+                z_out, status, x0_out, map);                                                                  \
+        else                                                                                                  \
+            rollout_kernel<TSH, ZI, ZO, false><<<grid, RO_THREADS, smem, st>>>(                               \
+                mean, cov, cross, Tm, x0, n, Tsh, (uint32_t)seed, (uint32_t)(seed >> 32), sample_offset, z, traj, \
+                z_out, status, x0_out, map);                                                                  \
+    } while (0)
 #define CCMPC_RO_PICK(TSH)                                                                                    \
     do {                                                                                                      \
         if (z && z_out) CCMPC_RO_LAUNCH(TSH, true, true);                                                     \
