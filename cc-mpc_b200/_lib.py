@@ -27,6 +27,8 @@ SIGNATURES = {
     "ccmpc_sums_len": (c_int64, [c_int]),
     "ccmpc_sample_sums_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int]),
     "ccmpc_sample_sums": (c_int, [_P, _P, c_int64, c_int64, c_int, _P, _P, c_int64, c_double, _P, _P, _P, c_size_t, _P]),
+    "ccmpc_sample_sums_static_max_bytes": (c_size_t, []),
+    "ccmpc_sample_sums_static": (c_int, [_P, _P, c_int64, c_int64, c_int, _P, _P, c_int64, c_double, _P, _P, _P]),
     "ccmpc_moments_from_sums": (c_int, [_P, _P, c_int64, c_int, _P, _P, _P, _P, _P, _P, _P]),
     "ccmpc_cell_pivot": (c_int, [_P, _P, c_int64, c_int, _P, _P]),
     "ccmpc_minkowski_halfplanes": (c_int, [_P, _P, _P, c_int64, _P, c_int64, c_int, c_int, c_double, c_double,

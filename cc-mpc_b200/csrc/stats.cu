@@ -583,3 +583,60 @@ extern "C" int ccmpc_cell_pivot(const double* samples, const int64_t* offsets, i
     cell_pivot_kernel<<<(unsigned)((tot + 127) / 128), 128, 0, (cudaStream_t)stream>>>(samples, offsets, C, T, pivot);
     return check_launch("cell_pivot_kernel");
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// ccmpc_sample_sums_static: ccmpc_sample_sums for callers that may not allocate device memory (CUDA graph
+// capture, serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// The workspace (unit table + per-unit partial sums) is a file-scope device array
+// of CCMPC_STATIC_SCRATCH_BYTES: every GPU that loads the library holds it until the process exits.  All calls
+// share it - two calls that overlap on the GPU (different streams, or threads) race on it.  Nothing in it has to
+// start at zero: unit_scan_kernel rewrites the unit table and every partial vector the finalize kernel reads is
+// written by sample_sums_kernel of the same call, so the contents left by the previous call are never read.
+static __device__ __align__(256) unsigned char g_static_scratch[CCMPC_STATIC_SCRATCH_BYTES];
+
+// In host code `g_static_scratch` is only a handle: its device address comes from cudaGetSymbolAddress, once per
+// device, with that device current.
+static void* static_scratch_address(int* rc_out) {
+    constexpr int MAX_DEV = 64;
+    static void* addr[MAX_DEV] = {};
+    *rc_out = CCMPC_OK;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= MAX_DEV) {
+        set_error("ccmpc_sample_sums_static: cudaGetDevice: %s (device %d)", cudaGetErrorString(e), dev);
+        *rc_out = CCMPC_E_LAUNCH;
+        return nullptr;
+    }
+    void* p = __atomic_load_n(&addr[dev], __ATOMIC_ACQUIRE);
+    if (!p) {
+        e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (e != cudaSuccess || !p) {
+            set_error("ccmpc_sample_sums_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+            *rc_out = CCMPC_E_LAUNCH;
+            return nullptr;
+        }
+        __atomic_store_n(&addr[dev], p, __ATOMIC_RELEASE);      // every thread resolves the same address
+    }
+    return p;
+}
+
+extern "C" size_t ccmpc_sample_sums_static_max_bytes(void) { return (size_t)CCMPC_STATIC_SCRATCH_BYTES; }
+
+extern "C" int ccmpc_sample_sums_static(const double* samples, const int64_t* offsets, int64_t n_total, int64_t C,
+                                        int T, const double* pivot, const double* ego, int64_t ego_cell_stride,
+                                        double R, const double* yaws, double* sums, void* stream) {
+    CCMPC_REQUIRE(T >= 1 && T <= CCMPC_MAX_T, "ccmpc_sample_sums_static: need 1 <= T <= %d", CCMPC_MAX_T);
+    CCMPC_REQUIRE(C >= 0 && n_total >= 0, "ccmpc_sample_sums_static: negative size");
+    const size_t need = ccmpc_sample_sums_workspace_bytes(n_total, C, T);
+    if (need > (size_t)CCMPC_STATIC_SCRATCH_BYTES) {
+        set_error("ccmpc_sample_sums_static: n_total = %lld, C = %lld, T = %d needs %zu bytes of scratch, the static "
+                  "array holds %zu: use ccmpc_sample_sums with a caller-owned workspace",
+                  (long long)n_total, (long long)C, T, need, (size_t)CCMPC_STATIC_SCRATCH_BYTES);
+        return CCMPC_E_WORKSPACE;
+    }
+    int rc = CCMPC_OK;
+    void* scratch = static_scratch_address(&rc);
+    if (rc) return rc;
+    return ccmpc_sample_sums(samples, offsets, n_total, C, T, pivot, ego, ego_cell_stride, R, yaws, sums, scratch,
+                             (size_t)CCMPC_STATIC_SCRATCH_BYTES, stream);
+}

@@ -152,6 +152,27 @@ int ccmpc_sample_sums(const double* samples, const int64_t* offsets, int64_t n_t
                       const double* yaws, double* sums, void* workspace, size_t workspace_bytes,
                       void* stream);
 
+/* ccmpc_sample_sums without a caller workspace and without any allocation.
+ * No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same arguments, results and status
+ * codes as ccmpc_sample_sums; the scratch is a static device array of
+ * CCMPC_STATIC_SCRATCH_BYTES inside the library (held by every GPU that loads
+ * the library until the process exits).
+ *   limit: ccmpc_sample_sums_workspace_bytes(n_total, C, T) must not exceed
+ *          CCMPC_STATIC_SCRATCH_BYTES, else CCMPC_E_WORKSPACE (e.g. c2: 0.2 MB,
+ *          c5: 1.0 MB, c3 (8M rows, 32 cells, T=16): 1.5 MB; T=16 with more than
+ *          about 800 cells is too big - use ccmpc_sample_sums there).
+ *   sharing: all calls use the same array; calls that overlap on the GPU
+ *          (two streams, two threads) race - serialise them.  Nothing in the
+ *          array has to be cleared between calls.
+ *   It calls no cudaMalloc / cudaFree / allocating library routine. */
+#define CCMPC_STATIC_SCRATCH_BYTES (4u << 20)
+size_t ccmpc_sample_sums_static_max_bytes(void);
+int ccmpc_sample_sums_static(const double* samples, const int64_t* offsets, int64_t n_total, int64_t C, int T,
+                             const double* pivot, const double* ego, int64_t ego_cell_stride, double R,
+                             const double* yaws, double* sums, void* stream);
+
 /* Moments as save_moments stores them (v8ideal:2586-2606) from the sums:
  *   mean [C,T,2], cov [C,T,2,2], cross [C,T,T,2,2] (cross[t][tau] for tau < t,
  *   = np.cov([x_t,y_t,x_tau,y_tau])[0:2,2:4]; other slots zero),
