@@ -61,7 +61,10 @@ constexpr int WS_CONS = WS_CONS_DEF;                  // consumer warps (whole w
 #endif
 constexpr int WS_PROD = WS_PROD_DEF;                  // producer warps (whole warpgroups)
 constexpr int WS_THREADS = 32 * (WS_CONS + WS_PROD);
-constexpr int WS_NB = 24;                             // tile buffers in the ring
+#ifndef WS_NB_DEF
+#define WS_NB_DEF 24
+#endif
+constexpr int WS_NB = WS_NB_DEF;                      // tile buffers in the ring
 // launch allocation 80 registers x 768 threads; 128 x 112 + 640 x 72 fits it
 #ifndef WS_REGS_PROD_DEF
 #define WS_REGS_PROD_DEF ((WS_CONS == 4 && WS_PROD <= 20) ? 72 : 64)
@@ -72,7 +75,8 @@ static_assert(WS_PROD % 4 == 0, "setmaxnreg works on whole warpgroups");
 __device__ __forceinline__ void cta_bar() { asm volatile("bar.sync 2, %0;" ::"n"(WS_THREADS) : "memory"); }
 
 // EXP: compile-time experiment switches (tools/fused_time.py <exp>): which part of the kernel binds?
-//   bit0 no Gram update, bit1 no A9 predicate, bit2 no Philox / Box-Muller, bit3 no chain.  0 in production.
+//   bit0 no Gram update, bit1 no A9 predicate, bit2 no Philox / Box-Muller, bit3 no chain, bit4 no pivot shift,
+//   bit6 no S1 adds (16 + 64: the consumer is LDS + DMMA only).  0 in production.
 static int g_ws_exp = 0;          // read only when built with -DCCMPC_WS_EXPERIMENTS
 [[maybe_unused]] static int* const g_ws_exp_ref = &g_ws_exp;
 
@@ -330,7 +334,7 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
 #pragma unroll
-                    for (int i = 0; i < NF; ++i) s1[i] += f[buf][h][i];
+                    for (int i = 0; i < NF; ++i) if (!(exp_flags & 64)) s1[i] += f[buf][h][i];
                     if (!(exp_flags & 1)) gram_update<NF>(acc, f[buf][h]);
                 }
             }
@@ -490,6 +494,16 @@ static int launch_ws(int G, cudaStream_t st, const double* mean, const double* c
     if (g_ws_exp == 12) kernel = rollout_sums_ws_kernel<NF, true, 12>;
     if (g_ws_exp == 16) kernel = rollout_sums_ws_kernel<NF, true, 16>;
     if (g_ws_exp == 28) kernel = rollout_sums_ws_kernel<NF, true, 28>;
+    if (g_ws_exp == 64) kernel = rollout_sums_ws_kernel<NF, true, 64>;
+    if (g_ws_exp == 4) kernel = rollout_sums_ws_kernel<NF, true, 4>;
+    if (g_ws_exp == 8) kernel = rollout_sums_ws_kernel<NF, true, 8>;
+    if (g_ws_exp == 6) kernel = rollout_sums_ws_kernel<NF, true, 6>;
+    if (g_ws_exp == 10) kernel = rollout_sums_ws_kernel<NF, true, 10>;
+    if (g_ws_exp == 14) kernel = rollout_sums_ws_kernel<NF, true, 14>;
+    if (g_ws_exp == 84) kernel = rollout_sums_ws_kernel<NF, true, 84>;
+    if (g_ws_exp == 88) kernel = rollout_sums_ws_kernel<NF, true, 88>;
+    if (g_ws_exp == 80) kernel = rollout_sums_ws_kernel<NF, true, 80>;
+    if (g_ws_exp == 92) kernel = rollout_sums_ws_kernel<NF, true, 92>;
 #endif
     {
         cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
