@@ -94,7 +94,7 @@ struct WsLayout {                                     // dynamic shared memory o
     static constexpr size_t O_X0 = O_BAR + 2 * WS_NB * 8;
     static constexpr size_t O_PIV = O_X0 + 16;                                  // double2 pivot[TSH]
     static constexpr size_t O_EGO = O_PIV + (size_t)TSH * 16;                   // double2 ego[TSH]
-    static constexpr size_t O_SCR = O_EGO + (size_t)TSH * 16;                   // uint4 screen[TSH]: kx, wx, ky, wy
+    static constexpr size_t O_SCR = O_EGO + (size_t)TSH * 16;                   // uint4 screen[TSH]: lo_x, w_x, lo_y, w_y
     static constexpr size_t O_PCNT = O_SCR + (size_t)TSH * 16;                  // producer counts [WS_PROD][PC_LEN]
     static constexpr int PC_LEN = 2 * TSH + 2;                                  // coll[T], pen[T], any, pad
     static constexpr size_t BYTES = O_PCNT + (size_t)WS_PROD * PC_LEN * 8;
@@ -194,7 +194,8 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
                     *reinterpret_cast<double2*>(row + (t >> 3) * WL::SUB + (((t & 7) ^ sw) << 4)) = make_double2(x, y);
                     if (!(exp_flags & 2)) {             // A9 screen: integer pipe, no branch (see below)
                         const uint4 k = s_scr[t];
-                        near_mask |= (unsigned)((hi_key(x) - k.x <= k.y) & (hi_key(y) - k.z <= k.w)) << t;
+                        near_mask |= (unsigned)(((uint32_t)__double2hiint(x) - k.x <= k.y) &
+                                                ((uint32_t)__double2hiint(y) - k.z <= k.w)) << t;
                     }
                 };
 #pragma unroll
@@ -289,10 +290,20 @@ rollout_sums_ws_kernel(const double* __restrict__ mean, const double* __restrict
             const double ex = ego[c * ego_cell_stride + 2 * t], ey = ego[c * ego_cell_stride + 2 * t + 1];
             s_piv[t] = make_double2(px, py);
             s_ego[t] = make_double2(ex, ey);
-            // integer screen: key(x) - kx <= wx  <=>  |ex - x| < box (ties in the low word count as near)
+            // integer screen on the raw hi words: hi(x) - lo <= w (unsigned) whenever |ex - x| < box.  The hi word
+            // of a double ascends with the value for positive numbers and with the magnitude for negative ones, so
+            // the window (ex - box, ex + box) maps to one interval of hi words when it lies on one side of zero
+            // (the other sign is >= 2^20 away after the unsigned wrap); a window that holds zero flags every
+            // sample (the exact predicate decides).  No false negatives; ties in the low word count as near.
+            auto window = [&](double e, uint32_t& lo, uint32_t& w) {
+                const double a = e - box, b = e + box;
+                if (a > 0.0) { lo = (uint32_t)__double2hiint(a); w = (uint32_t)__double2hiint(b) - lo; }
+                else if (b < 0.0) { lo = (uint32_t)__double2hiint(b); w = (uint32_t)__double2hiint(a) - lo; }
+                else { lo = 0u; w = 0xffffffffu; }
+            };
             uint4 k;
-            k.x = hi_key(ex - box); k.y = hi_key(ex + box) - k.x;
-            k.z = hi_key(ey - box); k.w = hi_key(ey + box) - k.z;
+            window(ex, k.x, k.y);
+            window(ey, k.z, k.w);
             s_scr[t] = k;
         }
         double piv[NF];                                 // pivot of my columns NF q .. NF q + NF - 1

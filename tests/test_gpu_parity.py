@@ -959,6 +959,36 @@ def test_step_plan_sampler_mode_with_unicycle_dynamics(dev):
         midlevel.StepPlan.from_gmm(V, N, T, pos_last, prediction_horizon=T, Z=Z).run_gmm(pmf, mus, ls, rho, ref_traj=ref, x0=x0)
 
 
+@pytest.mark.parametrize("Tsh,origin", [(16, "first"), (8, "first"), (16, "mid"), (11, "negative")])
+def test_mc_rollout_sums_counts_when_the_ego_plan_is_near_the_origin(dev, Tsh, origin):
+    """The A9 screen of the fused kernel works on the hi words of the coordinates, per sign of the window around the
+    ego: put the ego plan on the origin (windows that hold zero), across it, and in the all-negative quadrant; the
+    counts must stay bit-exact against rollout -> sample_sums (whose screen is built differently)."""
+    from ccmpc_b200 import ops
+    sc, mean, cov, cross = _scene_moments(4, 2, 2, Tsh + 1)
+    C, n = 4, 20_011
+    rng = np.random.default_rng(8)
+    ego = mean[:, 1:Tsh + 1] + rng.normal(size=(C, Tsh, 2)) * 1.0
+    at = {"first": ego[0, 0], "mid": ego[1, Tsh // 2], "negative": ego.max(axis=(0, 1)) + 500.0}[origin]
+    mean, ego = mean - at, ego - at
+    args = (T_(mean, dev), T_(cov, dev), T_(cross, dev))
+    pivot = T_(mean[:, 1:Tsh + 1], dev)
+    traj, _, _, _ = ops.mc_rollout(*args, None, n, Tsh, seed=5)
+    offsets = torch.arange(C + 1, dtype=torch.int64, device=dev) * n
+    want = ops.sample_sums(traj.view(C * n, Tsh, 2), offsets, pivot, ego=T_(ego, dev)).cpu().numpy()
+    traj2, sums, _, _ = ops.mc_rollout_sums(*args, None, n, Tsh, pivot, T_(ego, dev), seed=5)
+    assert torch.equal(traj2, traj)
+    L = ops.sums_layout(Tsh)
+    s = sums.cpu().numpy()
+    assert want[:, L["coll"]:L["coll"] + Tsh].sum() > 0
+    np.testing.assert_array_equal(s[:, L["coll"]:L["pen"]], want[:, L["coll"]:L["pen"]])
+    np.testing.assert_allclose(s[:, L["pen"]:L["d2s"]], want[:, L["pen"]:L["d2s"]], rtol=1e-11, atol=1e-9)
+    # the same predicate in plain torch fp64 (no FMA): d2 = dx*dx + dy*dy < R*R
+    d = T_(ego, dev)[:, None] - traj
+    hit = (d[..., 0] * d[..., 0] + d[..., 1] * d[..., 1]) < ops.R_EV_OV * ops.R_EV_OV
+    np.testing.assert_array_equal(s[:, L["coll"]:L["coll"] + Tsh], hit.sum(dim=1).cpu().numpy())
+
+
 @pytest.mark.parametrize("Tsh", [16, 8])
 def test_mc_rollout_sums_is_independent_of_the_world_size(dev, Tsh):
     """Eight sample shards (sharding.sample_shard, Philox counter = global sample index) rolled out and reduced
