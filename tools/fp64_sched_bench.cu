@@ -60,7 +60,7 @@ int main() {
     long long h[148 * 32];
     printf("# D = DMMA warps per sub-partition, F = chain warps per sub-partition, ilp = independent DFMA chains per F warp\n");
     printf("# cycles per warp-instruction (10 per iteration) seen by each role\n");
-    const int cfg[][3] = {{1, 0, 1}, {2, 0, 1}, {4, 0, 1}, {0, 1, 1}, {0, 4, 1}, {0, 1, 2}, {0, 1, 10}, {0, 4, 10},
+    const int cfg[][3] = {{1, 0, 1}, {2, 0, 1}, {3, 0, 1}, {4, 0, 1}, {6, 0, 1}, {8, 0, 1}, {0, 1, 1}, {0, 4, 1}, {0, 1, 2}, {0, 1, 10}, {0, 4, 10},
                           {1, 1, 1}, {1, 2, 1}, {1, 4, 1}, {2, 4, 1}, {1, 4, 2}, {2, 4, 2}, {1, 4, 10}, {2, 4, 10},
                           {1, 6, 1}, {2, 6, 2}};
     for (auto& c : cfg) {
