@@ -506,6 +506,10 @@ static int launch_ws(int G, cudaStream_t st, const double* mean, const double* c
     if (g_ws_exp == 16) kernel = rollout_sums_ws_kernel<NF, true, 16>;
     if (g_ws_exp == 28) kernel = rollout_sums_ws_kernel<NF, true, 28>;
     if (g_ws_exp == 64) kernel = rollout_sums_ws_kernel<NF, true, 64>;
+    if (g_ws_exp == 5) kernel = rollout_sums_ws_kernel<NF, true, 5>;
+    if (g_ws_exp == 7) kernel = rollout_sums_ws_kernel<NF, true, 7>;
+    if (g_ws_exp == 85) kernel = rollout_sums_ws_kernel<NF, true, 85>;
+    if (g_ws_exp == 87) kernel = rollout_sums_ws_kernel<NF, true, 87>;
     if (g_ws_exp == 4) kernel = rollout_sums_ws_kernel<NF, true, 4>;
     if (g_ws_exp == 8) kernel = rollout_sums_ws_kernel<NF, true, 8>;
     if (g_ws_exp == 6) kernel = rollout_sums_ws_kernel<NF, true, 6>;
