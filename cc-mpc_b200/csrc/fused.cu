@@ -22,7 +22,7 @@
 // else runs in 20 producer warps (`setmaxnreg.dec` to 72): the rollout - a long dependent chain of Philox
 // (integer), Box-Muller (MUFU) and 7 FMAs per step that does not mind waiting for DMMA gaps - and the A9
 // predicate, behind a screen on the INTEGER pipe: a sample whose x or y is at least 4 m (2^k > R) away from the
-// ego cannot be a hit, which the hi words of the doubles decide as unsigned keys; the exact fp64 predicate (the
+// ego cannot be a hit, which an unsigned window on the hi words of the doubles decides; the exact fp64 predicate (the
 // oracle's operation order, no FMA) runs only for the warp-steps that hold a near sample, and the counts live in
 // producer registers (lane t owns timestep t).  A tile = 32 samples x 8 or 16 timesteps, one sample per
 // producer lane, kept as sub-tiles of [32 rows][128 B] in the TMA 128-byte swizzle (16-byte chunk j of row i
