@@ -29,7 +29,15 @@ def _p(t: Optional[torch.Tensor]):
     return None if t is None else ctypes.c_void_p(t.data_ptr())
 
 
+try:                                   # the raw handle of the current stream without building a Stream object
+    _raw_stream, _cur_dev = torch._C._cuda_getCurrentRawStream, torch._C._cuda_getDevice
+except AttributeError:                 # (private helpers of torch; ~10 x cheaper per call than the public path)
+    _raw_stream = _cur_dev = None
+
+
 def _stream():
+    if _raw_stream is not None:
+        return ctypes.c_void_p(_raw_stream(_cur_dev()))
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
