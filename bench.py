@@ -280,8 +280,9 @@ def run_ours(args):
     main = torch.cuda.current_stream()
 
     def step(i, events=None):
-        """One c3 step, device resident: ONE kernel for rollout + store + sums, then (N > 1) the NCCL all-reduce of the
-        packed sums and the moments kernel on the side stream - step i + 1's kernel does not wait for them."""
+        """One c3 step, device resident: ONE kernel for rollout + store + sums, then - on the side stream - (N > 1) the
+        NCCL all-reduce of the packed sums and the moments kernel: step i + 1's kernel does not wait for them (the
+        timed region ends with join(), so every step's reduction and moments are inside it)."""
         b = i & 1
         if done[b] is not None:
             main.wait_event(done[b])                                   # buffer b is free again
@@ -291,14 +292,12 @@ def run_ours(args):
                             sample_offset=sample_offset, workspace=ws, out=traj, sums_out=sums2[b])
         if events:
             events[1].record()
-        if pg is None:
-            mom2[b] = ops.moments_from_sums(sums2[b], pivot, want_yaw=False, out=mom2[b])
-            return
         ready = torch.cuda.Event()
         ready.record(main)
         with torch.cuda.stream(side):
             side.wait_event(ready)
-            sharding.allreduce_sums(sums2[b], group=pg)
+            if pg is not None:
+                sharding.allreduce_sums(sums2[b], group=pg)
             mom2[b] = ops.moments_from_sums(sums2[b], pivot, want_yaw=False, out=mom2[b])
             done[b] = torch.cuda.Event()
             done[b].record(side)
