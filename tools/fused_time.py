@@ -3,7 +3,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from ccmpc_b200 import ops
 from oracle import synth
 dev = torch.device("cuda:0")
-O, K, T, n = 8, 4, 16, 250_000
+O, K, T, n = 8, 4, int(os.environ.get("FT_T", "16")), int(os.environ.get("FT_N", "250000"))
 C = O * K
 sc = synth.make_scene(3, O, K, T + 1)
 m, c, x = (torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in sc.moments())
