@@ -122,6 +122,27 @@ def raise_for_status(status: np.ndarray, populated: Optional[np.ndarray] = None,
             raise exc(f"{msg} ({what}: {hit.shape[0]} row(s), first at index {tuple(int(i) for i in hit[0])})")
 
 
+_PINNED_STAGE: Dict[str, list] = {}       # device -> [pinned uint8 buffer, event of the last copy out of it]
+
+
+def _pinned_stage(device, nbytes: int) -> torch.Tensor:
+    """``nbytes`` of a grow-only pinned host buffer for one packed H2D copy per step.  The previous copy out of the
+    buffer has finished before it is handed out again (event wait); one buffer per device, not thread-safe."""
+    ent = _PINNED_STAGE.setdefault(str(device), [None, None])
+    if ent[1] is not None:
+        ent[1].synchronize()
+    if ent[0] is None or ent[0].numel() < nbytes:
+        ent[0] = torch.empty(max(int(nbytes) * 5 // 4, 1 << 20), dtype=torch.uint8).pin_memory()
+    return ent[0][:max(int(nbytes), 8)]
+
+
+def _pinned_stage_done(device) -> None:
+    """Record that a copy out of the pinned stage was just enqueued on the current stream."""
+    ev = torch.cuda.Event()
+    ev.record()
+    _PINNED_STAGE[str(device)][1] = ev
+
+
 def _h2d(arr: np.ndarray, device, dtype=None) -> torch.Tensor:
     """Host ndarray -> device on the current stream.  Small arrays go from pageable memory (the driver stages them;
     pinning a fresh buffer per call costs more than the copy), large ones through a pinned buffer."""
@@ -201,11 +222,22 @@ class CellBatch:
                 ck.append(k)
         if not pos:
             raise ValueError("no cells")
-        flat = np.concatenate(pos, axis=0)
         offsets_host = np.asarray(offs, dtype=np.int64)
         bboxes = np.stack(bb)
-        return cls(samples=_h2d(flat, device),
-                   yaws=_h2d(np.concatenate(yaw, axis=0), device) if with_yaws else None,
+        # the per-mode arrays are concatenated straight into a reusable PINNED buffer (positions, then yaws) and go to
+        # the device in one asynchronous copy: no temporary, no pageable staging by the driver (2.6 + 1.3 MB at c2)
+        N = int(offs[-1])
+        n_pos, n_yaw = N * T * 2, (N * T if with_yaws else 0)
+        stage = _pinned_stage(device, (n_pos + n_yaw) * 8).view(torch.float64)
+        host = stage.numpy()
+        np.concatenate(pos, axis=0, out=host[:n_pos].reshape(N, T, 2))
+        if with_yaws:
+            np.concatenate(yaw, axis=0, out=host[n_pos:n_pos + n_yaw].reshape(N, T))
+        dev_buf = torch.empty(n_pos + n_yaw, dtype=torch.float64, device=device)
+        dev_buf.copy_(stage[:n_pos + n_yaw], non_blocking=True)
+        _pinned_stage_done(device)
+        return cls(samples=dev_buf[:n_pos].view(N, T, 2),
+                   yaws=dev_buf[n_pos:].view(N, T) if with_yaws else None,
                    offsets=_h2d(offsets_host, device), offsets_host=offsets_host,
                    cell_obstacle=np.asarray(co), cell_mode=np.asarray(ck), n_states=ns,
                    lw_cell=_h2d(bboxes[np.asarray(co)], device), bboxes=bboxes)
