@@ -203,21 +203,27 @@ class CellBatch:
         for o, ov in enumerate(ovehicles):
             ns.append(int(ov.n_states))
             bb.append(np.asarray(getattr(ov, "bbox", BBOX_DEFAULT), dtype=np.float64))
-            for k in range(int(ov.n_states)):
-                p = np.asarray(ov.pred_positions[k], dtype=np.float64)
-                if p.ndim != 3 or p.shape[2] != 2:
+            pp, yy = ov.pred_positions, (ov.pred_yaws if with_yaws else None)
+            for k in range(ns[-1]):
+                p = pp[k]
+                if type(p) is not np.ndarray or p.dtype != np.float64:
+                    p = np.asarray(p, dtype=np.float64)
+                shp = p.shape
+                if len(shp) != 3 or shp[2] != 2:
                     raise ValueError("pred_positions[k] must be (N_k, T, 2)")
                 if T is None:
-                    T = p.shape[1]
-                elif p.shape[1] != T:
+                    T = shp[1]
+                elif shp[1] != T:
                     raise ValueError("all cells must share the horizon T")
                 pos.append(p)
                 if with_yaws:
-                    y = np.asarray(ov.pred_yaws[k], dtype=np.float64)
-                    if y.shape != p.shape[:2]:
+                    y = yy[k]
+                    if type(y) is not np.ndarray or y.dtype != np.float64:
+                        y = np.asarray(y, dtype=np.float64)
+                    if y.shape != shp[:2]:
                         raise ValueError("pred_yaws[k] must be (N_k, T)")
                     yaw.append(y)
-                offs.append(offs[-1] + p.shape[0])
+                offs.append(offs[-1] + shp[0])
                 co.append(o)
                 ck.append(k)
         if not pos:
@@ -588,8 +594,9 @@ class MidlevelConstraints:
         if cells.C == O * Kmax and min(cells.n_states) == Kmax:
             # every obstacle has Kmax modes, cells obstacle-major: [C, T, ...] -> [T, K, O, ...] views, no Python
             # loop over the cells (100 x 8 assignments at c2)
-            tko = np.moveaxis(arr.reshape((O, Kmax) + arr.shape[1:]), (0, 1, 2), (2, 1, 0))
-            return [[list(tko[t, k]) for k in range(Kmax)] for t in range(T)]
+            tko = np.moveaxis(arr.reshape((O, Kmax) + arr.shape[1:]), (0, 1, 2), (2, 1, 0))[:T]
+            flat = list(np.ascontiguousarray(tko).reshape((T * Kmax * O,) + arr.shape[2:]))     # one pass: all views
+            return [[flat[(t * Kmax + k) * O:(t * Kmax + k + 1) * O] for k in range(Kmax)] for t in range(T)]
         out = np.empty((T, Kmax, O), dtype=object).tolist()
         for c, (o, k) in enumerate(zip(cells.cell_obstacle, cells.cell_mode)):
             for t in range(T):
