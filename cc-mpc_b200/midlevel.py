@@ -606,6 +606,8 @@ class MidlevelConstraints:
     @staticmethod
     def _nested_ok(cells: CellBatch, vec: np.ndarray):
         O, Kmax = cells.O, max(cells.n_states)
+        if cells.C == O * Kmax and min(cells.n_states) == Kmax:      # full, obstacle-major: rows of the reshaped vector
+            return [list(row) for row in np.asarray(vec).reshape(O, Kmax)]
         out = np.empty((O, Kmax), dtype=object).tolist()
         for c, (o, k) in enumerate(zip(cells.cell_obstacle, cells.cell_mode)):
             out[o][k] = vec[c]
