@@ -537,9 +537,20 @@ class MidlevelConstraints:
             out.setdefault(int(o), {})[int(k)] = traj[c].cpu().numpy() if as_numpy else traj[c]
         return out
 
-    def _predict_ideal_fused(self, cells: CellBatch, T: int, params, ego_xy, x0=None, n_samples=None, seed=None):
+    @staticmethod
+    def _raise_for_rollout_status(st: np.ndarray) -> None:
+        """What np.linalg.inv / cholesky raise inside predict_ideal (v8ideal:2683, :2699) for a degenerate cell."""
+        if st.any():
+            bad = int(np.nonzero(st)[0][0])
+            raise np.linalg.LinAlgError("Singular matrix" if st[bad] == ops.ST_SINGULAR
+                                        else "Matrix is not positive definite")
+
+    def _predict_ideal_fused(self, cells: CellBatch, T: int, params, ego_xy, x0=None, n_samples=None, seed=None,
+                             check: bool = True):
         """predict_ideal (v8ideal:2620-2711) + the sums the builder needs, in one kernel (ccmpc_mc_rollout_sums).
-        -> (CellBatch of the ideal trajectories, packed sums, pivot).  Raises like :meth:`predict_ideal`."""
+        -> (CellBatch of the ideal trajectories, packed sums, pivot).  Raises like :meth:`predict_ideal`;
+        ``check=False`` leaves the per-cell status on the device (``work.status``) for a caller that reads it
+        with its other results (one synchronisation per step instead of one in the middle of it)."""
         frame = int(getattr(params, "frame", 0)) - self.frame_stride
         moments = self._load_moments(frame, self.ego_vehicle_id)
         if moments.T < T + 1:
@@ -555,11 +566,8 @@ class MidlevelConstraints:
         x0_t = None if x0 is None else _h2d(np.asarray(x0, dtype=np.float64).reshape(len(sel), 2), self.device)
         traj, sums, status, x0_used = ops.mc_rollout_sums(mean, cov, cross, x0_t, n, T, pivot, ego_t, R=self.R,
                                                           seed=seed, workspace=self._fused_ws(len(sel), n, T))
-        st = status.cpu().numpy()
-        if st.any():
-            bad = int(np.nonzero(st)[0][0])
-            raise np.linalg.LinAlgError("Singular matrix" if st[bad] == ops.ST_SINGULAR
-                                        else "Matrix is not positive definite")
+        if check:
+            self._raise_for_rollout_status(status.cpu().numpy())
         work = CellBatch.uniform(traj, co, ck, cells.n_states)
         work.status, work.x0 = status, x0_used
         self.last_ideal = work
@@ -666,7 +674,7 @@ class MidlevelConstraints:
                 # Philox noise: ONE kernel rolls the ideal trajectories out, stores them and reduces them (:824-825
                 # + the moment reads of :893-904 and :960)
                 work, sums_w, pivot_w = self._predict_ideal_fused(cells, T, params, ref_traj if ego is None else ego,
-                                                                 **(ideal_noise or {}))
+                                                                 check=False, **(ideal_noise or {}))
                 out, _, _ = self.minkowski(work, ref_traj, eps_ura, want_violations=want_violations, sums=sums_w,
                                            pivot=pivot_w)
             else:
@@ -683,7 +691,10 @@ class MidlevelConstraints:
         moments = self.moments_of(work, sums_w, pivot_w)
         # ---- one synchronising copy of the small results
         allh = _to_host({**out, "_At": At, "_b0": b0, "_mean": mom["mean"], "_cov": mom["cov"],
-                         "_yaw_mean": mom["yaw_mean"], "_yaw_var": mom["yaw_var"]})
+                         "_yaw_mean": mom["yaw_mean"], "_yaw_var": mom["yaw_var"],
+                         "_ideal_status": getattr(work, "status", None) if work is not cells else None})
+        if "_ideal_status" in allh:
+            self._raise_for_rollout_status(allh["_ideal_status"])                    # predict_ideal's own exceptions first
         host = {k: v for k, v in allh.items() if not k.startswith("_")}
         raise_for_status(host["status"], what="Minkowski builder")                   # :907, :924-926
         A_union = self._nested_tko(cells, allh["_At"], Tpred)

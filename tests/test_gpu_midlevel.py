@@ -331,6 +331,25 @@ def test_c1_at_100k_predictions_matches_oracle(dev, tmp_path):
 
 
 # --------------------------------------------------------------------------- error behaviour, modes
+def test_shrinking_step_with_singular_saved_moments_raises_linalgerror(dev, golden):
+    """predict_ideal inverts cov_p0p1[t] (v8ideal:2683): a saved covariance that is singular raises LinAlgError there.
+    The fused rollout reports it as a per-cell status that the builder reads with its other results at the end of
+    the step - the exception must still be the reference's."""
+    from ccmpc_b200 import midlevel
+    g, K, ovs, _, _ = _c1(golden)
+    T = 8
+    mc = midlevel.MidlevelConstraints(T, ego_vehicle_id=0, out_dir=None, device=dev, n_ideal_samples=4096)
+    mc.compute_obstacle_constraints_GMM_Minkowski_idealprediction(
+        params_of(ovs, 100), ovs, None, None, None, g["s1_eps_ura"], None, T, g["ref_traj"])
+    mc._moments[100].cov[1, 2].zero_()                      # cell 1, timestep 2: Sigma_t = 0
+    with pytest.raises(np.linalg.LinAlgError):
+        mc.compute_obstacle_constraints_GMM_Minkowski_idealprediction(
+            params_of(ovs, 110), ovs, None, None, None, g["s1_eps_ura"], None, T - 1, g["ref_traj"])
+    # the stand-alone method raises at once
+    with pytest.raises(np.linalg.LinAlgError):
+        mc._predict_ideal_fused(midlevel.CellBatch.from_ovehicles(ovs, dev), T - 1, params_of(ovs, 110), g["ref_traj"])
+
+
 def test_degenerate_cells_raise_what_the_reference_raises(dev, golden, tmp_path):
     from ccmpc_b200 import midlevel
     g, K, ovs, _, _ = _c1(golden)
